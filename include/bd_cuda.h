@@ -1,0 +1,55 @@
+/*
+ * bd_cuda.h -- C ABI of the B200 Brownian-dynamics engine (libbd_b200.so).
+ *
+ * Plain pointers and sizes only; no C++ or torch types cross this boundary.  All pointer
+ * arguments are HOST pointers unless a function says otherwise; the engine owns every device
+ * buffer.  One host thread drives one engine handle (the reference is single-threaded and its
+ * forcefield objects are stateful: MD/forcefield/detail/neighbor_list.hpp:232-239).
+ *
+ * The entry points and the reference interface each one replaces are documented in
+ * bd_api_decl.inc; INTEGRATION.md shows the binding the reference side adds.
+ */
+#ifndef BD_CUDA_H
+#define BD_CUDA_H
+
+#include "bd_types.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct bd_engine bd_engine;
+
+#define BD_FN(name) bd_##name
+#define BD_HANDLE bd_engine
+#include "bd_api_decl.inc"
+#undef BD_FN
+#undef BD_HANDLE
+
+/* ---- engine-only controls (no reference counterpart) ------------------------------------ */
+
+/* Run the engine's kernels on an existing CUDA stream (cudaStream_t passed as void*), e.g. the
+ * stream a benchmark records its CUDA events on.  NULL restores the engine's own stream. */
+int bd_set_stream(bd_engine *h, void *cuda_stream);
+/* Block until all work queued by this engine has finished. */
+int bd_sync(bd_engine *h);
+
+/* Tunables.  Names: "verlet_factor" (list radius / dcut, reference value 1.5,
+ * MD/forcefield/detail/neighbor_list.hpp:182), "list_capacity" (ELL row length),
+ * "use_graph" (0/1: replay a captured CUDA graph of steps), "block_size". */
+int bd_set_option(bd_engine *h, const char *name, double value);
+int bd_get_option(bd_engine *h, const char *name, double *value);
+
+/* Device-resident variants used by bench.py's HBM-resident timing: xyz is a DEVICE pointer to
+ * [n_replicas][n_beads][3] doubles in original bead order. */
+int bd_set_positions_device(bd_engine *h, const double *d_xyz);
+int bd_get_positions_device(bd_engine *h, double *d_xyz);
+
+/* Number of kernels launched by this engine since creation (bench.py "gpu_launches"). */
+int bd_get_launch_count(bd_engine *h, int64_t *out);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* BD_CUDA_H */
