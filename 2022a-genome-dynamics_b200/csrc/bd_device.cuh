@@ -1,0 +1,338 @@
+/*
+ * bd_device.cuh -- device-side data layout and arithmetic of the B200 Brownian-dynamics engine.
+ *
+ * Reference algorithm (micromd, header-only C++; MD/ = submodules/github.com/snsinfu/micromd/
+ * include/md/).  Nothing here is translated from it: the reference walks a std::vector pair list
+ * with Newton's-third-law scatter on one CPU thread; this engine keeps beads sorted by cell in
+ * 32-byte records, evaluates every bead's full neighbour row without atomics, and updates the
+ * position in the same pass.
+ *
+ * HBM layout (per engine, R replicas of N beads, Ntot = R*N, "slot" = index in cell-sorted order,
+ * slots [r*N, (r+1)*N) belong to replica r):
+ *   pos[2][Ntot]   bead4 {x, y, z, w}  ping-pong; w packs original index, class, target masks
+ *   bpos[Ntot]     bead4               positions at the last Verlet-list build (same slots)
+ *   slot_of[Ntot]  u32                 original global index -> slot
+ *   nbr[cap][Ntot] u32, nnbr[Ntot]     ELL Verlet rows (both directions), column-major
+ *   bond/bend CSR  by original index   topology, uploaded once
+ */
+#pragma once
+
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "../../include/bd_types.h"
+
+namespace bd {
+
+// ---- records -----------------------------------------------------------------------------------
+
+struct __align__(32) bead4 {
+    double x, y, z;
+    uint64_t w;  // bits 0..31 original index within the replica, 32..39 class,
+                 // 40..47 pair-forcefield target mask, 48..55 point-forcefield target mask
+};
+
+__host__ __device__ inline uint64_t pack_w(uint32_t orig, uint32_t type, uint32_t pair_mask,
+                                           uint32_t point_mask)
+{
+    return (uint64_t) orig | ((uint64_t) (type & 0xff) << 32) | ((uint64_t) (pair_mask & 0xff) << 40)
+        | ((uint64_t) (point_mask & 0xff) << 48);
+}
+__host__ __device__ inline uint32_t w_orig(uint64_t w) { return (uint32_t) w; }
+__host__ __device__ inline uint32_t w_type(uint64_t w) { return (uint32_t) (w >> 32) & 0xff; }
+__host__ __device__ inline uint32_t w_pair_mask(uint64_t w) { return (uint32_t) (w >> 40) & 0xff; }
+__host__ __device__ inline uint32_t w_point_mask(uint64_t w) { return (uint32_t) (w >> 48) & 0xff; }
+
+/* flattened potential term with the constants the kernels need precomputed on the host */
+struct __align__(16) DTerm {
+    int32_t kind, p, q, pad;
+    double factor, energy, length;
+    double cutoff2;  // cutoff^2, 0 = none
+    double k2;       // 1 / length^2
+    double pad2;
+};
+static_assert(sizeof(DTerm) == 64, "DTerm is one 64-byte record");
+
+struct DPair { int32_t enabled, nterms, term_off, has_targets; double dcut, dcut2; };
+struct DBond { int32_t enabled, nterms, term_off, pad; };
+struct DBend { int32_t enabled, pad[3]; };
+struct DWall { int32_t enabled, nterms, term_off, shape, direction, pad[3]; double center[3]; double semi[3]; };
+struct DPoint { int32_t enabled, nterms, term_off, has_targets; double source[3]; double pad; };
+
+/* everything the host may change between steps; uploaded as one block when dirty */
+struct DParams {
+    int32_t ntypes, box_kind;
+    int32_t pad0[2];
+    double period[3], inv_period[3];
+    double mobility[BD_MAX_TYPES];
+    double dcut_max;       // max dcut over enabled pair forcefields (0 = none)
+    double verlet_factor;  // list radius / dcut_max
+    DPair pair[BD_MAX_PAIR_FF];
+    DBond bond[BD_MAX_BOND_FF];
+    DBend bend[BD_MAX_BEND_FF];
+    DWall wall[BD_MAX_WALL_FF];
+    DPoint point[BD_MAX_POINT_FF];
+};
+
+/* cell grid of the current Verlet list; written on the device at every rebuild */
+struct DGrid {
+    double origin[3];
+    double inv_cell[3];
+    int32_t n[3];
+    int32_t bits[3];
+    int32_t totalbits;
+    int32_t pad;
+    double radius;  // list radius the rows were built with
+};
+
+/* device-resident control block: kernels decide on rebuilds without returning to the host */
+struct DControl {
+    uint32_t need_rebuild;   // host request (positions replaced, capacity changed)
+    uint32_t doing_rebuild;  // latched copy for the kernels of one rebuild chain
+    uint32_t overflow;       // beads whose ELL row overflowed (sticky)
+    uint32_t cell_overflow;
+    unsigned long long rebuilds;
+    unsigned long long max_disp2_bits;  // bits of max_i |x_i - x_i(build)|^2, kept by the step kernel
+    unsigned long long listed_entries;  // sum of row lengths at the last build (2 x listed pairs)
+    unsigned long long bbox_lo[3], bbox_hi[3];  // order-preserving encodings of the bounding box
+    DGrid grid;
+};
+
+/* forcefield selection for compute_forces / compute_energy of a single forcefield */
+struct Select {
+    int32_t ff_class;  // BD_FF_ALL or one class
+    int32_t ff;
+};
+
+__device__ inline bool ff_on(Select sel, int cls, int k, int enabled)
+{
+    return sel.ff_class == BD_FF_ALL ? enabled != 0 : (sel.ff_class == cls && sel.ff == k);
+}
+
+// ---- exact fp64 helpers (never contracted into FMA: bucket ids, pair sets and the rebuild
+//      criterion must match the reference bit for bit) -------------------------------------------
+
+struct d3 { double x, y, z; };
+
+__device__ inline double sqnorm_exact(double x, double y, double z)
+{
+    // MD/basic_types/point.hpp:120-127: x*x + y*y + z*z, left to right
+    return __dadd_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)), __dmul_rn(z, z));
+}
+
+__device__ inline double round_mod_exact(double x, double m, double inv_m)
+{
+    // MD/misc/nsearch_detail/math.hpp:34-38: x - nearbyint(x * (1/m)) * m
+    return __dsub_rn(x, __dmul_rn(nearbyint(__dmul_rn(x, inv_m)), m));
+}
+
+__device__ inline double floor_mod_exact(double x, double m, double inv_m)
+{
+    // MD/misc/nsearch_detail/math.hpp:27-31
+    return __dsub_rn(x, __dmul_rn(floor(__dmul_rn(x, inv_m)), m));
+}
+
+/* MD/misc/box.hpp:25-28 (open), :45-51 (periodic): shortest displacement p1 - p2 */
+__device__ inline d3 displacement(const DParams &P, double ax, double ay, double az, double bx,
+                                  double by, double bz)
+{
+    d3 r;
+    r.x = __dsub_rn(ax, bx);
+    r.y = __dsub_rn(ay, by);
+    r.z = __dsub_rn(az, bz);
+    if (P.box_kind == BD_BOX_PERIODIC) {
+        r.x = round_mod_exact(r.x, P.period[0], P.inv_period[0]);
+        r.y = round_mod_exact(r.y, P.period[1], P.inv_period[1]);
+        r.z = round_mod_exact(r.z, P.period[2], P.inv_period[2]);
+    }
+    return r;
+}
+
+// ---- potentials (MD/potential/*.hpp) ------------------------------------------------------------
+
+/* MD/misc/math.hpp:18-33: power by repeated squaring */
+__device__ inline double power_n(int n, double x)
+{
+    if (n == 0) return 1.0;
+    double pw = x;
+    for (int k = n - 1; k > 0; k >>= 1) {
+        if (k & 1) pw *= x;
+        x *= x;
+    }
+    return pw;
+}
+
+/* MD/misc/math.hpp:37-44: x^(n/2) from x^2 */
+__device__ inline double power_sqrt_n(int n, double x2)
+{
+    return (n & 1) ? power_n(n, sqrt(x2)) : power_n(n >> 1, x2);
+}
+
+/* force of one term = scalar(r^2) * r for every kind; returns the scalar times the factor */
+__device__ inline double term_force_scalar(const DTerm &t, double r2)
+{
+    if (t.cutoff2 != 0.0 && r2 >= t.cutoff2) return 0.0;  // MD/potential/cutoff_potential.hpp:42-46
+    double s = 0.0;
+    switch (t.kind) {
+    case BD_TERM_SOFTCORE: {  // MD/potential/softcore_potential.hpp:49-61
+        double const u2 = t.k2 * r2;
+        double const v = power_sqrt_n(t.p - 2, u2);
+        double const g = 1.0 - v * u2;
+        if (g >= 0.0) s = (double) (t.p * t.q) * t.energy * t.k2 * power_n(t.q - 1, g) * v;
+        break;
+    }
+    case BD_TERM_SOFTWELL: {  // MD/potential/softwell_potential.hpp:44-52
+        double const u2 = t.k2 * r2;
+        double const up_2 = power_sqrt_n(t.p - 2, u2);
+        double const v1 = 1.0 + up_2 * u2;
+        s = ((double) (-t.p) * t.energy * t.k2) * up_2 / (v1 * v1);
+        break;
+    }
+    case BD_TERM_HARMONIC:  // MD/potential/harmonic_potential.hpp:29-32
+        s = -t.energy;
+        break;
+    case BD_TERM_SPRING: {  // MD/potential/spring_potential.hpp:32-39
+        double const r1 = sqrt(r2);
+        if (r1 != 0.0) s = t.energy * t.length / r1 - t.energy;
+        break;
+    }
+    case BD_TERM_SEMISPRING: {  // MD/potential/semispring_potential.hpp:37-44
+        double const r1 = sqrt(r2);
+        if (r1 > t.length) s = t.energy * t.length / r1 - t.energy;
+        break;
+    }
+    default:
+        break;
+    }
+    return t.factor * s;
+}
+
+__device__ inline double term_energy(const DTerm &t, double r2)
+{
+    if (t.cutoff2 != 0.0 && r2 >= t.cutoff2) return 0.0;
+    double e = 0.0;
+    switch (t.kind) {
+    case BD_TERM_SOFTCORE: {  // MD/potential/softcore_potential.hpp:35-47
+        double const g = 1.0 - power_sqrt_n(t.p, t.k2 * r2);
+        if (g >= 0.0) e = t.energy * power_n(t.q, g);
+        break;
+    }
+    case BD_TERM_SOFTWELL:  // MD/potential/softwell_potential.hpp:35-42
+        e = -t.energy / (1.0 + power_sqrt_n(t.p, t.k2 * r2));
+        break;
+    case BD_TERM_HARMONIC:  // MD/potential/harmonic_potential.hpp:24-27
+        e = 0.5 * t.energy * r2;
+        break;
+    case BD_TERM_SPRING: {  // MD/potential/spring_potential.hpp:26-30
+        double const u = sqrt(r2) - t.length;
+        e = 0.5 * t.energy * u * u;
+        break;
+    }
+    case BD_TERM_SEMISPRING: {  // MD/potential/semispring_potential.hpp:28-35
+        double const u = sqrt(r2) - t.length;
+        if (u > 0.0) e = 0.5 * t.energy * u * u;
+        break;
+    }
+    default:
+        break;
+    }
+    return t.factor * e;
+}
+
+/* sum_potential / scaled_potential (MD/potential/sum_potential.hpp:32-40) */
+__device__ inline double pot_force_scalar(const DTerm *__restrict__ row, int nterms, double r2)
+{
+    double s = 0.0;
+    for (int k = 0; k < nterms; k++) s += term_force_scalar(row[k], r2);
+    return s;
+}
+
+__device__ inline double pot_energy(const DTerm *__restrict__ row, int nterms, double r2)
+{
+    double e = 0.0;
+    for (int k = 0; k < nterms; k++) e += term_energy(row[k], r2);
+    return e;
+}
+
+// ---- cell keys ----------------------------------------------------------------------------------
+
+/* Morton interleave of cell coordinates with per-axis bit counts */
+__device__ inline uint32_t morton_key(uint32_t cx, uint32_t cy, uint32_t cz, const int32_t bits[3])
+{
+    uint32_t key = 0;
+    int pos = 0;
+    int const maxb = max(bits[0], max(bits[1], bits[2]));
+    for (int i = 0; i < maxb; i++) {
+        if (i < bits[0]) key |= ((cx >> i) & 1u) << pos++;
+        if (i < bits[1]) key |= ((cy >> i) & 1u) << pos++;
+        if (i < bits[2]) key |= ((cz >> i) & 1u) << pos++;
+    }
+    return key;
+}
+
+__device__ inline void cell_coords(const DParams &P, const DGrid &G, double x, double y, double z,
+                                   int c[3])
+{
+    double const v[3] = {x, y, z};
+#pragma unroll
+    for (int d = 0; d < 3; d++) {
+        double u;
+        if (P.box_kind == BD_BOX_PERIODIC) {
+            u = floor_mod_exact(v[d], P.period[d], P.inv_period[d]) * G.inv_cell[d];
+        } else {
+            u = (v[d] - G.origin[d]) * G.inv_cell[d];
+        }
+        int ci = (int) u;
+        ci = ci < 0 ? 0 : ci;
+        ci = ci >= G.n[d] ? G.n[d] - 1 : ci;
+        c[d] = ci;
+    }
+}
+
+/* order-preserving map double -> u64 (for atomicMin/Max bounding boxes) */
+__device__ inline unsigned long long encode_ordered(double v)
+{
+    unsigned long long b = (unsigned long long) __double_as_longlong(v);
+    return (b & 0x8000000000000000ull) ? ~b : (b | 0x8000000000000000ull);
+}
+__device__ inline double decode_ordered(unsigned long long e)
+{
+    unsigned long long b = (e & 0x8000000000000000ull) ? (e & 0x7fffffffffffffffull) : ~e;
+    return __longlong_as_double((long long) b);
+}
+
+// ---- Philox4x32-10 counter-based noise ----------------------------------------------------------
+
+__device__ inline void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1)
+{
+#pragma unroll
+    for (int r = 0; r < 10; r++) {
+        uint32_t const hi0 = __umulhi(0xD2511F53u, c[0]), lo0 = 0xD2511F53u * c[0];
+        uint32_t const hi1 = __umulhi(0xCD9E8D57u, c[2]), lo1 = 0xCD9E8D57u * c[2];
+        uint32_t const n0 = hi1 ^ c[1] ^ k0, n2 = hi0 ^ c[3] ^ k1;
+        c[0] = n0; c[1] = lo1; c[2] = n2; c[3] = lo0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+}
+
+/* three standard normals for (seed, step, replica, original bead index): the stream does not
+ * depend on the sort order, the launch shape or the number of GPUs */
+__device__ inline void philox_normals(uint64_t seed, uint64_t step, uint32_t replica, uint32_t orig,
+                                      double z[3])
+{
+    uint32_t c[4] = {orig, replica, (uint32_t) step, (uint32_t) (step >> 32)};
+    philox4x32_10(c, (uint32_t) seed, (uint32_t) (seed >> 32));
+    float const u1 = __uint2float_rn(c[0]) * 2.3283064365386963e-10f + 1.1641532182693481e-10f;
+    float const u2 = __uint2float_rn(c[1]) * 2.3283064365386963e-10f + 1.1641532182693481e-10f;
+    float const r1 = sqrtf(-2.0f * logf(fminf(u1, 1.0f)));
+    float const r2 = sqrtf(-2.0f * logf(fminf(u2, 1.0f)));
+    float s1, c1, s2, c2;
+    sincospif(__uint2float_rn(c[2]) * 4.6566128730773926e-10f, &s1, &c1);
+    sincospif(__uint2float_rn(c[3]) * 4.6566128730773926e-10f, &s2, &c2);
+    z[0] = (double) (r1 * c1);
+    z[1] = (double) (r1 * s1);
+    z[2] = (double) (r2 * c2);
+    (void) s2;
+}
+
+}  // namespace bd

@@ -1,0 +1,1045 @@
+/*
+ * bd_engine.cu -- host side of libbd_b200.so: the C ABI of include/bd_cuda.h.
+ *
+ * One bd_engine is one md::system (or an ensemble of R replicas of it) whose state lives in HBM.
+ * The host keeps only parameter tables and topology; every per-bead quantity is device-resident
+ * and a run of K steps is K enqueues of [gated rebuild chain] -> [fused step kernel] with no
+ * host synchronisation in between.  There is no CPU fallback: without a CUDA device every entry
+ * point fails.
+ */
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/bd_cuda.h"
+#include "bd_device.cuh"
+#include "bd_nlist.cuh"
+#include "bd_step.cuh"
+
+using namespace bd;
+
+// ---- errors --------------------------------------------------------------------------------------
+
+static thread_local std::string g_error;
+
+static int fail(const std::string &msg)
+{
+    g_error = msg;
+    return 1;
+}
+
+#define CK(call)                                                                                  \
+    do {                                                                                          \
+        cudaError_t const e_ = (call);                                                            \
+        if (e_ != cudaSuccess) {                                                                  \
+            return fail(std::string(#call) + ": " + cudaGetErrorString(e_));                      \
+        }                                                                                         \
+    } while (0)
+
+extern "C" const char *bd_last_error(void)
+{
+    return g_error.c_str();
+}
+
+// ---- engine state --------------------------------------------------------------------------------
+
+template <typename T>
+struct DevBuf {
+    T *p = nullptr;
+    size_t count = 0;
+    cudaError_t alloc(size_t n)
+    {
+        release();
+        count = n;
+        return cudaMalloc((void **) &p, std::max<size_t>(n, 1) * sizeof(T));
+    }
+    void release()
+    {
+        if (p) cudaFree(p);
+        p = nullptr;
+        count = 0;
+    }
+};
+
+struct HostFF {
+    bool used = false;
+    int nterms = 0;
+    int term_off = 0;
+    int cells = 0;  // table rows
+};
+
+struct bd_engine {
+    int device = 0;
+    uint32_t n = 0, replicas = 1, ntot = 0, chunks = 0;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+
+    // per-bead device state
+    DevBuf<bead4> pos[2], bpos;
+    int cur = 0;
+    DevBuf<uint32_t> slot_of, cellkey, rank, stage, cell_count, cell_start, block_sum, nbr, nnbr;
+    uint32_t cell_cap = 0, max_bits = 0, cap = 64;
+    DevBuf<DControl> ctl;
+    DevBuf<DParams> d_params;
+    DevBuf<DTerm> d_terms;
+    DevBuf<double> force, wprev, xyz_stage, wall_partial, wall_out, energy_partial, energy_out, dt_prev, dt_last;
+    DevBuf<unsigned long long> inter_partial, dt_bits, pair_count;
+    DevBuf<uint8_t> d_type, d_pair_mask, d_point_mask;
+    DevBuf<double> replay;
+
+    // topology (device CSR by original index)
+    DevBuf<uint32_t> bond_start, bend_start, bend_adj, triples;
+    DevBuf<uint2> bond_adj;
+    DevBuf<double> bend_energy;
+    DevBuf<uint8_t> bend_ff;
+
+    // host mirrors
+    DParams hp;
+    std::vector<DTerm> hterms;
+    bool params_dirty = true;
+    HostFF pair[BD_MAX_PAIR_FF], bond[BD_MAX_BOND_FF], wall[BD_MAX_WALL_FF], point[BD_MAX_POINT_FF];
+    bool bend_used[BD_MAX_BEND_FF] = {};
+    std::vector<uint8_t> h_type, h_pair_mask, h_point_mask;
+    std::vector<std::vector<uint32_t>> bond_pairs{BD_MAX_BOND_FF};
+    std::vector<std::vector<uint32_t>> bend_triples{BD_MAX_BEND_FF};
+    std::vector<std::vector<double>> bend_energies{BD_MAX_BEND_FF};
+    bool has_types_locked = false;
+
+    // run state
+    double last_dt = 0, last_kT = 0;
+    bool wprev_valid = false;
+    int64_t steps_done = 0;
+    int64_t launches = 0;
+    bool stats_adaptive_last = false;
+};
+
+static int sync_and_check(bd_engine *h);
+
+// ---- small helpers -------------------------------------------------------------------------------
+
+static inline unsigned blocks_for(size_t count, unsigned block)
+{
+    return (unsigned) std::max<size_t>(1, (count + block - 1) / block);
+}
+
+static DTerm make_dterm(const bd_term &t)
+{
+    DTerm d;
+    std::memset(&d, 0, sizeof d);
+    d.kind = t.kind;
+    d.p = t.p;
+    d.q = t.q;
+    d.factor = t.factor;
+    d.energy = t.energy;
+    d.length = t.length;
+    d.cutoff2 = t.cutoff * t.cutoff;
+    d.k2 = t.length != 0.0 ? 1.0 / (t.length * t.length) : 0.0;
+    return d;
+}
+
+static int check_terms(const bd_term *table, size_t count)
+{
+    for (size_t i = 0; i < count; i++) {
+        const bd_term &t = table[i];
+        if (t.kind < BD_TERM_NONE || t.kind > BD_TERM_SEMISPRING) return fail("bd: unknown potential kind");
+        if (t.kind == BD_TERM_SOFTCORE && (t.p < 2 || t.q < 1 || t.p > 64 || t.q > 64))
+            return fail("bd: softcore exponents out of range (need p >= 2, q >= 1)");
+        if (t.kind == BD_TERM_SOFTWELL && (t.p < 2 || t.p > 64)) return fail("bd: softwell exponent out of range");
+        if ((t.kind == BD_TERM_SOFTCORE || t.kind == BD_TERM_SOFTWELL) && !(t.length > 0))
+            return fail("bd: softcore/softwell length must be positive");
+    }
+    return 0;
+}
+
+static int store_table(bd_engine *h, HostFF &ff, int nterms, const bd_term *table, int cells)
+{
+    if (nterms < 1 || nterms > BD_MAX_TERMS) return fail("bd: nterms out of range");
+    if (check_terms(table, (size_t) cells * nterms)) return 1;
+    if (!ff.used) {
+        ff.used = true;
+        ff.nterms = nterms;
+        ff.cells = cells;
+        ff.term_off = (int) h->hterms.size();
+        h->hterms.resize(h->hterms.size() + (size_t) cells * nterms);
+    } else if (ff.nterms != nterms || ff.cells != cells) {
+        return fail("bd: table shape changed");
+    }
+    for (size_t i = 0; i < (size_t) cells * nterms; i++) h->hterms[ff.term_off + i] = make_dterm(table[i]);
+    h->params_dirty = true;
+    h->has_types_locked = true;
+    return 0;
+}
+
+static void refresh_dcut_max(bd_engine *h)
+{
+    double m = 0;
+    for (int k = 0; k < BD_MAX_PAIR_FF; k++)
+        if (h->pair[k].used && h->hp.pair[k].enabled) m = std::max(m, h->hp.pair[k].dcut);
+    h->hp.dcut_max = m;
+}
+
+static int upload_params(bd_engine *h)
+{
+    if (!h->params_dirty) return 0;
+    refresh_dcut_max(h);
+    if (h->d_terms.count < h->hterms.size()) {
+        CK(cudaStreamSynchronize(h->stream));
+        CK(h->d_terms.alloc(std::max<size_t>(64, h->hterms.size() * 2)));
+    }
+    if (!h->hterms.empty())
+        CK(cudaMemcpyAsync(h->d_terms.p, h->hterms.data(), h->hterms.size() * sizeof(DTerm),
+                           cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(h->d_params.p, &h->hp, sizeof(DParams), cudaMemcpyHostToDevice, h->stream));
+    h->params_dirty = false;
+    return 0;
+}
+
+static int request_rebuild(bd_engine *h)
+{
+    static const uint32_t one = 1;
+    CK(cudaMemcpyAsync(&h->ctl.p->need_rebuild, &one, sizeof one, cudaMemcpyHostToDevice, h->stream));
+    return 0;
+}
+
+static int upload_words(bd_engine *h)
+{
+    if (h->n == 0) return 0;
+    CK(cudaMemcpyAsync(h->d_type.p, h->h_type.data(), h->n, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(h->d_pair_mask.p, h->h_pair_mask.data(), h->n, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(h->d_point_mask.p, h->h_point_mask.data(), h->n, cudaMemcpyHostToDevice, h->stream));
+    k_set_words<<<blocks_for(h->ntot, 256), 256, 0, h->stream>>>(
+        h->pos[0].p, h->pos[1].p, h->bpos.p, h->slot_of.p, h->d_type.p, h->d_pair_mask.p,
+        h->d_point_mask.p, h->n, h->ntot);
+    h->launches++;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+/* CSR adjacency of all bond / bend forcefields by original bead index */
+static int upload_topology(bd_engine *h)
+{
+    uint32_t const n = h->n;
+    std::vector<uint32_t> start(n + 1, 0);
+    for (int f = 0; f < BD_MAX_BOND_FF; f++)
+        for (uint32_t v : h->bond_pairs[f]) start[v + 1]++;
+    for (uint32_t i = 0; i < n; i++) start[i + 1] += start[i];
+    std::vector<uint2> adj(start[n]);
+    std::vector<uint32_t> fill(start.begin(), start.end() - 1);
+    for (int f = 0; f < BD_MAX_BOND_FF; f++) {
+        const std::vector<uint32_t> &p = h->bond_pairs[f];
+        for (size_t k = 0; k + 1 < p.size(); k += 2) {
+            uint32_t const i = p[k], j = p[k + 1];
+            adj[fill[i]++] = make_uint2(j, (uint32_t) f);
+            adj[fill[j]++] = make_uint2(i, (uint32_t) f | 0x100u);
+        }
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    CK(h->bond_start.alloc(n + 1));
+    CK(h->bond_adj.alloc(adj.size()));
+    CK(cudaMemcpy(h->bond_start.p, start.data(), (n + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    if (!adj.empty()) CK(cudaMemcpy(h->bond_adj.p, adj.data(), adj.size() * sizeof(uint2), cudaMemcpyHostToDevice));
+
+    std::vector<uint32_t> tri;
+    std::vector<double> ten;
+    std::vector<uint8_t> tff;
+    for (int f = 0; f < BD_MAX_BEND_FF; f++) {
+        tri.insert(tri.end(), h->bend_triples[f].begin(), h->bend_triples[f].end());
+        ten.insert(ten.end(), h->bend_energies[f].begin(), h->bend_energies[f].end());
+        tff.insert(tff.end(), h->bend_energies[f].size(), (uint8_t) f);
+    }
+    std::fill(start.begin(), start.end(), 0u);
+    for (uint32_t v : tri) start[v + 1]++;
+    for (uint32_t i = 0; i < n; i++) start[i + 1] += start[i];
+    std::vector<uint32_t> badj(start[n]);
+    fill.assign(start.begin(), start.end() - 1);
+    for (size_t t = 0; t < ten.size(); t++)
+        for (uint32_t role = 0; role < 3; role++) badj[fill[tri[3 * t + role]]++] = (uint32_t) (t << 2) | role;
+    CK(h->bend_start.alloc(n + 1));
+    CK(h->bend_adj.alloc(badj.size()));
+    CK(h->triples.alloc(tri.size()));
+    CK(h->bend_energy.alloc(ten.size()));
+    CK(h->bend_ff.alloc(tff.size()));
+    CK(cudaMemcpy(h->bend_start.p, start.data(), (n + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    if (!badj.empty()) {
+        CK(cudaMemcpy(h->bend_adj.p, badj.data(), badj.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(h->triples.p, tri.data(), tri.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(h->bend_energy.p, ten.data(), ten.size() * sizeof(double), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(h->bend_ff.p, tff.data(), tff.size(), cudaMemcpyHostToDevice));
+    }
+    return 0;
+}
+
+// ---- lifetime ------------------------------------------------------------------------------------
+
+static int alloc_rows(bd_engine *h)
+{
+    CK(h->nbr.alloc((size_t) h->cap * h->ntot));
+    return 0;
+}
+
+extern "C" int bd_create(int64_t n_beads, int32_t n_replicas, int32_t device, bd_engine **out)
+{
+    if (!out) return fail("bd_create: null output");
+    *out = nullptr;
+    if (n_beads < 0 || n_replicas < 1) return fail("bd_create: bad bead or replica count");
+    if ((double) n_beads * n_replicas >= 4.0e9) return fail("bd_create: more than 2^32 beads");
+    if (n_replicas > 65535) return fail("bd_create: at most 65535 replicas per engine");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail("bd_create: no CUDA device (this engine has no CPU fallback)");
+    if (device < 0 || device >= ndev) return fail("bd_create: bad device ordinal");
+    CK(cudaSetDevice(device));
+
+    bd_engine *h = new bd_engine();
+    h->device = device;
+    h->n = (uint32_t) n_beads;
+    h->replicas = (uint32_t) n_replicas;
+    h->ntot = h->n * h->replicas;
+    h->chunks = blocks_for(h->n, STEP_BLOCK);
+    if (cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete h;
+        return fail("bd_create: cannot create a stream");
+    }
+    h->stream = h->own_stream;
+
+    // Morton bits per replica: about two cells per bead, whole key space within the cell arrays
+    uint32_t bits = 6;
+    while ((1u << bits) < 2u * std::max<uint32_t>(h->n, 1u) && bits < 24) bits++;
+    uint32_t rbits = 0;
+    while ((1u << rbits) < h->replicas) rbits++;
+    if (bits + rbits > 27) bits = 27 - rbits;
+    h->max_bits = bits;
+    h->cell_cap = h->replicas << bits;
+
+    std::memset(&h->hp, 0, sizeof h->hp);
+    h->hp.ntypes = 1;
+    h->hp.box_kind = BD_BOX_OPEN;
+    for (int d = 0; d < 3; d++) h->hp.period[d] = h->hp.inv_period[d] = 1.0;
+    h->hp.mobility[0] = 1.0;  // md::mobility_attribute default (MD/system.hpp:41-44)
+    h->hp.verlet_factor = 1.5;  // MD/forcefield/detail/neighbor_list.hpp:182
+    h->h_type.assign(h->n, 0);
+    h->h_pair_mask.assign(h->n, 0);
+    h->h_point_mask.assign(h->n, 0);
+
+    size_t const nt = h->ntot;
+    bool ok = h->pos[0].alloc(nt) == cudaSuccess && h->pos[1].alloc(nt) == cudaSuccess
+        && h->bpos.alloc(nt) == cudaSuccess && h->slot_of.alloc(nt) == cudaSuccess
+        && h->cellkey.alloc(nt) == cudaSuccess && h->rank.alloc(nt) == cudaSuccess
+        && h->stage.alloc(nt) == cudaSuccess && h->nnbr.alloc(nt) == cudaSuccess
+        && h->cell_count.alloc(h->cell_cap) == cudaSuccess
+        && h->cell_start.alloc((size_t) h->cell_cap + 1) == cudaSuccess
+        && h->block_sum.alloc(h->cell_cap / SCAN_TILE + 2) == cudaSuccess
+        && h->ctl.alloc(1) == cudaSuccess && h->d_params.alloc(1) == cudaSuccess
+        && h->d_terms.alloc(64) == cudaSuccess && h->force.alloc(3 * nt) == cudaSuccess
+        && h->xyz_stage.alloc(3 * (size_t) h->n) == cudaSuccess
+        && h->wall_partial.alloc((size_t) h->replicas * h->chunks * BD_MAX_WALL_FF * WALL_STATS) == cudaSuccess
+        && h->wall_out.alloc((size_t) h->replicas * BD_MAX_WALL_FF * WALL_STATS) == cudaSuccess
+        && h->energy_partial.alloc((size_t) h->replicas * h->chunks) == cudaSuccess
+        && h->energy_out.alloc(h->replicas) == cudaSuccess
+        && h->inter_partial.alloc((size_t) h->replicas * h->chunks) == cudaSuccess
+        && h->dt_bits.alloc(h->replicas) == cudaSuccess && h->dt_prev.alloc(h->replicas) == cudaSuccess
+        && h->dt_last.alloc(h->replicas) == cudaSuccess && h->pair_count.alloc(1) == cudaSuccess
+        && h->d_type.alloc(h->n) == cudaSuccess && h->d_pair_mask.alloc(h->n) == cudaSuccess
+        && h->d_point_mask.alloc(h->n) == cudaSuccess && h->nbr.alloc((size_t) h->cap * nt) == cudaSuccess;
+    if (!ok) {
+        bd_destroy(h);
+        return fail(std::string("bd_create: device allocation failed: ") + cudaGetErrorString(cudaGetLastError()));
+    }
+    cudaMemsetAsync(h->ctl.p, 0, sizeof(DControl), h->stream);
+    cudaMemsetAsync(h->wall_partial.p, 0, h->wall_partial.count * sizeof(double), h->stream);
+    cudaMemsetAsync(h->inter_partial.p, 0, h->inter_partial.count * sizeof(unsigned long long), h->stream);
+    cudaMemsetAsync(h->dt_last.p, 0, h->replicas * sizeof(double), h->stream);
+    cudaMemsetAsync(h->dt_prev.p, 0, h->replicas * sizeof(double), h->stream);
+    if (h->ntot) {
+        k_init_identity<<<blocks_for(h->ntot, 256), 256, 0, h->stream>>>(h->slot_of.p, h->pos[0].p, h->pos[1].p,
+                                                                         h->bpos.p, h->n, h->ntot);
+        h->launches++;
+    }
+    if (upload_topology(h) || request_rebuild(h)) {
+        bd_destroy(h);
+        return 1;
+    }
+    if (cudaStreamSynchronize(h->stream) != cudaSuccess) {
+        bd_destroy(h);
+        return fail("bd_create: device initialisation failed");
+    }
+    *out = h;
+    return 0;
+}
+
+extern "C" int bd_destroy(bd_engine *h)
+{
+    if (!h) return 0;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    for (auto *b : {&h->pos[0], &h->pos[1], &h->bpos}) b->release();
+    for (auto *b : {&h->slot_of, &h->cellkey, &h->rank, &h->stage, &h->cell_count, &h->cell_start,
+                    &h->block_sum, &h->nbr, &h->nnbr, &h->bond_start, &h->bend_start, &h->bend_adj, &h->triples})
+        b->release();
+    for (auto *b : {&h->force, &h->wprev, &h->xyz_stage, &h->wall_partial, &h->wall_out, &h->energy_partial,
+                    &h->energy_out, &h->dt_prev, &h->dt_last, &h->bend_energy, &h->replay})
+        b->release();
+    for (auto *b : {&h->inter_partial, &h->dt_bits, &h->pair_count}) b->release();
+    for (auto *b : {&h->d_type, &h->d_pair_mask, &h->d_point_mask, &h->bend_ff}) b->release();
+    h->ctl.release();
+    h->d_params.release();
+    h->d_terms.release();
+    h->bond_adj.release();
+    if (h->own_stream) cudaStreamDestroy(h->own_stream);
+    delete h;
+    return 0;
+}
+
+// ---- system description --------------------------------------------------------------------------
+
+#define NEED(h)                                                                                   \
+    do {                                                                                          \
+        if (!(h)) return fail("bd: null engine handle");                                          \
+        cudaSetDevice((h)->device);                                                               \
+    } while (0)
+
+extern "C" int bd_set_box(bd_engine *h, int32_t box_kind, const double period[3])
+{
+    NEED(h);
+    if (box_kind != BD_BOX_OPEN && box_kind != BD_BOX_PERIODIC) return fail("bd_set_box: unknown box kind");
+    h->hp.box_kind = box_kind;
+    for (int d = 0; d < 3; d++) {
+        double const p = box_kind == BD_BOX_PERIODIC ? period[d] : 1.0;
+        if (!(p > 0)) return fail("bd_set_box: periods must be positive");
+        h->hp.period[d] = p;
+        h->hp.inv_period[d] = 1 / p;  // MD/misc/nsearch_detail/math.hpp:34-38 multiplies by 1/m
+    }
+    h->params_dirty = true;
+    return request_rebuild(h);
+}
+
+extern "C" int bd_set_types(bd_engine *h, const uint8_t *type, int32_t ntypes, const double *mobility)
+{
+    NEED(h);
+    if (ntypes < 1 || ntypes > BD_MAX_TYPES) return fail("bd_set_types: ntypes out of range");
+    if (h->has_types_locked && ntypes != h->hp.ntypes)
+        return fail("bd_set_types: the number of classes cannot change after forcefields were added");
+    for (uint32_t i = 0; i < h->n; i++)
+        if (type[i] >= ntypes) return fail("bd_set_types: class id out of range");
+    h->hp.ntypes = ntypes;
+    for (int t = 0; t < ntypes; t++) h->hp.mobility[t] = mobility[t];
+    if (h->n) std::memcpy(h->h_type.data(), type, h->n);
+    h->params_dirty = true;
+    return upload_words(h);
+}
+
+extern "C" int bd_set_positions(bd_engine *h, int32_t replica, const double *xyz)
+{
+    NEED(h);
+    if (replica < 0 || (uint32_t) replica >= h->replicas) return fail("bd_set_positions: bad replica");
+    if (h->n == 0) return 0;
+    CK(cudaMemcpyAsync(h->xyz_stage.p, xyz, 3 * (size_t) h->n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    k_scatter_positions<<<blocks_for(h->n, 256), 256, 0, h->stream>>>(h->pos[h->cur].p, h->slot_of.p, h->xyz_stage.p,
+                                                                      (uint32_t) replica * h->n, h->n);
+    h->launches++;
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(h->stream));  // xyz may be pageable and is reused by the caller
+    return request_rebuild(h);
+}
+
+extern "C" int bd_get_positions(bd_engine *h, int32_t replica, double *xyz)
+{
+    NEED(h);
+    if (replica < 0 || (uint32_t) replica >= h->replicas) return fail("bd_get_positions: bad replica");
+    if (h->n) {
+        k_gather_positions<<<blocks_for(h->n, 256), 256, 0, h->stream>>>(h->pos[h->cur].p, h->slot_of.p,
+                                                                         h->xyz_stage.p, (uint32_t) replica * h->n, h->n);
+        h->launches++;
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(xyz, h->xyz_stage.p, 3 * (size_t) h->n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    }
+    return sync_and_check(h);
+}
+
+extern "C" int bd_set_positions_device(bd_engine *h, const double *d_xyz)
+{
+    NEED(h);
+    if (h->ntot == 0) return 0;
+    k_scatter_positions<<<blocks_for(h->ntot, 256), 256, 0, h->stream>>>(h->pos[h->cur].p, h->slot_of.p, d_xyz, 0, h->ntot);
+    h->launches++;
+    CK(cudaGetLastError());
+    return request_rebuild(h);
+}
+
+extern "C" int bd_get_positions_device(bd_engine *h, double *d_xyz)
+{
+    NEED(h);
+    if (h->ntot == 0) return 0;
+    k_gather_positions<<<blocks_for(h->ntot, 256), 256, 0, h->stream>>>(h->pos[h->cur].p, h->slot_of.p, d_xyz, 0, h->ntot);
+    h->launches++;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+static int set_mask_bit(std::vector<uint8_t> &mask, const uint8_t *targets, uint32_t n, int bit)
+{
+    for (uint32_t i = 0; i < n; i++) {
+        mask[i] = (uint8_t) (mask[i] & ~(1u << bit));
+        if (targets && targets[i]) mask[i] |= (uint8_t) (1u << bit);
+    }
+    return 0;
+}
+
+extern "C" int bd_add_pair_ff(bd_engine *h, int32_t nterms, const bd_term *table, double dcut,
+                              const uint8_t *targets, int32_t *ff_out)
+{
+    NEED(h);
+    if (!(dcut > 0)) return fail("bd_add_pair_ff: dcut must be positive");
+    for (int k = 0; k < BD_MAX_PAIR_FF; k++) {
+        if (h->pair[k].used) continue;
+        if (store_table(h, h->pair[k], nterms, table, h->hp.ntypes * h->hp.ntypes)) return 1;
+        DPair &p = h->hp.pair[k];
+        p.enabled = 1;
+        p.nterms = nterms;
+        p.term_off = h->pair[k].term_off;
+        p.has_targets = targets != nullptr;
+        p.dcut = dcut;
+        p.dcut2 = dcut * dcut;
+        set_mask_bit(h->h_pair_mask, targets, h->n, k);
+        *ff_out = k;
+        return upload_words(h);
+    }
+    return fail("bd_add_pair_ff: too many pair forcefields");
+}
+
+extern "C" int bd_update_pair_ff(bd_engine *h, int32_t ff, const bd_term *table, double dcut)
+{
+    NEED(h);
+    if (ff < 0 || ff >= BD_MAX_PAIR_FF || !h->pair[ff].used) return fail("bd_update_pair_ff: bad forcefield id");
+    if (!(dcut > 0)) return fail("bd_update_pair_ff: dcut must be positive");
+    if (table && store_table(h, h->pair[ff], h->pair[ff].nterms, table, h->pair[ff].cells)) return 1;
+    h->hp.pair[ff].dcut = dcut;
+    h->hp.pair[ff].dcut2 = dcut * dcut;
+    h->params_dirty = true;
+    return 0;
+}
+
+extern "C" int bd_add_bond_ff(bd_engine *h, int32_t nterms, const bd_term *table, const uint32_t *pairs,
+                              int64_t m, int32_t *ff_out)
+{
+    NEED(h);
+    if (m < 0) return fail("bd_add_bond_ff: negative pair count");
+    for (int64_t b = 0; b < 2 * m; b++)
+        if (pairs[b] >= h->n) return fail("bd_add_bond_ff: bond index out of range");
+    for (int k = 0; k < BD_MAX_BOND_FF; k++) {
+        if (h->bond[k].used) continue;
+        if (store_table(h, h->bond[k], nterms, table, h->hp.ntypes * h->hp.ntypes)) return 1;
+        DBond &b = h->hp.bond[k];
+        b.enabled = 1;
+        b.nterms = nterms;
+        b.term_off = h->bond[k].term_off;
+        h->bond_pairs[k].assign(pairs, pairs + 2 * m);
+        *ff_out = k;
+        return upload_topology(h);
+    }
+    return fail("bd_add_bond_ff: too many bond forcefields");
+}
+
+extern "C" int bd_update_bond_ff(bd_engine *h, int32_t ff, const bd_term *table)
+{
+    NEED(h);
+    if (ff < 0 || ff >= BD_MAX_BOND_FF || !h->bond[ff].used) return fail("bd_update_bond_ff: bad forcefield id");
+    return store_table(h, h->bond[ff], h->bond[ff].nterms, table, h->bond[ff].cells);
+}
+
+extern "C" int bd_add_bend_ff(bd_engine *h, const uint32_t *triples, const double *bending_energy, int64_t m,
+                              int32_t *ff_out)
+{
+    NEED(h);
+    if (m < 0 || m >= (1ll << 30)) return fail("bd_add_bend_ff: bad triple count");
+    for (int64_t b = 0; b < 3 * m; b++)
+        if (triples[b] >= h->n) return fail("bd_add_bend_ff: triple index out of range");
+    for (int k = 0; k < BD_MAX_BEND_FF; k++) {
+        if (h->bend_used[k]) continue;
+        h->bend_used[k] = true;
+        h->hp.bend[k].enabled = 1;
+        h->bend_triples[k].assign(triples, triples + 3 * m);
+        h->bend_energies[k].assign(bending_energy, bending_energy + m);
+        h->params_dirty = true;
+        *ff_out = k;
+        return upload_topology(h);
+    }
+    return fail("bd_add_bend_ff: too many bending forcefields");
+}
+
+extern "C" int bd_add_wall_ff(bd_engine *h, int32_t shape, int32_t direction, int32_t nterms,
+                              const bd_term *table, const double center[3], const double semiaxes[3],
+                              int32_t *ff_out)
+{
+    NEED(h);
+    if (shape != BD_WALL_SPHERE && shape != BD_WALL_ELLIPSOID) return fail("bd_add_wall_ff: unknown shape");
+    if (direction != BD_WALL_INWARD && direction != BD_WALL_OUTWARD) return fail("bd_add_wall_ff: unknown direction");
+    for (int k = 0; k < BD_MAX_WALL_FF; k++) {
+        if (h->wall[k].used) continue;
+        if (store_table(h, h->wall[k], nterms, table, h->hp.ntypes)) return 1;
+        DWall &w = h->hp.wall[k];
+        w.enabled = 1;
+        w.nterms = nterms;
+        w.term_off = h->wall[k].term_off;
+        w.shape = shape;
+        w.direction = direction;
+        for (int d = 0; d < 3; d++) {
+            w.center[d] = center[d];
+            w.semi[d] = semiaxes[d];
+        }
+        *ff_out = k;
+        return 0;
+    }
+    return fail("bd_add_wall_ff: too many wall forcefields");
+}
+
+extern "C" int bd_update_wall_ff(bd_engine *h, int32_t ff, const bd_term *table, const double center[3],
+                                 const double semiaxes[3])
+{
+    NEED(h);
+    if (ff < 0 || ff >= BD_MAX_WALL_FF || !h->wall[ff].used) return fail("bd_update_wall_ff: bad forcefield id");
+    if (table && store_table(h, h->wall[ff], h->wall[ff].nterms, table, h->wall[ff].cells)) return 1;
+    for (int d = 0; d < 3; d++) {
+        h->hp.wall[ff].center[d] = center[d];
+        h->hp.wall[ff].semi[d] = semiaxes[d];
+    }
+    h->params_dirty = true;
+    return 0;
+}
+
+extern "C" int bd_add_point_ff(bd_engine *h, int32_t nterms, const bd_term *table, const double source[3],
+                               const uint8_t *targets, int32_t *ff_out)
+{
+    NEED(h);
+    for (int k = 0; k < BD_MAX_POINT_FF; k++) {
+        if (h->point[k].used) continue;
+        if (store_table(h, h->point[k], nterms, table, h->hp.ntypes)) return 1;
+        DPoint &p = h->hp.point[k];
+        p.enabled = 1;
+        p.nterms = nterms;
+        p.term_off = h->point[k].term_off;
+        p.has_targets = targets != nullptr;
+        for (int d = 0; d < 3; d++) p.source[d] = source[d];
+        set_mask_bit(h->h_point_mask, targets, h->n, k);
+        *ff_out = k;
+        return upload_words(h);
+    }
+    return fail("bd_add_point_ff: too many point-source forcefields");
+}
+
+extern "C" int bd_set_ff_enabled(bd_engine *h, int32_t ff_class, int32_t ff, int32_t enabled)
+{
+    NEED(h);
+    int32_t *flag = nullptr;
+    switch (ff_class) {
+    case BD_FF_PAIR: if (ff >= 0 && ff < BD_MAX_PAIR_FF && h->pair[ff].used) flag = &h->hp.pair[ff].enabled; break;
+    case BD_FF_BOND: if (ff >= 0 && ff < BD_MAX_BOND_FF && h->bond[ff].used) flag = &h->hp.bond[ff].enabled; break;
+    case BD_FF_BEND: if (ff >= 0 && ff < BD_MAX_BEND_FF && h->bend_used[ff]) flag = &h->hp.bend[ff].enabled; break;
+    case BD_FF_WALL: if (ff >= 0 && ff < BD_MAX_WALL_FF && h->wall[ff].used) flag = &h->hp.wall[ff].enabled; break;
+    case BD_FF_POINT: if (ff >= 0 && ff < BD_MAX_POINT_FF && h->point[ff].used) flag = &h->hp.point[ff].enabled; break;
+    default: break;
+    }
+    if (!flag) return fail("bd_set_ff_enabled: bad forcefield class / id");
+    *flag = enabled != 0;
+    h->params_dirty = true;
+    return 0;
+}
+
+// ---- the step path -------------------------------------------------------------------------------
+
+static NlistArrays nlist_arrays(bd_engine *h)
+{
+    NlistArrays A;
+    A.pos = h->pos[h->cur].p;
+    A.pos_out = h->pos[h->cur].p;
+    A.bpos = h->bpos.p;
+    A.slot_of = h->slot_of.p;
+    A.cellkey = h->cellkey.p;
+    A.rank = h->rank.p;
+    A.stage = h->stage.p;
+    A.cell_count = h->cell_count.p;
+    A.cell_start = h->cell_start.p;
+    A.block_sum = h->block_sum.p;
+    A.nbr = h->nbr.p;
+    A.nnbr = h->nnbr.p;
+    A.ctl = h->ctl.p;
+    A.params = h->d_params.p;
+    A.n = h->n;
+    A.replicas = h->replicas;
+    A.ntot = h->ntot;
+    A.cell_cap = h->cell_cap;
+    A.max_bits = h->max_bits;
+    A.cap = h->cap;
+    return A;
+}
+
+static StepArrays step_arrays(bd_engine *h)
+{
+    StepArrays A;
+    A.pos = h->pos[h->cur].p;
+    A.pos_out = h->pos[h->cur ^ 1].p;
+    A.bpos = h->bpos.p;
+    A.slot_of = h->slot_of.p;
+    A.nbr = h->nbr.p;
+    A.nnbr = h->nnbr.p;
+    A.bond_start = h->bond_start.p;
+    A.bond_adj = h->bond_adj.p;
+    A.bend_start = h->bend_start.p;
+    A.bend_adj = h->bend_adj.p;
+    A.triples = h->triples.p;
+    A.bend_energy = h->bend_energy.p;
+    A.bend_ff = h->bend_ff.p;
+    A.terms = h->d_terms.p;
+    A.params = h->d_params.p;
+    A.ctl = h->ctl.p;
+    A.wall_partial = h->wall_partial.p;
+    A.inter_partial = h->inter_partial.p;
+    A.force = h->force.p;
+    A.wprev = h->wprev.p;
+    A.dt_bits = h->dt_bits.p;
+    A.dt_prev = h->dt_prev.p;
+    A.n = h->n;
+    A.replicas = h->replicas;
+    A.ntot = h->ntot;
+    A.chunks = h->chunks;
+    return A;
+}
+
+/* Enqueue the rebuild chain.  Every kernel returns at once unless k_rebuild_begin latched a
+ * rebuild, so the host never has to know whether the list is still valid. */
+static int enqueue_rebuild_chain(bd_engine *h)
+{
+    if (h->ntot == 0) return 0;
+    if (upload_params(h)) return 1;
+    NlistArrays const A = nlist_arrays(h);
+    cudaStream_t const st = h->stream;
+    unsigned const bead_blocks = blocks_for(h->ntot, NL_BLOCK);
+    unsigned const tile_blocks = blocks_for(h->cell_cap, SCAN_TILE);
+    k_rebuild_begin<<<1, 32, 0, st>>>(h->ctl.p, h->d_params.p);
+    k_bbox_zero<<<std::min(bead_blocks + tile_blocks, 148u * 8u), NL_BLOCK, 0, st>>>(A);
+    k_make_grid<<<1, 32, 0, st>>>(A);
+    k_cell_count<<<bead_blocks, NL_BLOCK, 0, st>>>(A);
+    k_scan_reduce<<<tile_blocks, NL_BLOCK, 0, st>>>(A);
+    k_scan_top<<<1, 1024, 0, st>>>(A);
+    k_scan_down<<<tile_blocks, NL_BLOCK, 0, st>>>(A);
+    k_group<<<bead_blocks, NL_BLOCK, 0, st>>>(A);
+    k_place<<<bead_blocks, NL_BLOCK, 0, st>>>(A);
+    k_rows<<<bead_blocks, NL_BLOCK, 0, st>>>(A);
+    h->launches += 10;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+/* Blocks until the stream is idle and turns sticky device-side conditions into errors. */
+static int sync_and_check(bd_engine *h)
+{
+    CK(cudaStreamSynchronize(h->stream));
+    uint32_t overflow = 0;
+    CK(cudaMemcpy(&overflow, &h->ctl.p->overflow, sizeof overflow, cudaMemcpyDeviceToHost));
+    if (overflow) {
+        char msg[200];
+        std::snprintf(msg, sizeof msg,
+                      "bd: %u neighbour rows exceeded list_capacity=%u; raise it with bd_set_option", overflow, h->cap);
+        return fail(msg);
+    }
+    return 0;
+}
+
+/* Make the list current and make sure no row overflowed; grows the rows when they did. */
+static int prepare_list(bd_engine *h)
+{
+    for (int attempt = 0; attempt < 6; attempt++) {
+        if (enqueue_rebuild_chain(h)) return 1;
+        CK(cudaStreamSynchronize(h->stream));
+        uint32_t overflow = 0;
+        CK(cudaMemcpy(&overflow, &h->ctl.p->overflow, sizeof overflow, cudaMemcpyDeviceToHost));
+        if (!overflow) return 0;
+        h->cap *= 2;
+        if (alloc_rows(h)) return 1;
+        CK(cudaMemset(&h->ctl.p->overflow, 0, sizeof(uint32_t)));
+        if (request_rebuild(h)) return 1;
+    }
+    return fail("bd: neighbour rows keep overflowing (positions degenerate?)");
+}
+
+extern "C" int bd_step(bd_engine *h, const bd_step_config *cfg)
+{
+    NEED(h);
+    if (!cfg) return fail("bd_step: null config");
+    if (cfg->steps < 0 || cfg->first_step < 1) return fail("bd_step: bad step range");
+    if (!(cfg->timestep > 0) || cfg->temperature < 0 || cfg->spacestep < 0) return fail("bd_step: bad parameters");
+    if (h->ntot == 0 || cfg->steps == 0) return 0;
+    bool const adaptive = cfg->spacestep != 0;
+    bool const replay = cfg->replay_normals != nullptr;
+    size_t const per_step = 3 * (size_t) h->ntot;
+    cudaStream_t const st = h->stream;
+
+    if (replay && h->wprev.count == 0) {
+        CK(h->wprev.alloc(per_step));
+        CK(cudaMemsetAsync(h->wprev.p, 0, per_step * sizeof(double), st));
+    }
+    if (cfg->first_step == 1) {
+        // brownian_simulator constructor: previous noise starts at zero (brownian_simulator.hpp:37-40)
+        if (h->wprev.count) CK(cudaMemsetAsync(h->wprev.p, 0, per_step * sizeof(double), st));
+        h->last_dt = cfg->timestep;
+        h->last_kT = cfg->temperature;
+    } else if (replay && !h->wprev_valid) {
+        return fail("bd_step: a replayed run must start at first_step = 1");
+    }
+    h->wprev_valid = replay;
+    if (adaptive) {
+        std::vector<unsigned long long> init(h->replicas);
+        double const max_dt = cfg->timestep;
+        unsigned long long bits;
+        std::memcpy(&bits, &max_dt, sizeof bits);
+        std::fill(init.begin(), init.end(), bits);
+        CK(cudaMemcpyAsync(h->dt_bits.p, init.data(), init.size() * sizeof(bits), cudaMemcpyHostToDevice, st));
+        if (cfg->first_step == 1 || !h->stats_adaptive_last) {
+            // no adaptive history: the previous step (if any) used the fixed timestep
+            std::vector<double> prev(h->replicas, cfg->first_step == 1 ? 0.0 : h->last_dt);
+            CK(cudaMemcpyAsync(h->dt_prev.p, prev.data(), prev.size() * sizeof(double), cudaMemcpyHostToDevice, st));
+        }
+    }
+
+    // replayed normals are staged through a bounded device buffer
+    size_t const max_stage_steps = std::max<size_t>(1, ((size_t) 256 << 20) / (per_step * sizeof(double)));
+    size_t staged_from = 0, staged_count = 0;
+
+    StepScalars S;
+    S.kT = cfg->temperature;
+    S.spacestep = cfg->spacestep;
+    S.seed = cfg->seed;
+    S.adaptive = adaptive;
+    S.replay = nullptr;
+    dim3 const grid(h->chunks, h->replicas);
+    Select const all = {BD_FF_ALL, -1};
+
+    for (int64_t k = 0; k < cfg->steps; k++) {
+        if (replay && (size_t) k >= staged_from + staged_count) {
+            staged_from = (size_t) k;
+            staged_count = std::min<size_t>(max_stage_steps, (size_t) (cfg->steps - k));
+            if (h->replay.count < staged_count * per_step) {
+                CK(cudaStreamSynchronize(st));
+                CK(h->replay.alloc(staged_count * per_step));
+            }
+            CK(cudaStreamSynchronize(st));  // the previous chunk is still being read
+            CK(cudaMemcpyAsync(h->replay.p, cfg->replay_normals + staged_from * per_step,
+                               staged_count * per_step * sizeof(double), cudaMemcpyHostToDevice, st));
+        }
+        if (enqueue_rebuild_chain(h)) return 1;
+        StepArrays const A = step_arrays(h);
+        S.step = cfg->first_step + k;
+        S.dt = cfg->timestep;
+        S.dt_prev = h->last_dt;
+        S.kT_prev = h->last_kT;
+        if (replay) S.replay = h->replay.p + ((size_t) k - staged_from) * per_step;
+        if (!adaptive) {
+            k_step_fused<<<grid, STEP_BLOCK, 0, st>>>(A, S);
+            h->launches += 1;
+        } else {
+            k_force<<<grid, STEP_BLOCK, 0, st>>>(A, S, all);
+            k_integrate<<<grid, STEP_BLOCK, 0, st>>>(A, S);
+            k_dt_rotate<<<blocks_for(h->replicas, 128), 128, 0, st>>>(h->dt_bits.p, h->dt_prev.p, h->dt_last.p,
+                                                                      cfg->timestep, h->replicas);
+            h->launches += 3;
+        }
+        CK(cudaGetLastError());
+        h->cur ^= 1;
+        h->last_dt = cfg->timestep;
+        h->last_kT = cfg->temperature;
+        h->steps_done++;
+    }
+    h->stats_adaptive_last = adaptive;
+    if (replay) return sync_and_check(h);  // the caller's noise buffer must outlive the copies
+    return 0;
+}
+
+extern "C" int bd_get_last_timestep(bd_engine *h, int32_t replica, double *out)
+{
+    NEED(h);
+    if (replica < 0 || (uint32_t) replica >= h->replicas) return fail("bd_get_last_timestep: bad replica");
+    if (!h->stats_adaptive_last) {
+        *out = h->last_dt;
+        return 0;
+    }
+    CK(cudaMemcpyAsync(out, h->dt_last.p + replica, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    return sync_and_check(h);
+}
+
+static int check_select(bd_engine *h, int32_t ff_class, int32_t ff)
+{
+    bool ok = false;
+    switch (ff_class) {
+    case BD_FF_ALL: ok = true; break;
+    case BD_FF_PAIR: ok = ff >= 0 && ff < BD_MAX_PAIR_FF && h->pair[ff].used; break;
+    case BD_FF_BOND: ok = ff >= 0 && ff < BD_MAX_BOND_FF && h->bond[ff].used; break;
+    case BD_FF_BEND: ok = ff >= 0 && ff < BD_MAX_BEND_FF && h->bend_used[ff]; break;
+    case BD_FF_WALL: ok = ff >= 0 && ff < BD_MAX_WALL_FF && h->wall[ff].used; break;
+    case BD_FF_POINT: ok = ff >= 0 && ff < BD_MAX_POINT_FF && h->point[ff].used; break;
+    default: break;
+    }
+    return ok ? 0 : fail("bd: bad forcefield class / id");
+}
+
+extern "C" int bd_compute_forces(bd_engine *h, int32_t replica, int32_t ff_class, int32_t ff, double *out_xyz)
+{
+    NEED(h);
+    if (replica < 0 || (uint32_t) replica >= h->replicas) return fail("bd_compute_forces: bad replica");
+    if (check_select(h, ff_class, ff)) return 1;
+    if (h->ntot == 0) return 0;
+    if (prepare_list(h)) return 1;
+    StepArrays const A = step_arrays(h);
+    StepScalars S;
+    std::memset(&S, 0, sizeof S);
+    Select const sel = {ff_class, ff};
+    k_force<<<dim3(h->chunks, h->replicas), STEP_BLOCK, 0, h->stream>>>(A, S, sel);
+    k_gather_forces<<<blocks_for(h->n, 256), 256, 0, h->stream>>>(h->force.p, h->slot_of.p, h->xyz_stage.p,
+                                                                  (uint32_t) replica * h->n, h->n);
+    h->launches += 2;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out_xyz, h->xyz_stage.p, 3 * (size_t) h->n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    return sync_and_check(h);
+}
+
+extern "C" int bd_compute_energy(bd_engine *h, int32_t replica, int32_t ff_class, int32_t ff, double *out)
+{
+    NEED(h);
+    if (replica < 0 || (uint32_t) replica >= h->replicas) return fail("bd_compute_energy: bad replica");
+    if (check_select(h, ff_class, ff)) return 1;
+    *out = 0;
+    if (h->ntot == 0) return 0;
+    if (prepare_list(h)) return 1;
+    StepArrays const A = step_arrays(h);
+    Select const sel = {ff_class, ff};
+    k_energy<<<dim3(h->chunks, h->replicas), STEP_BLOCK, 0, h->stream>>>(A, sel, h->energy_partial.p);
+    k_reduce_partials<<<h->replicas, 32, 0, h->stream>>>(h->energy_partial.p, h->energy_out.p, h->chunks, 1);
+    h->launches += 2;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out, h->energy_out.p + replica, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    return sync_and_check(h);
+}
+
+extern "C" int bd_get_wall_stats(bd_engine *h, int32_t ff, int32_t replica, double out[4])
+{
+    NEED(h);
+    if (ff < 0 || ff >= BD_MAX_WALL_FF || !h->wall[ff].used) return fail("bd_get_wall_stats: bad forcefield id");
+    if (replica < 0 || (uint32_t) replica >= h->replicas) return fail("bd_get_wall_stats: bad replica");
+    for (int c = 0; c < 4; c++) out[c] = 0;
+    if (h->ntot == 0) return 0;
+    unsigned const width = BD_MAX_WALL_FF * WALL_STATS;
+    k_reduce_partials<<<h->replicas, 32, 0, h->stream>>>(h->wall_partial.p, h->wall_out.p, h->chunks, width);
+    h->launches += 1;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out, h->wall_out.p + (size_t) replica * width + (size_t) ff * WALL_STATS,
+                       WALL_STATS * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    return sync_and_check(h);
+}
+
+extern "C" int bd_get_neighbor_list(bd_engine *h, int32_t replica, uint32_t *pairs_out, int64_t cap,
+                                    int64_t *count_out)
+{
+    NEED(h);
+    if (replica < 0 || (uint32_t) replica >= h->replicas) return fail("bd_get_neighbor_list: bad replica");
+    *count_out = 0;
+    if (h->ntot == 0) return 0;
+    if (prepare_list(h)) return 1;
+    DevBuf<uint32_t> d_pairs;
+    CK(d_pairs.alloc(2 * (size_t) std::max<int64_t>(cap, 1)));
+    CK(cudaMemsetAsync(h->pair_count.p, 0, sizeof(unsigned long long), h->stream));
+    k_export_pairs<<<blocks_for(h->n, NL_BLOCK), NL_BLOCK, 0, h->stream>>>(
+        nlist_arrays(h), (uint32_t) replica, d_pairs.p, (unsigned long long) std::max<int64_t>(cap, 0), h->pair_count.p);
+    h->launches += 1;
+    unsigned long long count = 0;
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&count, h->pair_count.p, sizeof count, cudaMemcpyDeviceToHost, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    if (e == cudaSuccess && cap > 0)
+        e = cudaMemcpy(pairs_out, d_pairs.p, 2 * (size_t) std::min<unsigned long long>(count, (unsigned long long) cap) * sizeof(uint32_t),
+                       cudaMemcpyDeviceToHost);
+    d_pairs.release();
+    if (e != cudaSuccess) return fail(std::string("bd_get_neighbor_list: ") + cudaGetErrorString(e));
+    *count_out = (int64_t) count;
+    return 0;
+}
+
+extern "C" int bd_get_counters(bd_engine *h, bd_counters *out)
+{
+    NEED(h);
+    std::memset(out, 0, sizeof *out);
+    if (sync_and_check(h)) return 1;
+    DControl c;
+    CK(cudaMemcpy(&c, h->ctl.p, sizeof c, cudaMemcpyDeviceToHost));
+    std::vector<unsigned long long> part(h->inter_partial.count);
+    if (!part.empty())
+        CK(cudaMemcpy(part.data(), h->inter_partial.p, part.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    unsigned long long inter = 0;
+    for (unsigned long long v : part) inter += v;
+    out->steps_done = h->steps_done;
+    out->list_rebuilds = (int64_t) c.rebuilds;
+    out->pair_interactions = (int64_t) inter;
+    out->listed_pairs = (int64_t) (c.listed_entries / 2);
+    out->overflow_beads = c.overflow;
+    return 0;
+}
+
+// ---- engine-only controls ------------------------------------------------------------------------
+
+extern "C" int bd_set_stream(bd_engine *h, void *cuda_stream)
+{
+    NEED(h);
+    CK(cudaStreamSynchronize(h->stream));
+    h->stream = cuda_stream ? (cudaStream_t) cuda_stream : h->own_stream;
+    return 0;
+}
+
+extern "C" int bd_sync(bd_engine *h)
+{
+    NEED(h);
+    return sync_and_check(h);
+}
+
+extern "C" int bd_set_option(bd_engine *h, const char *name, double value)
+{
+    NEED(h);
+    std::string const key = name ? name : "";
+    if (key == "verlet_factor") {
+        if (!(value >= 1.0)) return fail("bd_set_option: verlet_factor must be >= 1");
+        h->hp.verlet_factor = value;
+        h->params_dirty = true;
+        return request_rebuild(h);
+    }
+    if (key == "list_capacity") {
+        if (!(value >= 1 && value <= 4096)) return fail("bd_set_option: list_capacity out of range");
+        CK(cudaStreamSynchronize(h->stream));
+        h->cap = (uint32_t) value;
+        if (alloc_rows(h)) return 1;
+        CK(cudaMemset(&h->ctl.p->overflow, 0, sizeof(uint32_t)));
+        return request_rebuild(h);
+    }
+    return fail("bd_set_option: unknown option '" + key + "'");
+}
+
+extern "C" int bd_get_option(bd_engine *h, const char *name, double *value)
+{
+    NEED(h);
+    std::string const key = name ? name : "";
+    if (key == "verlet_factor") *value = h->hp.verlet_factor;
+    else if (key == "list_capacity") *value = h->cap;
+    else if (key == "block_size") *value = STEP_BLOCK;
+    else return fail("bd_get_option: unknown option '" + key + "'");
+    return 0;
+}
+
+extern "C" int bd_get_launch_count(bd_engine *h, int64_t *out)
+{
+    NEED(h);
+    *out = h->launches;
+    return 0;
+}
+
+int bd_internal_fail(const char *msg)
+{
+    return fail(msg);
+}

@@ -1,0 +1,394 @@
+/*
+ * bd_nlist.cuh -- GPU cell list and Verlet neighbour rows.
+ *
+ * Replaces md::neighbor_list<Box> + md::neighbor_searcher<Box> + search_grid
+ * (MD/forcefield/detail/neighbor_list.hpp:63-239, MD/misc/neighbor_searcher.hpp:23-131,
+ * MD/misc/nsearch_detail/search_grid.hpp:67-295).  The reference hashes beads into
+ * std::vector buckets and emits a std::pair list on the host; here a rebuild is a chain of kernels
+ * that never returns to the host: bounding box -> grid -> counting sort by (replica, Morton cell
+ * key) with a deterministic in-cell order -> ELL rows.  Every kernel of the chain is gated on a
+ * device-side flag, so the step loop can enqueue the chain unconditionally.
+ *
+ * What is kept bit-for-bit from the reference: the list radius 1.5*dcut (neighbor_list.hpp:182),
+ * the fp64 distance test r^2 <= radius^2 on the build positions (neighbor_searcher.hpp:81-92) and
+ * the rebuild criterion (neighbor_list.hpp:132-158), so the listed pair SET equals the reference's.
+ */
+#pragma once
+
+#include "bd_device.cuh"
+
+namespace bd {
+
+constexpr int NL_BLOCK = 256;
+constexpr int SCAN_ITEMS = 8;                       // counts per thread in the scan kernels
+constexpr int SCAN_TILE = NL_BLOCK * SCAN_ITEMS;    // 2048 counts per block
+
+struct NlistArrays {
+    const bead4 *pos;        // current positions (slot order of the previous build)
+    bead4 *pos_out;          // == pos buffer, rewritten in the new slot order by k_rows
+    bead4 *bpos;             // build positions, new slot order
+    uint32_t *slot_of;       // [Ntot]
+    uint32_t *cellkey;       // [Ntot] key of the bead at OLD slot
+    uint32_t *rank;          // [Ntot] arrival rank within the cell
+    uint32_t *stage;         // [Ntot] old slot, grouped by cell
+    uint32_t *cell_count;    // [cell_cap]
+    uint32_t *cell_start;    // [cell_cap + 1]
+    uint32_t *block_sum;     // [cell_cap / SCAN_TILE + 1]
+    uint32_t *nbr;           // [cap][Ntot]
+    uint32_t *nnbr;          // [Ntot]
+    DControl *ctl;
+    const DParams *params;
+    uint32_t n;              // beads per replica
+    uint32_t replicas;
+    uint32_t ntot;
+    uint32_t cell_cap;       // capacity of cell arrays (power of two)
+    uint32_t max_bits;       // Morton bits available per replica
+    uint32_t cap;            // ELL row capacity
+};
+
+/* decide whether this chain rebuilds the list (neighbor_list.hpp:101-159) and latch the answer:
+ * a host request (new positions), a list radius that no longer covers dcut, or a bead that has
+ * moved further than (radius - dcut)/2 from its build position */
+__global__ void k_rebuild_begin(DControl *ctl, const DParams *params)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    uint32_t need = ctl->need_rebuild;
+    double const dcut = params->dcut_max;
+    if (dcut > 0.0) {
+        double const thr = __dmul_rn(__dsub_rn(ctl->grid.radius, dcut), 0.5);
+        double const moved2 = __longlong_as_double((long long) ctl->max_disp2_bits);
+        if (thr <= 0.0 || moved2 > __dmul_rn(thr, thr)) need = 1;
+    }
+    ctl->doing_rebuild = need;
+    ctl->need_rebuild = 0;
+    if (need) {
+        ctl->rebuilds += 1;
+        ctl->listed_entries = 0;
+        ctl->max_disp2_bits = 0;
+        for (int d = 0; d < 3; d++) {
+            ctl->bbox_lo[d] = ~0ull;
+            ctl->bbox_hi[d] = 0ull;
+        }
+    }
+}
+
+/* bounding box of all replicas (open box) and zero-fill of the cell counters */
+__global__ void __launch_bounds__(NL_BLOCK) k_bbox_zero(NlistArrays A)
+{
+    if (!A.ctl->doing_rebuild) return;
+    uint32_t const tid = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t const stride = gridDim.x * blockDim.x;
+    for (uint32_t c = tid; c < A.cell_cap; c += stride) A.cell_count[c] = 0;
+
+    unsigned long long lo[3] = {~0ull, ~0ull, ~0ull}, hi[3] = {0, 0, 0};
+    for (uint32_t s = tid; s < A.ntot; s += stride) {
+        bead4 const b = A.pos[s];
+        double const v[3] = {b.x, b.y, b.z};
+#pragma unroll
+        for (int d = 0; d < 3; d++) {
+            unsigned long long const e = encode_ordered(v[d]);
+            lo[d] = e < lo[d] ? e : lo[d];
+            hi[d] = e > hi[d] ? e : hi[d];
+        }
+    }
+#pragma unroll
+    for (int d = 0; d < 3; d++) {
+        for (int o = 16; o > 0; o >>= 1) {
+            unsigned long long const l2 = __shfl_xor_sync(0xffffffffu, lo[d], o);
+            unsigned long long const h2 = __shfl_xor_sync(0xffffffffu, hi[d], o);
+            lo[d] = l2 < lo[d] ? l2 : lo[d];
+            hi[d] = h2 > hi[d] ? h2 : hi[d];
+        }
+    }
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int d = 0; d < 3; d++) {
+            atomicMin(&A.ctl->bbox_lo[d], lo[d]);
+            atomicMax(&A.ctl->bbox_hi[d], hi[d]);
+        }
+    }
+}
+
+/* choose the grid: cell edge >= list radius, Morton bits within the cell-array capacity */
+__global__ void k_make_grid(NlistArrays A)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    DControl *ctl = A.ctl;
+    if (!ctl->doing_rebuild) return;
+    const DParams &P = *A.params;
+    DGrid &G = ctl->grid;
+    double radius = __dmul_rn(P.verlet_factor, P.dcut_max);  // neighbor_list.hpp:182
+    G.radius = radius;
+    double const edge = radius > 0 ? radius * (1.0 + 1e-9) : 1.0;
+    double extent[3];
+    for (int d = 0; d < 3; d++) {
+        if (P.box_kind == BD_BOX_PERIODIC) {
+            G.origin[d] = 0;
+            extent[d] = P.period[d];
+        } else {
+            double const lo = decode_ordered(ctl->bbox_lo[d]), hi = decode_ordered(ctl->bbox_hi[d]);
+            G.origin[d] = lo;
+            extent[d] = (hi - lo) * (1.0 + 1e-12) + 1e-12;
+        }
+        double const cells = floor(extent[d] / edge);
+        int n = cells < 1.0 ? 1 : (cells > 1048576.0 ? 1048576 : (int) cells);
+        int b = 0;
+        while ((1 << b) < n) b++;
+        G.n[d] = n;
+        G.bits[d] = b;
+    }
+    // shed bits from the finest axis until the key fits
+    while (G.bits[0] + G.bits[1] + G.bits[2] > (int) A.max_bits) {
+        int d = 0;
+        if (G.bits[1] > G.bits[d]) d = 1;
+        if (G.bits[2] > G.bits[d]) d = 2;
+        G.bits[d] -= 1;
+        if (G.n[d] > (1 << G.bits[d])) G.n[d] = 1 << G.bits[d];
+    }
+    G.totalbits = G.bits[0] + G.bits[1] + G.bits[2];
+    for (int d = 0; d < 3; d++) G.inv_cell[d] = (double) G.n[d] / extent[d];
+}
+
+__device__ inline uint32_t bead_cell_key(const DParams &P, const DGrid &G, const bead4 &b,
+                                         uint32_t replica)
+{
+    int c[3];
+    cell_coords(P, G, b.x, b.y, b.z, c);
+    return (replica << G.totalbits) | morton_key(c[0], c[1], c[2], G.bits);
+}
+
+__global__ void __launch_bounds__(NL_BLOCK) k_cell_count(NlistArrays A)
+{
+    if (!A.ctl->doing_rebuild) return;
+    uint32_t const s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= A.ntot) return;
+    uint32_t const key = bead_cell_key(*A.params, A.ctl->grid, A.pos[s], s / A.n);
+    A.cellkey[s] = key;
+    A.rank[s] = atomicAdd(&A.cell_count[key], 1u);
+}
+
+/* ---- exclusive scan of cell_count[0 .. replicas << totalbits) -> cell_start --------------- */
+
+__device__ inline uint32_t ncells_total(const NlistArrays &A)
+{
+    return A.replicas << A.ctl->grid.totalbits;
+}
+
+__global__ void __launch_bounds__(NL_BLOCK) k_scan_reduce(NlistArrays A)
+{
+    if (!A.ctl->doing_rebuild) return;
+    uint32_t const ncell = ncells_total(A);
+    uint32_t const base = blockIdx.x * SCAN_TILE;
+    if (base >= ncell) return;
+    uint32_t sum = 0;
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        uint32_t const i = base + k * NL_BLOCK + threadIdx.x;
+        sum += i < ncell ? A.cell_count[i] : 0u;
+    }
+    __shared__ uint32_t warp_sum[NL_BLOCK / 32];
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if ((threadIdx.x & 31) == 0) warp_sum[threadIdx.x >> 5] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+        for (int w = 0; w < NL_BLOCK / 32; w++) t += warp_sum[w];
+        A.block_sum[blockIdx.x] = t;
+    }
+}
+
+/* one block: exclusive scan of the per-tile sums */
+__global__ void __launch_bounds__(1024) k_scan_top(NlistArrays A)
+{
+    if (!A.ctl->doing_rebuild) return;
+    uint32_t const ncell = ncells_total(A);
+    uint32_t const ntile = (ncell + SCAN_TILE - 1) / SCAN_TILE;
+    __shared__ uint32_t warp_tot[32];
+    __shared__ uint32_t carry_s;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < ntile; base += 1024) {
+        uint32_t const i = base + threadIdx.x;
+        uint32_t const v = i < ntile ? A.block_sum[i] : 0u;
+        uint32_t incl = v;
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t const t = __shfl_up_sync(0xffffffffu, incl, o);
+            if ((threadIdx.x & 31) >= o) incl += t;
+        }
+        if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = incl;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            uint32_t w = warp_tot[threadIdx.x];
+            for (int o = 1; o < 32; o <<= 1) {
+                uint32_t const t = __shfl_up_sync(0xffffffffu, w, o);
+                if (threadIdx.x >= o) w += t;
+            }
+            warp_tot[threadIdx.x] = w;  // inclusive totals of warps
+        }
+        __syncthreads();
+        uint32_t const warp_off = (threadIdx.x >> 5) ? warp_tot[(threadIdx.x >> 5) - 1] : 0u;
+        uint32_t const carry = carry_s;
+        if (i < ntile) A.block_sum[i] = carry + warp_off + incl - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry_s = carry + warp_off + incl;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(NL_BLOCK) k_scan_down(NlistArrays A)
+{
+    if (!A.ctl->doing_rebuild) return;
+    uint32_t const ncell = ncells_total(A);
+    uint32_t const base = blockIdx.x * SCAN_TILE;
+    if (base >= ncell) return;
+    // thread t owns SCAN_ITEMS consecutive counts
+    uint32_t v[SCAN_ITEMS];
+    uint32_t sum = 0;
+    uint32_t const first = base + threadIdx.x * SCAN_ITEMS;
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        v[k] = first + k < ncell ? A.cell_count[first + k] : 0u;
+        sum += v[k];
+    }
+    uint32_t incl = sum;
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t const t = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((threadIdx.x & 31) >= o) incl += t;
+    }
+    __shared__ uint32_t warp_tot[NL_BLOCK / 32];
+    if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = incl;
+    __syncthreads();
+    uint32_t off = A.block_sum[blockIdx.x];
+    for (int w = 0; w < (int) (threadIdx.x >> 5); w++) off += warp_tot[w];
+    off += incl - sum;
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        if (first + k < ncell) A.cell_start[first + k] = off;
+        off += v[k];
+    }
+    if (first < ncell && first + SCAN_ITEMS >= ncell) A.cell_start[ncell] = A.ntot;
+}
+
+/* group old slots by cell (arrival order) */
+__global__ void __launch_bounds__(NL_BLOCK) k_group(NlistArrays A)
+{
+    if (!A.ctl->doing_rebuild) return;
+    uint32_t const s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= A.ntot) return;
+    A.stage[A.cell_start[A.cellkey[s]] + A.rank[s]] = s;
+}
+
+/* deterministic order inside each cell (ascending original index), then move the records */
+__global__ void __launch_bounds__(NL_BLOCK) k_place(NlistArrays A)
+{
+    if (!A.ctl->doing_rebuild) return;
+    uint32_t const t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= A.ntot) return;
+    uint32_t const old = A.stage[t];
+    uint32_t const key = A.cellkey[old];
+    uint32_t const b = A.cell_start[key], e = A.cell_start[key + 1];
+    bead4 const rec = A.pos[old];
+    uint32_t const mine = w_orig(rec.w);
+    uint32_t rnk = 0;
+    for (uint32_t u = b; u < e; u++) {
+        uint32_t const other = w_orig(A.pos[A.stage[u]].w);
+        rnk += other < mine;
+    }
+    uint32_t const slot = b + rnk;
+    A.bpos[slot] = rec;
+    A.slot_of[(old / A.n) * A.n + mine] = slot;
+}
+
+/* ELL rows: every bead lists all beads of its replica within the list radius at build time */
+__global__ void __launch_bounds__(NL_BLOCK) k_rows(NlistArrays A)
+{
+    if (!A.ctl->doing_rebuild) return;
+    __shared__ DParams P;
+    __shared__ DGrid G;
+    for (uint32_t i = threadIdx.x; i < sizeof(DParams) / 4; i += blockDim.x)
+        ((uint32_t *) &P)[i] = ((const uint32_t *) A.params)[i];
+    for (uint32_t i = threadIdx.x; i < sizeof(DGrid) / 4; i += blockDim.x)
+        ((uint32_t *) &G)[i] = ((const uint32_t *) &A.ctl->grid)[i];
+    __syncthreads();
+
+    uint32_t const s = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t count = 0;
+    if (s < A.ntot) {
+        bead4 const me = A.bpos[s];
+        A.pos_out[s] = me;
+        uint32_t const replica = s / A.n;
+        double const r2max = __dmul_rn(G.radius, G.radius);
+        int c[3];
+        cell_coords(P, G, me.x, me.y, me.z, c);
+        int lst[3][3], cnt[3];
+        for (int d = 0; d < 3; d++) {
+            int const n = G.n[d];
+            cnt[d] = 0;
+            if (P.box_kind == BD_BOX_PERIODIC) {
+                if (n == 1) {
+                    lst[d][cnt[d]++] = c[d];
+                } else if (n == 2) {
+                    lst[d][cnt[d]++] = c[d];
+                    lst[d][cnt[d]++] = c[d] ^ 1;
+                } else {
+                    lst[d][cnt[d]++] = c[d] == 0 ? n - 1 : c[d] - 1;
+                    lst[d][cnt[d]++] = c[d];
+                    lst[d][cnt[d]++] = c[d] == n - 1 ? 0 : c[d] + 1;
+                }
+            } else {
+                if (c[d] > 0) lst[d][cnt[d]++] = c[d] - 1;
+                lst[d][cnt[d]++] = c[d];
+                if (c[d] < n - 1) lst[d][cnt[d]++] = c[d] + 1;
+            }
+        }
+        bool over = false;
+        for (int iz = 0; iz < cnt[2]; iz++)
+            for (int iy = 0; iy < cnt[1]; iy++)
+                for (int ix = 0; ix < cnt[0]; ix++) {
+                    uint32_t const key = (replica << G.totalbits)
+                        | morton_key(lst[0][ix], lst[1][iy], lst[2][iz], G.bits);
+                    uint32_t const b = A.cell_start[key], e = A.cell_start[key + 1];
+                    for (uint32_t j = b; j < e; j++) {
+                        if (j == s) continue;
+                        bead4 const o = A.bpos[j];
+                        d3 const r = displacement(P, me.x, me.y, me.z, o.x, o.y, o.z);
+                        if (sqnorm_exact(r.x, r.y, r.z) > r2max) continue;
+                        if (count < A.cap) {
+                            A.nbr[(size_t) count * A.ntot + s] = j;
+                            count++;
+                        } else {
+                            over = true;
+                        }
+                    }
+                }
+        A.nnbr[s] = count;
+        if (over) atomicAdd(&A.ctl->overflow, 1u);
+    }
+    // listed entries (2 x listed pairs)
+    unsigned long long tot = count;
+    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+    if ((threadIdx.x & 31) == 0 && tot) atomicAdd(&A.ctl->listed_entries, tot);
+}
+
+/* Verlet list as unordered pairs of original indices (validation, get_neighbor_list) */
+__global__ void __launch_bounds__(NL_BLOCK) k_export_pairs(NlistArrays A, uint32_t replica,
+                                                           uint32_t *pairs_out,
+                                                           unsigned long long cap,
+                                                           unsigned long long *count)
+{
+    uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= A.n) return;
+    uint32_t const s = replica * A.n + i;
+    uint32_t const oi = w_orig(A.bpos[s].w);
+    uint32_t const m = A.nnbr[s];
+    for (uint32_t k = 0; k < m; k++) {
+        uint32_t const j = A.nbr[(size_t) k * A.ntot + s];
+        uint32_t const oj = w_orig(A.bpos[j].w);
+        if (oi < oj) {
+            unsigned long long const at = atomicAdd(count, 1ull);
+            if (at < cap) {
+                pairs_out[2 * at] = oi;
+                pairs_out[2 * at + 1] = oj;
+            }
+        }
+    }
+}
+
+}  // namespace bd

@@ -1,0 +1,123 @@
+/*
+ * bd_nsearch.cu -- stateless neighbour-search entry points (validation and analysis callers).
+ *
+ *   bd_nsearch_buckets  md::neighbor_searcher<Box>::set_points -> search_grid::locate_bucket
+ *                       (MD/misc/nsearch_detail/search_grid.hpp:80-86,142-145,231-252,
+ *                        MD/misc/linear_hash.hpp:21-43, MD/misc/nsearch_detail/math.hpp:27-86):
+ *                       the reference's own bucket index of every point, bit for bit.
+ *   bd_nsearch_pairs    md::neighbor_searcher<Box>::search (MD/misc/neighbor_searcher.hpp:54-100):
+ *                       all unordered pairs within dcut, found with the engine's cell list (list
+ *                       radius = dcut) and the reference's fp64 distance test.
+ */
+#include <algorithm>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/bd_cuda.h"
+#include "bd_device.cuh"
+
+using namespace bd;
+
+extern int bd_internal_fail(const char *msg);
+
+struct BucketGrid {
+    int box_kind;
+    double freq;        // open: 1 / spacing
+    uint32_t modulus;   // open: hash modulus
+    double step[3];     // periodic: bin width
+    double inv_step[3];
+    double span[3], inv_span[3];
+    uint32_t count[3];
+};
+
+__global__ void k_locate_bucket(BucketGrid g, const double *xyz, uint32_t *out, size_t n)
+{
+    size_t const i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double const p[3] = {xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]};
+    if (g.box_kind == BD_BOX_OPEN) {
+        // search_grid.hpp:231-244: uint32(2^20 + freq * x), then linear_hash mod M
+        uint32_t c[3];
+        for (int d = 0; d < 3; d++) c[d] = (uint32_t) __dadd_rn(1048576.0, __dmul_rn(g.freq, p[d]));
+        unsigned long long sum = 0;
+        sum += 3929498747ull * c[0];
+        sum += 1008281837ull * c[1];
+        sum += 1832832077ull * c[2];
+        out[i] = (uint32_t) (sum % g.modulus);
+    } else {
+        // math.hpp:78-86 locate_bin per axis, search_grid.hpp:142-145 x + nx*(y + ny*z)
+        uint32_t b[3];
+        for (int d = 0; d < 3; d++) {
+            double const image = floor_mod_exact(p[d], g.span[d], g.inv_span[d]);
+            uint32_t const idx = (uint32_t) (int32_t) __dmul_rn(image, g.inv_step[d]);
+            b[d] = idx < g.count[d] ? idx : g.count[d] - 1;
+        }
+        out[i] = b[0] + g.count[0] * (b[1] + g.count[1] * b[2]);
+    }
+}
+
+extern "C" int bd_nsearch_buckets(int32_t box_kind, const double period[3], int64_t particle_count,
+                                  double spacing, const double *xyz, int64_t n, uint32_t *bucket_out,
+                                  int32_t device)
+{
+    if (n < 0 || !(spacing > 0)) return bd_internal_fail("bd_nsearch_buckets: bad arguments");
+    if (cudaSetDevice(device) != cudaSuccess) return bd_internal_fail("bd_nsearch_buckets: no such CUDA device");
+    BucketGrid g;
+    std::memset(&g, 0, sizeof g);
+    g.box_kind = box_kind;
+    if (box_kind == BD_BOX_OPEN) {
+        g.freq = 1 / spacing;
+        g.modulus = (uint32_t) ((uint64_t) particle_count * 2 / 11) | 1u;  // search_grid.hpp:247-252
+    } else if (box_kind == BD_BOX_PERIODIC) {
+        for (int d = 0; d < 3; d++) {
+            // math.hpp:68-76 define_bins(span, min_step)
+            uint32_t const c = (uint32_t) (int32_t) (period[d] / spacing);
+            g.count[d] = c > 1 ? c : 1;
+            g.step[d] = period[d] / (double) g.count[d];
+            g.inv_step[d] = 1 / g.step[d];
+            g.span[d] = g.step[d] * (double) g.count[d];
+            g.inv_span[d] = 1 / g.span[d];
+        }
+    } else {
+        return bd_internal_fail("bd_nsearch_buckets: unknown box kind");
+    }
+    if (n == 0) return 0;
+    double *d_xyz = nullptr;
+    uint32_t *d_out = nullptr;
+    cudaError_t e = cudaMalloc((void **) &d_xyz, 3 * (size_t) n * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc((void **) &d_out, (size_t) n * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMemcpy(d_xyz, xyz, 3 * (size_t) n * sizeof(double), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        k_locate_bucket<<<(unsigned) ((n + 255) / 256), 256>>>(g, d_xyz, d_out, (size_t) n);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(bucket_out, d_out, (size_t) n * sizeof(uint32_t), cudaMemcpyDeviceToHost);
+    cudaFree(d_xyz);
+    cudaFree(d_out);
+    if (e != cudaSuccess) return bd_internal_fail((std::string("bd_nsearch_buckets: ") + cudaGetErrorString(e)).c_str());
+    return 0;
+}
+
+extern "C" int bd_nsearch_pairs(int32_t box_kind, const double period[3], int64_t particle_count, double dcut,
+                                const double *xyz, int64_t n, uint32_t *pairs_out, int64_t cap,
+                                int64_t *count_out, int32_t device)
+{
+    (void) particle_count;  // only shapes the reference's hash table, not the result
+    *count_out = 0;
+    if (n < 0 || !(dcut > 0)) return bd_internal_fail("bd_nsearch_pairs: bad arguments");
+    if (n == 0) return 0;
+    bd_engine *h = nullptr;
+    if (bd_create(n, 1, device, &h)) return 1;
+    int rc = bd_set_box(h, box_kind, period);
+    // a list radius of exactly dcut: the rows then hold precisely the pairs with r^2 <= dcut^2
+    if (!rc) rc = bd_set_option(h, "verlet_factor", 1.0);
+    bd_term none;
+    std::memset(&none, 0, sizeof none);
+    int32_t ff = -1;
+    if (!rc) rc = bd_add_pair_ff(h, 1, &none, dcut, nullptr, &ff);
+    if (!rc) rc = bd_set_positions(h, 0, xyz);
+    if (!rc) rc = bd_get_neighbor_list(h, 0, pairs_out, cap, count_out);
+    bd_destroy(h);
+    return rc;
+}

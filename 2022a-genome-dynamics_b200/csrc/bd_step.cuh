@@ -1,0 +1,600 @@
+/*
+ * bd_step.cuh -- force evaluation and the Brownian update.
+ *
+ * Replaces, in one pass over cell-sorted beads:
+ *   md::neighbor_pairwise_forcefield::compute_force   MD/forcefield/neighbor_pairwise_forcefield.hpp:68-84
+ *   md::bonded_pairwise_forcefield::compute_force     MD/forcefield/bonded_pairwise_forcefield.hpp:78-93
+ *   md::bonded_triplewise_forcefield::compute_force   MD/forcefield/bonded_triplewise_forcefield.hpp:82-103
+ *   sphere / ellipsoid surface forcefields            MD/forcefield/sphere_surface_forcefield.hpp:108-143,
+ *                                                     MD/forcefield/ellipsoid_surface_forcefield.hpp:167-211
+ *   md::point_source_forcefield::compute_force        MD/forcefield/point_source_forcefield.hpp:78-103
+ *   brownian_simulator::simulate_step                 MD/simulation/detail/brownian_simulator.hpp:44-76
+ *   neighbor_list::check_consistency                  MD/forcefield/detail/neighbor_list.hpp:101-159
+ *
+ * One thread owns one bead: it gathers every partner itself (each pair is evaluated from both
+ * sides), so no force is ever scattered and nothing is atomic except block-level statistics.
+ * Positions are double-buffered: the fused kernel reads pos[cur] and writes pos[1-cur], which is
+ * the single HBM round trip of a step.
+ */
+#pragma once
+
+#include "bd_device.cuh"
+
+namespace bd {
+
+constexpr int STEP_BLOCK = 128;
+constexpr int WALL_STATS = 4;
+
+struct StepArrays {
+    const bead4 *pos;
+    bead4 *pos_out;
+    const bead4 *bpos;
+    const uint32_t *slot_of;
+    const uint32_t *nbr;
+    const uint32_t *nnbr;
+    const uint32_t *bond_start;   // [n+1] CSR by original index
+    const uint2 *bond_adj;        // {partner original index, ff | second<<8}
+    const uint32_t *bend_start;   // [n+1]
+    const uint32_t *bend_adj;     // triple id << 2 | role
+    const uint32_t *triples;      // [m][3] original indices
+    const double *bend_energy;    // [m]
+    const uint8_t *bend_ff;       // [m]
+    const DTerm *terms;
+    const DParams *params;
+    DControl *ctl;
+    double *wall_partial;         // [replicas][chunks][BD_MAX_WALL_FF][4]
+    unsigned long long *inter_partial;  // [replicas*chunks] running count of interacting pairs
+    double *force;                // [Ntot][3] by slot (two-pass path and compute_forces)
+    double *wprev;                // [Ntot][3] by original global index (replay mode)
+    unsigned long long *dt_bits;  // [replicas] adaptive: min timestep of the current step
+    const double *dt_prev;        // [replicas] adaptive: timestep of the previous step
+    uint32_t n, replicas, ntot, chunks;
+};
+
+struct StepScalars {
+    double dt, dt_prev;      // fixed-timestep path
+    double kT, kT_prev;
+    double spacestep;
+    unsigned long long seed;
+    long long step;          // 1-based index of this step within the run
+    const double *replay;    // device, [replicas][n][3] standard normals of this step, or null
+    int adaptive;
+};
+
+template <typename T>
+__device__ inline T ldg(const T *p) { return __ldg(p); }
+
+__device__ inline bead4 load_bead(const bead4 *p)
+{
+    bead4 b;
+    const double2 *q = reinterpret_cast<const double2 *>(p);
+    double2 const a = q[0];
+    double2 const c = q[1];
+    b.x = a.x; b.y = a.y; b.z = c.x; b.w = (uint64_t) __double_as_longlong(c.y);
+    return b;
+}
+
+__device__ inline void store_bead(bead4 *p, double x, double y, double z, uint64_t w)
+{
+    double2 *q = reinterpret_cast<double2 *>(p);
+    q[0] = make_double2(x, y);
+    q[1] = make_double2(z, __longlong_as_double((long long) w));
+}
+
+/* forces of all selected forcefields on the bead at slot s; wall statistics into ws[][4] */
+__device__ inline d3 bead_force(const StepArrays &A, const DParams &P, Select sel, uint32_t s,
+                                uint32_t replica, const bead4 &me, double ws[BD_MAX_WALL_FF][WALL_STATS],
+                                uint32_t &interactions)
+{
+    d3 F = {0.0, 0.0, 0.0};
+    uint32_t const oi = w_orig(me.w), ti = w_type(me.w);
+    int const T = P.ntypes;
+    uint32_t const base = replica * A.n;
+
+    // ---- non-bonded pairs over the Verlet row ----
+    bool any_pair = false;
+    for (int f = 0; f < BD_MAX_PAIR_FF; f++) any_pair |= ff_on(sel, BD_FF_PAIR, f, P.pair[f].enabled);
+    if (any_pair) {
+        uint32_t const m = A.nnbr[s];
+        for (uint32_t k = 0; k < m; k++) {
+            uint32_t const j = A.nbr[(size_t) k * A.ntot + s];
+            bead4 const o = load_bead(A.pos + j);
+            d3 const r = displacement(P, me.x, me.y, me.z, o.x, o.y, o.z);
+            double const r2 = sqnorm_exact(r.x, r.y, r.z);
+            uint32_t const oj = w_orig(o.w), tj = w_type(o.w);
+            int const cell = oi < oj ? (int) (ti * T + tj) : (int) (tj * T + ti);
+            bool hit = false;
+#pragma unroll
+            for (int f = 0; f < BD_MAX_PAIR_FF; f++) {
+                const DPair &pf = P.pair[f];
+                if (!ff_on(sel, BD_FF_PAIR, f, pf.enabled) || r2 > pf.dcut2) continue;
+                if (pf.has_targets && !((w_pair_mask(me.w) >> f) & (w_pair_mask(o.w) >> f) & 1u)) continue;
+                double const sc = pot_force_scalar(A.terms + pf.term_off + cell * pf.nterms, pf.nterms, r2);
+                F.x += sc * r.x; F.y += sc * r.y; F.z += sc * r.z;
+                hit = true;
+            }
+            interactions += (hit && oi < oj) ? 1u : 0u;
+        }
+    }
+
+    // ---- bonded pairs (no minimum image: bonded_pairwise_forcefield.hpp:64) ----
+    {
+        uint32_t const b = A.bond_start[oi], e = A.bond_start[oi + 1];
+        for (uint32_t k = b; k < e; k++) {
+            uint2 const adj = A.bond_adj[k];
+            int const f = adj.y & 0xff;
+            const DBond &bf = P.bond[f];
+            if (!ff_on(sel, BD_FF_BOND, f, bf.enabled)) continue;
+            bead4 const o = load_bead(A.pos + A.slot_of[base + adj.x]);
+            uint32_t const tj = w_type(o.w);
+            bool const second = (adj.y >> 8) & 1u;
+            // r = x_first - x_second, row (type_first, type_second); this bead gets +f or -f
+            double rx = me.x - o.x, ry = me.y - o.y, rz = me.z - o.z;
+            int const cell = second ? (int) (tj * T + ti) : (int) (ti * T + tj);
+            double const r2 = rx * rx + ry * ry + rz * rz;
+            double const sc = pot_force_scalar(A.terms + bf.term_off + cell * bf.nterms, bf.nterms, r2);
+            F.x += sc * rx; F.y += sc * ry; F.z += sc * rz;
+        }
+    }
+
+    // ---- bending triples (cosine_bending_potential.hpp:43-60) ----
+    {
+        uint32_t const b = A.bend_start[oi], e = A.bend_start[oi + 1];
+        for (uint32_t k = b; k < e; k++) {
+            uint32_t const adj = A.bend_adj[k];
+            uint32_t const t = adj >> 2, role = adj & 3u;
+            int const f = A.bend_ff[t];
+            if (!ff_on(sel, BD_FF_BEND, f, P.bend[f].enabled)) continue;
+            double const E = A.bend_energy[t];
+            uint32_t const i0 = A.triples[3 * t], i1 = A.triples[3 * t + 1], i2 = A.triples[3 * t + 2];
+            bead4 const pi = role == 0 ? me : load_bead(A.pos + A.slot_of[base + i0]);
+            bead4 const pj = role == 1 ? me : load_bead(A.pos + A.slot_of[base + i1]);
+            bead4 const pk = role == 2 ? me : load_bead(A.pos + A.slot_of[base + i2]);
+            double const ax = pi.x - pj.x, ay = pi.y - pj.y, az = pi.z - pj.z;  // rij
+            double const bx = pj.x - pk.x, by = pj.y - pk.y, bz = pj.z - pk.z;  // rjk
+            double const dij = ax * ax + ay * ay + az * az, djk = bx * bx + by * by + bz * bz;
+            double const dd = sqrt(dij * djk);
+            if (dd == 0.0) continue;
+            double const dot = ax * bx + ay * by + az * bz;
+            double const ed = E / dd, ca = dot / dij, cb = dot / djk;
+            double const fijx = ed * (bx - ca * ax), fijy = ed * (by - ca * ay), fijz = ed * (bz - ca * az);
+            double const fjkx = ed * (ax - cb * bx), fjky = ed * (ay - cb * by), fjkz = ed * (az - cb * bz);
+            if (role == 0) { F.x += fijx; F.y += fijy; F.z += fijz; }
+            else if (role == 1) { F.x += fjkx - fijx; F.y += fjky - fijy; F.z += fjkz - fijz; }
+            else { F.x -= fjkx; F.y -= fjky; F.z -= fjkz; }
+        }
+    }
+
+    // ---- walls ----
+#pragma unroll 1
+    for (int f = 0; f < BD_MAX_WALL_FF; f++) {
+        const DWall &wf = P.wall[f];
+        ws[f][0] = ws[f][1] = ws[f][2] = ws[f][3] = 0.0;
+        if (!ff_on(sel, BD_FF_WALL, f, wf.enabled)) continue;
+        double const rx = me.x - wf.center[0], ry = me.y - wf.center[1], rz = me.z - wf.center[2];
+        const DTerm *row = A.terms + wf.term_off + ti * wf.nterms;
+        if (wf.shape == BD_WALL_SPHERE) {
+            // sphere_surface_forcefield.hpp:108-143
+            double const radius = wf.semi[0];
+            double const r2 = rx * rx + ry * ry + rz * rz;
+            if (r2 == 0.0) continue;
+            double const r1 = sqrt(r2);
+            double const scale = radius / r1;
+            double const sx = rx - scale * rx, sy = ry - scale * ry, sz = rz - scale * rz;
+            bool const inside = r2 < radius * radius;
+            bool const active = inside ? wf.direction == BD_WALL_INWARD : wf.direction == BD_WALL_OUTWARD;
+            if (!active) continue;
+            double const sc = pot_force_scalar(row, wf.nterms, sx * sx + sy * sy + sz * sz);
+            double const fx = sc * sx, fy = sc * sy, fz = sc * sz;
+            double const pr = (fx * rx + fy * ry + fz * rz) / r2;  // project(force, r)
+            F.x += fx + scale * (pr * rx - fx);
+            F.y += fy + scale * (pr * ry - fy);
+            F.z += fz + scale * (pr * rz - fz);
+            ws[f][0] = -(fx * rx + fy * ry + fz * rz) / r1;
+        } else {
+            // ellipsoid_surface_forcefield.hpp:54-99 (evaluate_point), :167-211
+            double const qx = 1.0 / (wf.semi[0] * wf.semi[0]), qy = 1.0 / (wf.semi[1] * wf.semi[1]),
+                         qz = 1.0 / (wf.semi[2] * wf.semi[2]);
+            double const dx = qx * rx, dy = qy * ry, dz = qz * rz;  // dual
+            double const d2 = dx * dx + dy * dy + dz * dz;
+            if (d2 == 0.0) continue;
+            double const implicit = dx * rx + dy * ry + dz * rz - 1.0;
+            double const scale = implicit / (2.0 * d2);
+            double const ex = scale * dx, ey = scale * dy, ez = scale * dz;  // delta
+            bool const inside = implicit < 0.0;
+            bool const active = inside ? wf.direction == BD_WALL_INWARD : wf.direction == BD_WALL_OUTWARD;
+            if (!active) continue;
+            double const e2 = ex * ex + ey * ey + ez * ez;
+            double const sc = pot_force_scalar(row, wf.nterms, e2);
+            double const bx = sc * ex, by = sc * ey, bz = sc * ez;  // basic force
+            double const pr = e2 != 0.0 ? (bx * ex + by * ey + bz * ez) / e2 : 0.0;
+            double const ix = pr * ex, iy = pr * ey, iz = pr * ez;  // iso = project(basic, delta)
+            double const fx = ix + ((bx - ix) - ix) * (scale * qx);
+            double const fy = iy + ((by - iy) - iy) * (scale * qy);
+            double const fz = iz + ((bz - iz) - iz) * (scale * qz);
+            F.x += fx; F.y += fy; F.z += fz;
+            double const en = e2 != 0.0 ? (inside ? -1.0 : 1.0) / sqrt(e2) : 0.0;
+            double const nx = en * ex, ny = en * ey, nz = en * ez;  // outward normal
+            ws[f][0] = -(fx * nx + fy * ny + fz * nz);
+            ws[f][1] = -(nx > 0 ? fx : -fx);
+            ws[f][2] = -(ny > 0 ? fy : -fy);
+            ws[f][3] = -(nz > 0 ? fz : -fz);
+        }
+    }
+
+    // ---- point sources ----
+#pragma unroll 1
+    for (int f = 0; f < BD_MAX_POINT_FF; f++) {
+        const DPoint &pf = P.point[f];
+        if (!ff_on(sel, BD_FF_POINT, f, pf.enabled)) continue;
+        if (pf.has_targets && !((w_point_mask(me.w) >> f) & 1u)) continue;
+        double const rx = me.x - pf.source[0], ry = me.y - pf.source[1], rz = me.z - pf.source[2];
+        double const sc = pot_force_scalar(A.terms + pf.term_off + ti * pf.nterms, pf.nterms,
+                                           rx * rx + ry * ry + rz * rz);
+        F.x += sc * rx; F.y += sc * ry; F.z += sc * rz;
+    }
+    return F;
+}
+
+/* block-level sums of the wall statistics -> wall_partial[replica][chunk][wall][4] */
+__device__ inline void reduce_wall_stats(const StepArrays &A, const DParams &P, Select sel,
+                                         uint32_t replica, uint32_t chunk,
+                                         double ws[BD_MAX_WALL_FF][WALL_STATS])
+{
+    __shared__ double red[STEP_BLOCK / 32][WALL_STATS];
+#pragma unroll 1
+    for (int f = 0; f < BD_MAX_WALL_FF; f++) {
+        if (!ff_on(sel, BD_FF_WALL, f, P.wall[f].enabled)) continue;  // block-uniform
+        double v[WALL_STATS] = {ws[f][0], ws[f][1], ws[f][2], ws[f][3]};
+#pragma unroll
+        for (int c = 0; c < WALL_STATS; c++)
+            for (int o = 16; o > 0; o >>= 1) v[c] += __shfl_xor_sync(0xffffffffu, v[c], o);
+        if ((threadIdx.x & 31) == 0)
+            for (int c = 0; c < WALL_STATS; c++) red[threadIdx.x >> 5][c] = v[c];
+        __syncthreads();
+        if (threadIdx.x < WALL_STATS) {
+            double t = 0.0;
+            for (int w = 0; w < STEP_BLOCK / 32; w++) t += red[w][threadIdx.x];
+            A.wall_partial[(((size_t) replica * A.chunks + chunk) * BD_MAX_WALL_FF + f) * WALL_STATS
+                           + threadIdx.x] = t;
+        }
+        __syncthreads();
+    }
+}
+
+__device__ inline void load_params(DParams &P, const DParams *src)
+{
+    for (uint32_t i = threadIdx.x; i < sizeof(DParams) / 4; i += blockDim.x)
+        ((uint32_t *) &P)[i] = ((const uint32_t *) src)[i];
+    __syncthreads();
+}
+
+/* MD/simulation/detail/brownian_simulator.hpp:57-75 + neighbor_list.hpp:132-158 for one bead */
+__device__ inline double integrate_bead(const StepArrays &A, const DParams &P, const StepScalars &S,
+                                        uint32_t s, uint32_t replica, const bead4 &me, d3 F, double dt,
+                                        double dt_prev)
+{
+    uint32_t const oi = w_orig(me.w);
+    double const mu = P.mobility[w_type(me.w)];
+    double const mu_dt = dt * mu;
+    double const sigma = sqrt(2.0 * S.kT * mu_dt);
+    double wx, wy, wz, px, py, pz;
+    size_t const g = (size_t) replica * A.n + oi;
+    if (S.replay) {
+        wx = sigma * S.replay[3 * g]; wy = sigma * S.replay[3 * g + 1]; wz = sigma * S.replay[3 * g + 2];
+        px = A.wprev[3 * g]; py = A.wprev[3 * g + 1]; pz = A.wprev[3 * g + 2];
+        A.wprev[3 * g] = wx; A.wprev[3 * g + 1] = wy; A.wprev[3 * g + 2] = wz;
+    } else {
+        double z[3];
+        philox_normals(S.seed, (uint64_t) S.step, replica, oi, z);
+        wx = sigma * z[0]; wy = sigma * z[1]; wz = sigma * z[2];
+        if (S.step > 1) {
+            double const sp = sqrt(2.0 * S.kT_prev * (dt_prev * mu));
+            philox_normals(S.seed, (uint64_t) (S.step - 1), replica, oi, z);
+            px = sp * z[0]; py = sp * z[1]; pz = sp * z[2];
+        } else {
+            px = py = pz = 0.0;
+        }
+    }
+    double x = me.x + mu_dt * F.x, y = me.y + mu_dt * F.y, z2 = me.z + mu_dt * F.z;
+    x += 0.5 * (wx + px); y += 0.5 * (wy + py); z2 += 0.5 * (wz + pz);
+    store_bead(A.pos_out + s, x, y, z2, me.w);
+
+    // distance from the build position, for the Verlet-list skin test
+    bead4 const b0 = load_bead(A.bpos + s);
+    d3 const d = displacement(P, x, y, z2, b0.x, b0.y, b0.z);
+    return sqnorm_exact(d.x, d.y, d.z);
+}
+
+/* fold the block's largest displacement^2 into the control block; the rebuild decision itself is
+ * taken by k_rebuild_begin before the next force evaluation (neighbor_list.hpp:132-158) */
+__device__ inline void publish_displacement(const StepArrays &A, double moved2, double known)
+{
+    for (int o = 16; o > 0; o >>= 1) moved2 = fmax(moved2, __shfl_xor_sync(0xffffffffu, moved2, o));
+    if ((threadIdx.x & 31) == 0 && moved2 > known)
+        atomicMax(&A.ctl->max_disp2_bits, (unsigned long long) __double_as_longlong(moved2));
+}
+
+/* the hot kernel: forces + Brownian update + skin test, fixed timestep */
+__global__ void __launch_bounds__(STEP_BLOCK) k_step_fused(StepArrays A, StepScalars S)
+{
+    __shared__ DParams P;
+    load_params(P, A.params);
+    uint32_t const replica = blockIdx.y, chunk = blockIdx.x;
+    uint32_t const local = chunk * STEP_BLOCK + threadIdx.x;
+    uint32_t const s = replica * A.n + local;
+    bool const live = local < A.n;
+    Select const all = {BD_FF_ALL, -1};
+    double ws[BD_MAX_WALL_FF][WALL_STATS];
+    uint32_t inter = 0;
+    double const known = __longlong_as_double((long long) A.ctl->max_disp2_bits);
+    double moved2 = 0.0;
+    if (live) {
+        bead4 const me = load_bead(A.pos + s);
+        d3 const F = bead_force(A, P, all, s, replica, me, ws, inter);
+        moved2 = integrate_bead(A, P, S, s, replica, me, F, S.dt, S.dt_prev);
+    } else {
+        for (int f = 0; f < BD_MAX_WALL_FF; f++) ws[f][0] = ws[f][1] = ws[f][2] = ws[f][3] = 0.0;
+    }
+    publish_displacement(A, moved2, known);
+    reduce_wall_stats(A, P, all, replica, chunk, ws);
+    for (int o = 16; o > 0; o >>= 1) inter += __shfl_xor_sync(0xffffffffu, inter, o);
+    __shared__ uint32_t inter_s[STEP_BLOCK / 32];
+    if ((threadIdx.x & 31) == 0) inter_s[threadIdx.x >> 5] = inter;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+        for (int w = 0; w < STEP_BLOCK / 32; w++) t += inter_s[w];
+        A.inter_partial[(size_t) replica * A.chunks + chunk] += t;
+    }
+}
+
+/* forces only (compute_forces, and the first pass of an adaptive-timestep step) */
+__global__ void __launch_bounds__(STEP_BLOCK) k_force(StepArrays A, StepScalars S, Select sel)
+{
+    __shared__ DParams P;
+    load_params(P, A.params);
+    uint32_t const replica = blockIdx.y, chunk = blockIdx.x;
+    uint32_t const local = chunk * STEP_BLOCK + threadIdx.x;
+    uint32_t const s = replica * A.n + local;
+    bool const live = local < A.n;
+    double ws[BD_MAX_WALL_FF][WALL_STATS];
+    uint32_t inter = 0;
+    double dt = S.dt;
+    if (live) {
+        bead4 const me = load_bead(A.pos + s);
+        d3 const F = bead_force(A, P, sel, s, replica, me, ws, inter);
+        A.force[3 * (size_t) s] = F.x;
+        A.force[3 * (size_t) s + 1] = F.y;
+        A.force[3 * (size_t) s + 2] = F.z;
+        if (S.adaptive) {
+            // brownian_timestepper.hpp:72-91,109-136
+            double const mu = P.mobility[w_type(me.w)];
+            double const f2 = F.x * F.x + F.y * F.y + F.z * F.z;
+            if (mu != 0.0 || f2 != 0.0) {
+                double const a = mu * mu * f2, b = 2.55 * mu * S.kT, c = S.spacestep * S.spacestep;
+                dt = (a * c < 1e-6 * b * b) ? c / b : (-b + sqrt(b * b + 4.0 * a * c)) / (2.0 * a);
+            }
+            dt = fmin(dt, S.dt);
+        }
+    } else {
+        for (int f = 0; f < BD_MAX_WALL_FF; f++) ws[f][0] = ws[f][1] = ws[f][2] = ws[f][3] = 0.0;
+    }
+    reduce_wall_stats(A, P, sel, replica, chunk, ws);
+    if (S.adaptive) {
+        for (int o = 16; o > 0; o >>= 1) dt = fmin(dt, __shfl_xor_sync(0xffffffffu, dt, o));
+        if ((threadIdx.x & 31) == 0)
+            atomicMin(A.dt_bits + replica, (unsigned long long) __double_as_longlong(dt));
+    }
+}
+
+/* second pass of an adaptive step: update from the stored forces */
+__global__ void __launch_bounds__(STEP_BLOCK) k_integrate(StepArrays A, StepScalars S)
+{
+    __shared__ DParams P;
+    load_params(P, A.params);
+    uint32_t const replica = blockIdx.y;
+    uint32_t const local = blockIdx.x * STEP_BLOCK + threadIdx.x;
+    double const known = __longlong_as_double((long long) A.ctl->max_disp2_bits);
+    double moved2 = 0.0;
+    if (local < A.n) {
+        uint32_t const s = replica * A.n + local;
+        bead4 const me = load_bead(A.pos + s);
+        d3 const F = {A.force[3 * (size_t) s], A.force[3 * (size_t) s + 1], A.force[3 * (size_t) s + 2]};
+        double const dt = __longlong_as_double((long long) A.dt_bits[replica]);
+        moved2 = integrate_bead(A, P, S, s, replica, me, F, dt, A.dt_prev[replica]);
+    }
+    publish_displacement(A, moved2, known);
+}
+
+/* adaptive bookkeeping between steps: dt_prev <- dt, dt <- max timestep */
+__global__ void k_dt_rotate(unsigned long long *dt_bits, double *dt_prev, double *dt_last,
+                            double max_dt, uint32_t replicas)
+{
+    uint32_t const r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= replicas) return;
+    double const dt = __longlong_as_double((long long) dt_bits[r]);
+    dt_prev[r] = dt;
+    dt_last[r] = dt;
+    dt_bits[r] = (unsigned long long) __double_as_longlong(max_dt);
+}
+
+/* potential energy of the selected forcefields: per-block partial sums, fixed order */
+__global__ void __launch_bounds__(STEP_BLOCK) k_energy(StepArrays A, Select sel, double *partial)
+{
+    __shared__ DParams P;
+    load_params(P, A.params);
+    uint32_t const replica = blockIdx.y, chunk = blockIdx.x;
+    uint32_t const local = chunk * STEP_BLOCK + threadIdx.x;
+    uint32_t const s = replica * A.n + local;
+    double E = 0.0;
+    if (local < A.n) {
+        bead4 const me = load_bead(A.pos + s);
+        uint32_t const oi = w_orig(me.w), ti = w_type(me.w);
+        int const T = P.ntypes;
+        uint32_t const base = replica * A.n;
+        uint32_t const m = A.nnbr[s];
+        for (uint32_t k = 0; k < m; k++) {
+            uint32_t const j = A.nbr[(size_t) k * A.ntot + s];
+            bead4 const o = load_bead(A.pos + j);
+            uint32_t const oj = w_orig(o.w), tj = w_type(o.w);
+            if (oi >= oj) continue;
+            d3 const r = displacement(P, me.x, me.y, me.z, o.x, o.y, o.z);
+            double const r2 = sqnorm_exact(r.x, r.y, r.z);
+            for (int f = 0; f < BD_MAX_PAIR_FF; f++) {
+                const DPair &pf = P.pair[f];
+                if (!ff_on(sel, BD_FF_PAIR, f, pf.enabled) || r2 > pf.dcut2) continue;
+                if (pf.has_targets && !((w_pair_mask(me.w) >> f) & (w_pair_mask(o.w) >> f) & 1u)) continue;
+                E += pot_energy(A.terms + pf.term_off + (ti * T + tj) * pf.nterms, pf.nterms, r2);
+            }
+        }
+        for (uint32_t k = A.bond_start[oi]; k < A.bond_start[oi + 1]; k++) {
+            uint2 const adj = A.bond_adj[k];
+            int const f = adj.y & 0xff;
+            if ((adj.y >> 8) & 1u) continue;  // counted from the first bead
+            const DBond &bf = P.bond[f];
+            if (!ff_on(sel, BD_FF_BOND, f, bf.enabled)) continue;
+            bead4 const o = load_bead(A.pos + A.slot_of[base + adj.x]);
+            double const rx = me.x - o.x, ry = me.y - o.y, rz = me.z - o.z;
+            E += pot_energy(A.terms + bf.term_off + (ti * T + w_type(o.w)) * bf.nterms, bf.nterms,
+                            rx * rx + ry * ry + rz * rz);
+        }
+        for (uint32_t k = A.bend_start[oi]; k < A.bend_start[oi + 1]; k++) {
+            uint32_t const adj = A.bend_adj[k];
+            if ((adj & 3u) != 0) continue;  // counted from the first bead
+            uint32_t const t = adj >> 2;
+            int const f = A.bend_ff[t];
+            if (!ff_on(sel, BD_FF_BEND, f, P.bend[f].enabled)) continue;
+            bead4 const pj = load_bead(A.pos + A.slot_of[base + A.triples[3 * t + 1]]);
+            bead4 const pk = load_bead(A.pos + A.slot_of[base + A.triples[3 * t + 2]]);
+            double const ax = me.x - pj.x, ay = me.y - pj.y, az = me.z - pj.z;
+            double const bx = pj.x - pk.x, by = pj.y - pk.y, bz = pj.z - pk.z;
+            double const dij = ax * ax + ay * ay + az * az, djk = bx * bx + by * by + bz * bz;
+            if (dij * djk == 0.0) continue;
+            double const e = A.bend_energy[t];
+            E += e - e * ((ax * bx + ay * by + az * bz) / sqrt(dij * djk));
+        }
+        for (int f = 0; f < BD_MAX_WALL_FF; f++) {
+            const DWall &wf = P.wall[f];
+            if (!ff_on(sel, BD_FF_WALL, f, wf.enabled)) continue;
+            double const rx = me.x - wf.center[0], ry = me.y - wf.center[1], rz = me.z - wf.center[2];
+            const DTerm *row = A.terms + wf.term_off + ti * wf.nterms;
+            if (wf.shape == BD_WALL_SPHERE) {
+                double const radius = wf.semi[0];
+                double const r2 = rx * rx + ry * ry + rz * rz;
+                if (r2 == 0.0) continue;
+                double const scale = radius / sqrt(r2);
+                double const sx = rx - scale * rx, sy = ry - scale * ry, sz = rz - scale * rz;
+                bool const inside = r2 < radius * radius;
+                if (inside ? wf.direction == BD_WALL_INWARD : wf.direction == BD_WALL_OUTWARD)
+                    E += pot_energy(row, wf.nterms, sx * sx + sy * sy + sz * sz);
+            } else {
+                double const qx = 1.0 / (wf.semi[0] * wf.semi[0]), qy = 1.0 / (wf.semi[1] * wf.semi[1]),
+                             qz = 1.0 / (wf.semi[2] * wf.semi[2]);
+                double const dx = qx * rx, dy = qy * ry, dz = qz * rz;
+                double const d2 = dx * dx + dy * dy + dz * dz;
+                if (d2 == 0.0) continue;
+                double const implicit = dx * rx + dy * ry + dz * rz - 1.0;
+                double const scale = implicit / (2.0 * d2);
+                bool const inside = implicit < 0.0;
+                if (inside ? wf.direction == BD_WALL_INWARD : wf.direction == BD_WALL_OUTWARD)
+                    E += pot_energy(row, wf.nterms, scale * scale * d2);
+            }
+        }
+        for (int f = 0; f < BD_MAX_POINT_FF; f++) {
+            const DPoint &pf = P.point[f];
+            if (!ff_on(sel, BD_FF_POINT, f, pf.enabled)) continue;
+            if (pf.has_targets && !((w_point_mask(me.w) >> f) & 1u)) continue;
+            double const rx = me.x - pf.source[0], ry = me.y - pf.source[1], rz = me.z - pf.source[2];
+            E += pot_energy(A.terms + pf.term_off + ti * pf.nterms, pf.nterms, rx * rx + ry * ry + rz * rz);
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) E += __shfl_xor_sync(0xffffffffu, E, o);
+    __shared__ double red[STEP_BLOCK / 32];
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = E;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < STEP_BLOCK / 32; w++) t += red[w];
+        partial[(size_t) replica * A.chunks + chunk] = t;
+    }
+}
+
+/* out[replica][c] = sum over chunks of partial[replica][chunk][c], in chunk order */
+__global__ void k_reduce_partials(const double *partial, double *out, uint32_t chunks, uint32_t width)
+{
+    uint32_t const replica = blockIdx.x;
+    for (uint32_t c = threadIdx.x; c < width; c += blockDim.x) {
+        double t = 0.0;
+        for (uint32_t k = 0; k < chunks; k++) t += partial[((size_t) replica * chunks + k) * width + c];
+        out[(size_t) replica * width + c] = t;
+    }
+}
+
+// ---- original-order <-> slot-order movement -----------------------------------------------------
+
+/* xyz[replica][n][3] (original order) -> pos[slot] */
+__global__ void k_scatter_positions(bead4 *pos, const uint32_t *slot_of, const double *xyz,
+                                    uint32_t first, uint32_t count)
+{
+    uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    uint32_t const g = first + i;
+    bead4 *p = pos + slot_of[g];
+    p->x = xyz[3 * (size_t) i];
+    p->y = xyz[3 * (size_t) i + 1];
+    p->z = xyz[3 * (size_t) i + 2];
+}
+
+__global__ void k_gather_positions(const bead4 *pos, const uint32_t *slot_of, double *xyz,
+                                   uint32_t first, uint32_t count)
+{
+    uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const bead4 *p = pos + slot_of[first + i];
+    xyz[3 * (size_t) i] = p->x;
+    xyz[3 * (size_t) i + 1] = p->y;
+    xyz[3 * (size_t) i + 2] = p->z;
+}
+
+__global__ void k_gather_forces(const double *force, const uint32_t *slot_of, double *out,
+                                uint32_t first, uint32_t count)
+{
+    uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    size_t const s = slot_of[first + i];
+    out[3 * (size_t) i] = force[3 * s];
+    out[3 * (size_t) i + 1] = force[3 * s + 1];
+    out[3 * (size_t) i + 2] = force[3 * s + 2];
+}
+
+/* (re)write the packed word of every bead: original index, class, target masks */
+__global__ void k_set_words(bead4 *pos0, bead4 *pos1, bead4 *bpos, const uint32_t *slot_of,
+                            const uint8_t *type, const uint8_t *pair_mask, const uint8_t *point_mask,
+                            uint32_t n, uint32_t ntot)
+{
+    uint32_t const g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= ntot) return;
+    uint32_t const o = g % n;
+    uint64_t const w = pack_w(o, type[o], pair_mask[o], point_mask[o]);
+    uint32_t const s = slot_of[g];
+    pos0[s].w = w;
+    pos1[s].w = w;
+    bpos[s].w = w;
+}
+
+__global__ void k_init_identity(uint32_t *slot_of, bead4 *pos0, bead4 *pos1, bead4 *bpos, uint32_t n,
+                                uint32_t ntot)
+{
+    uint32_t const g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= ntot) return;
+    slot_of[g] = g;
+    bead4 b;
+    b.x = b.y = b.z = 0.0;
+    b.w = pack_w(g % n, 0, 0, 0);
+    pos0[g] = b;
+    pos1[g] = b;
+    bpos[g] = b;
+}
+
+}  // namespace bd

@@ -1,0 +1,307 @@
+"""Parity of the B200 engine (libbd_b200.so, through the C ABI) with the CPU oracle and with the
+golden vectors generated from the unmodified reference.  GPU only.
+
+Tolerances (stated, not assumed):
+* bucket indices, neighbour pair sets, Verlet-list pair sets, rebuild counts: bit-exact / set-equal
+* forces: max_i |f_i - f_ref_i| / max_i |f_ref_i| <= 1e-12 (fp64 everywhere; only the summation
+  order and FMA contraction differ); BASELINE.json asks for 1e-6
+* energies, wall statistics: 1e-12 relative
+* noise-replay trajectories: max |dx| <= 1e-10 over 25-30 steps (positions are O(1..10))
+"""
+import os
+
+import numpy as np
+import pytest
+
+import bdb200 as bd
+import scenarios as sc
+from cases import GOLDEN, GOLDEN_SEED, GOLDEN_STEPS, SMALL, build, rel_force_error, sort_pairs, brute_pairs
+
+pytestmark = pytest.mark.gpu
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+FORCE_TOL = 1e-12
+ENERGY_TOL = 1e-12
+TRAJ_TOL = 1e-10
+
+CLASSES = ((bd.FF_PAIR, "pair"), (bd.FF_BOND, "bond"), (bd.FF_BEND, "bend"), (bd.FF_WALL, "wall"),
+           (bd.FF_POINT, "point"))
+
+
+def assert_close(a, b, tol):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    scale = max(np.abs(b).max(), 1e-300) if b.size else 1.0
+    assert np.abs(a - b).max() <= tol * scale if a.size else True, (np.abs(a - b).max() / scale)
+
+
+# ---- neighbour search -------------------------------------------------------------------------
+
+@pytest.mark.parametrize("kind,period", [(bd.BOX_OPEN, None), (bd.BOX_PERIODIC, (0.9, 1.0, 1.1)),
+                                         (bd.BOX_PERIODIC, (0.5, 2.0, 0.31))])
+@pytest.mark.parametrize("n", [0, 1, 2, 100, 1000, 20000])
+def test_buckets_bit_exact(engine, oracle, kind, period, n):
+    x = np.random.default_rng(n + 7).normal(size=(n, 3)) * 1.3
+    for spacing in (0.3, 0.45):
+        assert np.array_equal(engine.nsearch_buckets(kind, period, n, spacing, x),
+                              oracle.nsearch_buckets(kind, period, n, spacing, x))
+
+
+@pytest.mark.parametrize("kind,period", [(bd.BOX_OPEN, None), (bd.BOX_PERIODIC, (0.9, 1.0, 1.1)),
+                                         (bd.BOX_PERIODIC, (0.5, 2.0, 0.31))])
+@pytest.mark.parametrize("n", [0, 1, 2, 100, 1000, 5000])
+def test_pair_sets_equal(engine, oracle, kind, period, n):
+    x = np.random.default_rng(n + 7).normal(size=(n, 3)) * 1.3
+    for dcut in (0.3, 0.45):
+        got = sort_pairs(engine.nsearch_pairs(kind, period, n, dcut, x))
+        want = sort_pairs(oracle.nsearch_pairs(kind, period, n, dcut, x))
+        assert np.array_equal(got, want)
+        if n <= 1000:
+            assert np.array_equal(got, sort_pairs(brute_pairs(x, dcut, period)))
+
+
+@pytest.mark.parametrize("tag,n", [("t100", 100), ("t1000", 1000)])
+@pytest.mark.parametrize("kname,kind,period", [("open", bd.BOX_OPEN, None), ("per", bd.BOX_PERIODIC, (0.9, 1.0, 1.1))])
+def test_nsearch_golden(engine, tag, n, kname, kind, period):
+    g = np.load(os.path.join(GOLD, "nsearch.npz"))
+    x = g[f"{tag}_x"]
+    assert np.array_equal(engine.nsearch_buckets(kind, period, n, 0.3, x), g[f"{tag}_{kname}_buckets"])
+    assert np.array_equal(sort_pairs(engine.nsearch_pairs(kind, period, n, 0.3, x)),
+                          sort_pairs(g[f"{tag}_{kname}_pairs"]))
+
+
+def test_pair_search_dense_cluster_grows_rows(engine, oracle):
+    """every point within dcut of every other: rows longer than the default capacity"""
+    x = np.random.default_rng(3).normal(size=(300, 3)) * 0.01
+    got = sort_pairs(engine.nsearch_pairs(bd.BOX_OPEN, None, 300, 0.3, x))
+    assert len(got) == 300 * 299 // 2
+    assert np.array_equal(got, sort_pairs(oracle.nsearch_pairs(bd.BOX_OPEN, None, 300, 0.3, x)))
+
+
+def test_coincident_and_far_points(engine, oracle):
+    x = np.zeros((50, 3))
+    x[25:] += 1000.0
+    got = sort_pairs(engine.nsearch_pairs(bd.BOX_OPEN, None, 50, 0.3, x))
+    assert np.array_equal(got, sort_pairs(oracle.nsearch_pairs(bd.BOX_OPEN, None, 50, 0.3, x)))
+    assert len(got) == 2 * (25 * 24 // 2)
+
+
+# ---- forces, energies, statistics ---------------------------------------------------------------
+
+@pytest.mark.parametrize("name", sorted(SMALL))
+def test_forces_and_energies_match_oracle(engine, oracle, name):
+    scen = SMALL[name]()
+    se, ids = build(engine, scen)
+    so, _ = build(oracle, scen)
+    assert rel_force_error(se.compute_forces(), so.compute_forces()) <= FORCE_TOL
+    assert se.compute_energy() == pytest.approx(so.compute_energy(), rel=ENERGY_TOL)
+    for cls, key in CLASSES:
+        for ff in ids[key]:
+            fo = so.compute_forces(0, cls, ff)
+            assert rel_force_error(se.compute_forces(0, cls, ff), fo) <= FORCE_TOL, (key, ff)
+            assert se.compute_energy(0, cls, ff) == pytest.approx(so.compute_energy(0, cls, ff), rel=ENERGY_TOL, abs=1e-300)
+            if cls == bd.FF_WALL:
+                assert_close(se.get_wall_stats(ff), so.get_wall_stats(ff), 1e-11)
+    assert np.array_equal(sort_pairs(se.get_neighbor_list()), sort_pairs(so.get_neighbor_list()))
+
+
+@pytest.mark.parametrize("name", sorted(GOLDEN))
+def test_scenario_golden(engine, name):
+    """against arrays produced by the unmodified reference (tests/golden/make_golden.py)"""
+    g = np.load(os.path.join(GOLD, f"{name}.npz"))
+    scen = GOLDEN[name]()
+    assert np.array_equal(scen.positions[0], g["positions0"])
+    s, ids = build(engine, scen)
+    assert rel_force_error(s.compute_forces(), g["forces"]) <= FORCE_TOL
+    assert s.compute_energy() == pytest.approx(float(g["energy"]), rel=ENERGY_TOL)
+    assert np.array_equal(sort_pairs(s.get_neighbor_list()), sort_pairs(g["neighbor_list"]))
+    for cls, key in CLASSES:
+        for ff in ids[key]:
+            assert rel_force_error(s.compute_forces(0, cls, ff), g[f"forces_{key}{ff}"]) <= FORCE_TOL
+            assert s.compute_energy(0, cls, ff) == pytest.approx(float(g[f"energy_{key}{ff}"]), rel=ENERGY_TOL, abs=1e-300)
+            if cls == bd.FF_WALL:
+                assert_close(s.get_wall_stats(ff), g[f"stats_{key}{ff}"], 1e-11)
+    # validation mode: replay the normals the reference drew
+    s.step(GOLDEN_STEPS, scen.timestep, scen.temperature, replay_normals=g["normals"])
+    assert np.abs(s.get_positions() - g["positions_after"]).max() <= TRAJ_TOL
+    assert s.compute_energy() == pytest.approx(float(g["energy_after"]), rel=1e-9)
+
+
+# ---- trajectories -------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("name", sorted(SMALL))
+def test_replayed_trajectory_matches_oracle(engine, oracle, name):
+    scen = SMALL[name]()
+    se, _ = build(engine, scen)
+    so, _ = build(oracle, scen)
+    z = oracle.normals(5, 30 * scen.n * 3).reshape(30, scen.n, 3)
+    # two chunks: the second continues the previous-noise state
+    for s in (se, so):
+        s.step(20, scen.timestep, scen.temperature, replay_normals=z[:20], first_step=1)
+        s.step(10, scen.timestep, scen.temperature, replay_normals=z[20:], first_step=21)
+    assert np.abs(se.get_positions() - so.get_positions()).max() <= TRAJ_TOL
+
+
+def test_long_replay_rebuilds_with_the_oracle(engine, oracle):
+    """200 steps at a large timestep: the Verlet list is rebuilt several times, at the same steps."""
+    scen = sc.ab_sphere(20, 20)
+    se, _ = build(engine, scen)
+    so, _ = build(oracle, scen)
+    steps, dt = 200, 2e-4
+    z = oracle.normals(9, steps * scen.n * 3)
+    se.step(steps, dt, scen.temperature, replay_normals=z)
+    so.step(steps, dt, scen.temperature, replay_normals=z)
+    assert np.abs(se.get_positions() - so.get_positions()).max() <= 1e-8
+    ce, co = se.get_counters(), so.get_counters()
+    assert co.list_rebuilds >= 3
+    assert ce.list_rebuilds == co.list_rebuilds
+    assert ce.steps_done == steps
+
+
+def test_adaptive_timestep_matches_oracle(engine, oracle):
+    scen = SMALL["genome_10mb"]()
+    se, _ = build(engine, scen)
+    so, _ = build(oracle, scen)
+    z = oracle.normals(9, 10 * scen.n * 3)
+    for s in (se, so):
+        s.step(10, 1e-3, scen.temperature, spacestep=0.01, replay_normals=z)
+    assert se.get_last_timestep() == pytest.approx(so.get_last_timestep(), rel=1e-9)
+    assert np.abs(se.get_positions() - so.get_positions()).max() <= TRAJ_TOL
+
+
+def test_parameter_updates_every_step(engine, oracle):
+    """bead_scale / bond_scale / wall semiaxes change every step in the 100kb driver
+    (5-sim-genome/src/simulation_interphase/simulation_driver_interphase.cc:42-80)."""
+    scen = SMALL["genome_100kb"]()
+    se, ids = build(engine, scen)
+    so, _ = build(oracle, scen)
+    semi = np.array(scen.params["semiaxes"])
+    z = oracle.normals(3, 8 * scen.n * 3).reshape(8, scen.n, 3)
+    for k in range(8):
+        t = sc.c4_tables(scen.params, bead_scale=0.8 + 0.02 * k, bond_scale=0.9 + 0.01 * k)
+        semi = semi * 0.999
+        for s in (se, so):
+            s.update_pair_ff(ids["pair"][0], t["pair"], t["dcut"])
+            s.update_bond_ff(ids["bond"][0], t["chain_bond"])
+            s.update_bond_ff(ids["bond"][1], t["loop_bond"])
+            s.update_bond_ff(ids["bond"][2], t["nuc_bond"])
+            s.update_wall_ff(ids["wall"][0], (0, 0, 0), semi, t["wall_in"])
+            s.update_wall_ff(ids["wall"][1], (0, 0, 0), semi)
+            s.step(1, scen.timestep, scen.temperature, first_step=k + 1, replay_normals=z[k])
+        assert_close(se.get_wall_stats(ids["wall"][0]), so.get_wall_stats(ids["wall"][0]), 1e-10)
+    assert np.abs(se.get_positions() - so.get_positions()).max() <= TRAJ_TOL
+
+
+def test_enable_disable_forcefields(engine, oracle):
+    """forcefields are added/removed between phases (simulation_spindle/simulation_driver.cc:207,238)"""
+    scen = SMALL["genome_10mb"]()
+    se, ids = build(engine, scen)
+    so, _ = build(oracle, scen)
+    for s in (se, so):
+        s.set_ff_enabled(bd.FF_POINT, ids["point"][1], False)
+        s.set_ff_enabled(bd.FF_BEND, ids["bend"][0], False)
+    assert rel_force_error(se.compute_forces(), so.compute_forces()) <= FORCE_TOL
+    for s in (se, so):
+        s.set_ff_enabled(bd.FF_POINT, ids["point"][1], True)
+        s.set_ff_enabled(bd.FF_PAIR, ids["pair"][0], False)
+    assert rel_force_error(se.compute_forces(), so.compute_forces()) <= FORCE_TOL
+    assert se.compute_energy() == pytest.approx(so.compute_energy(), rel=ENERGY_TOL)
+
+
+# ---- replicas -----------------------------------------------------------------------------------
+
+def test_replica_ensemble_equals_independent_systems(engine, oracle):
+    R = 5
+    scen = sc.genome_10mb(total=320, replicas=R, bend_energy=0.7)
+    ens = bd.System(engine, scen.n, R)
+    scen.apply(ens)
+    steps = 12
+    z = np.stack([oracle.normals(100 + r, steps * scen.n * 3).reshape(steps, scen.n, 3) for r in range(R)], axis=1)
+    ens.step(steps, scen.timestep, scen.temperature, replay_normals=z)
+    for r in range(R):
+        so = bd.System(oracle, scen.n)
+        scen.apply(so, replicas=[r])
+        f0 = so.compute_forces()
+        so.step(steps, scen.timestep, scen.temperature, replay_normals=z[:, r])
+        assert np.abs(ens.get_positions(r) - so.get_positions()).max() <= TRAJ_TOL, r
+        assert ens.compute_energy(r) == pytest.approx(so.compute_energy(), rel=1e-9)
+        del f0
+
+
+# ---- production noise (Philox) -------------------------------------------------------------------
+
+def test_zero_temperature_freezes_free_particles(engine):
+    # micromd tests/simulation/test_brownian_dynamics.cc:42-57
+    n = 100
+    x = np.random.default_rng(0).normal(size=(n, 3))
+    s = bd.System(engine, n)
+    s.set_types(np.zeros(n, np.uint8), [1.0])
+    s.set_positions(x)
+    s.step(50, 1e-3, temperature=0.0, seed=1)
+    assert np.array_equal(s.get_positions(), x)
+
+
+def test_philox_is_reproducible_and_chunking_invariant(engine):
+    scen = SMALL["ab_sphere"]()
+    a, _ = build(engine, scen)
+    b, _ = build(engine, scen)
+    a.step(30, scen.timestep, scen.temperature, seed=42)
+    b.step(10, scen.timestep, scen.temperature, seed=42, first_step=1)
+    b.step(20, scen.timestep, scen.temperature, seed=42, first_step=11)
+    assert np.array_equal(a.get_positions(), b.get_positions())
+    c, _ = build(engine, scen)
+    c.step(30, scen.timestep, scen.temperature, seed=43)
+    assert not np.array_equal(a.get_positions(), c.get_positions())
+
+
+def test_free_diffusion_statistics(engine):
+    """<dx^2> = 2 kT mu t per axis for the BAOAB-limit scheme after many steps (the half-sum of
+    consecutive noises loses half a step's variance at each end)."""
+    n, steps, dt, kT, mu = 20000, 200, 1e-3, 0.7, 1.3
+    s = bd.System(engine, n)
+    s.set_types(np.zeros(n, np.uint8), [mu])
+    s.set_positions(np.zeros((n, 3)))
+    s.step(steps, dt, temperature=kT, seed=11)
+    x = s.get_positions()
+    want = 2 * kT * mu * dt * (steps - 0.5)
+    got = (x * x).mean(axis=0)
+    assert np.allclose(got, want, rtol=0.04), (got, want)
+    assert np.abs(x.mean(axis=0)).max() < 4 * np.sqrt(want / n)
+
+
+def test_harmonic_well_canonical_distribution(engine):
+    """micromd tests/simulation/test_brownian_dynamics.cc:135-215: radial distribution of
+    particles in a harmonic well follows the canonical distribution (KS test)."""
+    from scipy import stats
+
+    n, K, kT = 5000, 2.0, 0.8
+    s = bd.System(engine, n)
+    s.set_types(np.zeros(n, np.uint8), [1.0])
+    s.set_positions(np.zeros((n, 3)))
+    s.add_point_ff(bd.table([[bd.harmonic(K)]]), (0, 0, 0))
+    s.step(4000, 2e-3, temperature=kT, seed=5)
+    x = s.get_positions()
+    # each coordinate ~ N(0, kT/K)
+    for d in range(3):
+        p = stats.kstest(x[:, d] / np.sqrt(kT / K), "norm").pvalue
+        assert p > 1e-3, (d, p)
+
+
+# ---- errors -------------------------------------------------------------------------------------
+
+def test_error_reporting(engine):
+    s = bd.System(engine, 10)
+    with pytest.raises(bd.BackendError):
+        s.set_types(np.full(10, 3, np.uint8), [1.0])
+    with pytest.raises(bd.BackendError):
+        s.add_bond_ff(bd.table([[bd.harmonic(1.0)]]), [[0, 10]])
+    with pytest.raises(bd.BackendError):
+        s.compute_forces(0, bd.FF_WALL, 0)
+    with pytest.raises(bd.BackendError):
+        s.step(1, -1.0)
+
+
+def test_empty_system(engine):
+    s = bd.System(engine, 0)
+    s.step(3, 1e-3)
+    assert s.get_positions().shape == (0, 3)
+    assert s.compute_energy() == 0.0
