@@ -164,6 +164,8 @@ ENGINE_ONLY = {
     "set_positions_device": [C.c_void_p, C.c_void_p],
     "get_positions_device": [C.c_void_p, C.c_void_p],
     "get_launch_count": [C.c_void_p, _P(C.c_int64)],
+    "set_all_positions": [C.c_void_p, C.c_void_p],
+    "get_all_positions": [C.c_void_p, C.c_void_p],
 }
 
 
@@ -451,6 +453,13 @@ class System:
 
     def get_positions_device(self, dptr: int):
         self.b.call("get_positions_device", self.h, C.c_void_p(dptr))
+
+    def set_all_positions(self, host_ptr: int):
+        """host buffer [replicas][n][3] doubles (address), e.g. a pinned torch tensor's data_ptr()"""
+        self.b.call("set_all_positions", self.h, C.c_void_p(host_ptr))
+
+    def get_all_positions(self, host_ptr: int):
+        self.b.call("get_all_positions", self.h, C.c_void_p(host_ptr))
 
     def get_launch_count(self) -> int:
         v = C.c_int64(0)

@@ -90,7 +90,7 @@ struct DControl {
     uint32_t need_rebuild;   // host request (positions replaced, capacity changed)
     uint32_t doing_rebuild;  // latched copy for the kernels of one rebuild chain
     uint32_t overflow;       // beads whose ELL row overflowed (sticky)
-    uint32_t cell_overflow;
+    uint32_t max_row;        // longest ELL row at the last build
     unsigned long long rebuilds;
     unsigned long long max_disp2_bits;  // bits of max_i |x_i - x_i(build)|^2, kept by the step kernel
     unsigned long long listed_entries;  // sum of row lengths at the last build (2 x listed pairs)

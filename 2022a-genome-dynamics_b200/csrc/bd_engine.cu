@@ -80,14 +80,18 @@ struct bd_engine {
     DevBuf<bead4> pos[2], bpos;
     int cur = 0;
     DevBuf<uint32_t> slot_of, cellkey, rank, stage, cell_count, cell_start, block_sum, nbr, nnbr;
-    uint32_t cell_cap = 0, max_bits = 0, cap = 64;
+    uint32_t cell_cap = 0, max_bits = 0, cap = 32;
     DevBuf<DControl> ctl;
     DevBuf<DParams> d_params;
     DevBuf<DTerm> d_terms;
+    DevBuf<PairRow> d_pair_rows;
+    int prog = PROG_GENERIC;   // specialised pair program of the current tables (upload_params)
+    int fast_ff = 0;
+    bool specialize = true;
     DevBuf<double> force, wprev, xyz_stage, wall_partial, wall_out, energy_partial, energy_out, dt_prev, dt_last;
     DevBuf<unsigned long long> inter_partial, dt_bits, pair_count;
     DevBuf<uint8_t> d_type, d_pair_mask, d_point_mask;
-    DevBuf<double> replay;
+    DevBuf<double> replay, xyz_all;
 
     // topology (device CSR by original index)
     DevBuf<uint32_t> bond_start, bend_start, bend_adj, triples;
@@ -113,6 +117,11 @@ struct bd_engine {
     int64_t steps_done = 0;
     int64_t launches = 0;
     bool stats_adaptive_last = false;
+    bool list_verified = false;  // rows were checked for overflow since the last host-side change
+
+    // optional CUDA-event timing of the step kernel alone (bench.py roofline)
+    bool time_kernel = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> kernel_events;
 };
 
 static int sync_and_check(bd_engine *h);
@@ -180,10 +189,58 @@ static void refresh_dcut_max(bd_engine *h)
     h->hp.dcut_max = m;
 }
 
+/* Recognise the pair table's program (bd_step.cuh: PairProgram) and compile its rows.  Anything
+ * outside the recognised shapes keeps the interpreter. */
+static int compile_pair_program(bd_engine *h, std::vector<PairRow> &rows)
+{
+    h->prog = PROG_GENERIC;
+    if (!h->specialize) return 0;
+    int used = 0, ff = -1;
+    for (int k = 0; k < BD_MAX_PAIR_FF; k++)
+        if (h->pair[k].used && h->hp.pair[k].enabled) {
+            used++;
+            ff = k;
+        }
+    if (used != 1 || h->hp.pair[ff].has_targets) return 0;
+    int const T = h->hp.ntypes, nterms = h->pair[ff].nterms;
+    if (nterms > 2) return 0;
+    const DTerm *tab = h->hterms.data() + h->pair[ff].term_off;
+    bool second = false;
+    rows.assign((size_t) T * T, PairRow{0, 0, 0, 0});
+    for (int c = 0; c < T * T; c++) {
+        for (int k = 0; k < nterms; k++) {
+            const DTerm &t = tab[c * nterms + k];
+            if (t.kind == BD_TERM_NONE) continue;
+            if (t.kind != BD_TERM_SOFTCORE || t.q != 3 || t.cutoff2 != 0.0 || t.p != (k == 0 ? 2 : 8)) return 0;
+            double const coef = t.factor * ((double) (t.p * t.q) * t.energy * t.k2);
+            if (k == 0) {
+                rows[c].k2a = t.k2;
+                rows[c].ca = coef;
+            } else {
+                rows[c].k2b = t.k2;
+                rows[c].cb = coef;
+                second = true;
+            }
+        }
+    }
+    // the specialised kernels index rows by (own class, partner class): the table must be symmetric
+    for (int a = 0; a < T; a++)
+        for (int b = 0; b < a; b++)
+            if (std::memcmp(&rows[a * T + b], &rows[b * T + a], sizeof(PairRow)) != 0) return 0;
+    h->prog = second ? PROG_SC23_SC83 : PROG_SC23;
+    h->fast_ff = ff;
+    return 0;
+}
+
 static int upload_params(bd_engine *h)
 {
     if (!h->params_dirty) return 0;
     refresh_dcut_max(h);
+    std::vector<PairRow> rows;
+    compile_pair_program(h, rows);
+    if (h->prog != PROG_GENERIC)
+        CK(cudaMemcpyAsync(h->d_pair_rows.p, rows.data(), rows.size() * sizeof(PairRow), cudaMemcpyHostToDevice,
+                           h->stream));
     if (h->d_terms.count < h->hterms.size()) {
         CK(cudaStreamSynchronize(h->stream));
         CK(h->d_terms.alloc(std::max<size_t>(64, h->hterms.size() * 2)));
@@ -198,6 +255,7 @@ static int upload_params(bd_engine *h)
 
 static int request_rebuild(bd_engine *h)
 {
+    h->list_verified = false;
     static const uint32_t one = 1;
     CK(cudaMemcpyAsync(&h->ctl.p->need_rebuild, &one, sizeof one, cudaMemcpyHostToDevice, h->stream));
     return 0;
@@ -332,7 +390,7 @@ extern "C" int bd_create(int64_t n_beads, int32_t n_replicas, int32_t device, bd
         && h->cell_start.alloc((size_t) h->cell_cap + 1) == cudaSuccess
         && h->block_sum.alloc(h->cell_cap / SCAN_TILE + 2) == cudaSuccess
         && h->ctl.alloc(1) == cudaSuccess && h->d_params.alloc(1) == cudaSuccess
-        && h->d_terms.alloc(64) == cudaSuccess && h->force.alloc(3 * nt) == cudaSuccess
+        && h->d_terms.alloc(64) == cudaSuccess && h->d_pair_rows.alloc(BD_MAX_TYPES * BD_MAX_TYPES) == cudaSuccess && h->force.alloc(3 * nt) == cudaSuccess
         && h->xyz_stage.alloc(3 * (size_t) h->n) == cudaSuccess
         && h->wall_partial.alloc((size_t) h->replicas * h->chunks * BD_MAX_WALL_FF * WALL_STATS) == cudaSuccess
         && h->wall_out.alloc((size_t) h->replicas * BD_MAX_WALL_FF * WALL_STATS) == cudaSuccess
@@ -379,13 +437,14 @@ extern "C" int bd_destroy(bd_engine *h)
                     &h->block_sum, &h->nbr, &h->nnbr, &h->bond_start, &h->bend_start, &h->bend_adj, &h->triples})
         b->release();
     for (auto *b : {&h->force, &h->wprev, &h->xyz_stage, &h->wall_partial, &h->wall_out, &h->energy_partial,
-                    &h->energy_out, &h->dt_prev, &h->dt_last, &h->bend_energy, &h->replay})
+                    &h->energy_out, &h->dt_prev, &h->dt_last, &h->bend_energy, &h->replay, &h->xyz_all})
         b->release();
     for (auto *b : {&h->inter_partial, &h->dt_bits, &h->pair_count}) b->release();
     for (auto *b : {&h->d_type, &h->d_pair_mask, &h->d_point_mask, &h->bend_ff}) b->release();
     h->ctl.release();
     h->d_params.release();
     h->d_terms.release();
+    h->d_pair_rows.release();
     h->bond_adj.release();
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     delete h;
@@ -455,6 +514,31 @@ extern "C" int bd_get_positions(bd_engine *h, int32_t replica, double *xyz)
         CK(cudaGetLastError());
         CK(cudaMemcpyAsync(xyz, h->xyz_stage.p, 3 * (size_t) h->n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     }
+    return sync_and_check(h);
+}
+
+/* every replica at once, host buffers [replicas][n][3] (pinned buffers make the copies asynchronous) */
+extern "C" int bd_set_all_positions(bd_engine *h, const double *xyz)
+{
+    NEED(h);
+    if (h->ntot == 0) return 0;
+    if (h->xyz_all.count < 3 * (size_t) h->ntot) CK(h->xyz_all.alloc(3 * (size_t) h->ntot));
+    CK(cudaMemcpyAsync(h->xyz_all.p, xyz, 3 * (size_t) h->ntot * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    k_scatter_positions<<<blocks_for(h->ntot, 256), 256, 0, h->stream>>>(h->pos[h->cur].p, h->slot_of.p, h->xyz_all.p, 0, h->ntot);
+    h->launches++;
+    CK(cudaGetLastError());
+    return request_rebuild(h);
+}
+
+extern "C" int bd_get_all_positions(bd_engine *h, double *xyz)
+{
+    NEED(h);
+    if (h->ntot == 0) return 0;
+    if (h->xyz_all.count < 3 * (size_t) h->ntot) CK(h->xyz_all.alloc(3 * (size_t) h->ntot));
+    k_gather_positions<<<blocks_for(h->ntot, 256), 256, 0, h->stream>>>(h->pos[h->cur].p, h->slot_of.p, h->xyz_all.p, 0, h->ntot);
+    h->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(xyz, h->xyz_all.p, 3 * (size_t) h->ntot * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     return sync_and_check(h);
 }
 
@@ -700,11 +784,59 @@ static StepArrays step_arrays(bd_engine *h)
     A.wprev = h->wprev.p;
     A.dt_bits = h->dt_bits.p;
     A.dt_prev = h->dt_prev.p;
+    A.pair_rows = h->d_pair_rows.p;
+    A.ntypes2 = (uint32_t) (h->hp.ntypes * h->hp.ntypes);
+    A.fast_ff = h->fast_ff;
     A.n = h->n;
     A.replicas = h->replicas;
     A.ntot = h->ntot;
     A.chunks = h->chunks;
     return A;
+}
+
+template <int BOX>
+static void launch_step_box(int prog, dim3 grid, cudaStream_t st, const StepArrays &A, const StepScalars &S)
+{
+    switch (prog) {
+    case PROG_SC23_SC83: k_step_fused<BOX, PROG_SC23_SC83><<<grid, STEP_BLOCK, 0, st>>>(A, S); break;
+    case PROG_SC23: k_step_fused<BOX, PROG_SC23><<<grid, STEP_BLOCK, 0, st>>>(A, S); break;
+    default: k_step_fused<BOX, PROG_GENERIC><<<grid, STEP_BLOCK, 0, st>>>(A, S); break;
+    }
+}
+
+template <int BOX>
+static void launch_force_box(int prog, dim3 grid, cudaStream_t st, const StepArrays &A, const StepScalars &S,
+                             Select sel)
+{
+    switch (prog) {
+    case PROG_SC23_SC83: k_force<BOX, PROG_SC23_SC83><<<grid, STEP_BLOCK, 0, st>>>(A, S, sel); break;
+    case PROG_SC23: k_force<BOX, PROG_SC23><<<grid, STEP_BLOCK, 0, st>>>(A, S, sel); break;
+    default: k_force<BOX, PROG_GENERIC><<<grid, STEP_BLOCK, 0, st>>>(A, S, sel); break;
+    }
+}
+
+static void launch_step(bd_engine *h, const StepArrays &A, const StepScalars &S)
+{
+    dim3 const grid(h->chunks, h->replicas);
+    if (h->hp.box_kind == BD_BOX_PERIODIC) launch_step_box<BD_BOX_PERIODIC>(h->prog, grid, h->stream, A, S);
+    else launch_step_box<BD_BOX_OPEN>(h->prog, grid, h->stream, A, S);
+}
+
+static void launch_force(bd_engine *h, const StepArrays &A, const StepScalars &S, Select sel)
+{
+    dim3 const grid(h->chunks, h->replicas);
+    // the specialised programs evaluate exactly one pair forcefield; other selections interpret
+    bool const fast = sel.ff_class == BD_FF_ALL || (sel.ff_class == BD_FF_PAIR && sel.ff == h->fast_ff);
+    int const prog = fast ? h->prog : PROG_GENERIC;
+    if (h->hp.box_kind == BD_BOX_PERIODIC) launch_force_box<BD_BOX_PERIODIC>(prog, grid, h->stream, A, S, sel);
+    else launch_force_box<BD_BOX_OPEN>(prog, grid, h->stream, A, S, sel);
+}
+
+static void launch_integrate(bd_engine *h, const StepArrays &A, const StepScalars &S)
+{
+    dim3 const grid(h->chunks, h->replicas);
+    if (h->hp.box_kind == BD_BOX_PERIODIC) k_integrate<BD_BOX_PERIODIC><<<grid, STEP_BLOCK, 0, h->stream>>>(A, S);
+    else k_integrate<BD_BOX_OPEN><<<grid, STEP_BLOCK, 0, h->stream>>>(A, S);
 }
 
 /* Enqueue the rebuild chain.  Every kernel returns at once unless k_rebuild_begin latched a
@@ -747,16 +879,30 @@ static int sync_and_check(bd_engine *h)
     return 0;
 }
 
-/* Make the list current and make sure no row overflowed; grows the rows when they did. */
+/* Make the list current, make sure no row overflowed and keep 2x headroom over the longest row,
+ * so that a run of steps without host synchronisation does not outgrow the rows. */
 static int prepare_list(bd_engine *h)
 {
-    for (int attempt = 0; attempt < 6; attempt++) {
+    for (int attempt = 0; attempt < 12; attempt++) {
         if (enqueue_rebuild_chain(h)) return 1;
         CK(cudaStreamSynchronize(h->stream));
-        uint32_t overflow = 0;
-        CK(cudaMemcpy(&overflow, &h->ctl.p->overflow, sizeof overflow, cudaMemcpyDeviceToHost));
-        if (!overflow) return 0;
-        h->cap *= 2;
+        DControl c;
+        CK(cudaMemcpy(&c, h->ctl.p, sizeof c, cudaMemcpyDeviceToHost));
+        uint32_t const limit = std::max<uint32_t>(h->n, 16u);
+        uint32_t want = h->cap;
+        if (c.overflow) {
+            if (h->cap >= h->n) return fail("bd: neighbour rows overflow although they hold every bead");
+            want = std::min<uint32_t>(h->cap * 4, limit);
+        } else if (2 * c.max_row > h->cap && h->cap < limit) {
+            want = std::min<uint32_t>((2 * c.max_row + 15u) & ~15u, limit);
+        }
+        if (want == h->cap) {
+            h->list_verified = true;
+            return 0;
+        }
+        if ((double) want * h->ntot * sizeof(uint32_t) > 64e9)
+            return fail("bd: neighbour rows would exceed 64 GB (list radius too large for this density)");
+        h->cap = want;
         if (alloc_rows(h)) return 1;
         CK(cudaMemset(&h->ctl.p->overflow, 0, sizeof(uint32_t)));
         if (request_rebuild(h)) return 1;
@@ -803,6 +949,8 @@ extern "C" int bd_step(bd_engine *h, const bd_step_config *cfg)
         }
     }
 
+    if (!h->list_verified && prepare_list(h)) return 1;
+
     // replayed normals are staged through a bounded device buffer
     size_t const max_stage_steps = std::max<size_t>(1, ((size_t) 256 << 20) / (per_step * sizeof(double)));
     size_t staged_from = 0, staged_count = 0;
@@ -813,7 +961,6 @@ extern "C" int bd_step(bd_engine *h, const bd_step_config *cfg)
     S.seed = cfg->seed;
     S.adaptive = adaptive;
     S.replay = nullptr;
-    dim3 const grid(h->chunks, h->replicas);
     Select const all = {BD_FF_ALL, -1};
 
     for (int64_t k = 0; k < cfg->steps; k++) {
@@ -836,11 +983,21 @@ extern "C" int bd_step(bd_engine *h, const bd_step_config *cfg)
         S.kT_prev = h->last_kT;
         if (replay) S.replay = h->replay.p + ((size_t) k - staged_from) * per_step;
         if (!adaptive) {
-            k_step_fused<<<grid, STEP_BLOCK, 0, st>>>(A, S);
+            cudaEvent_t e0 = nullptr, e1 = nullptr;
+            if (h->time_kernel) {
+                CK(cudaEventCreate(&e0));
+                CK(cudaEventCreate(&e1));
+                CK(cudaEventRecord(e0, st));
+            }
+            launch_step(h, A, S);
+            if (h->time_kernel) {
+                CK(cudaEventRecord(e1, st));
+                h->kernel_events.emplace_back(e0, e1);
+            }
             h->launches += 1;
         } else {
-            k_force<<<grid, STEP_BLOCK, 0, st>>>(A, S, all);
-            k_integrate<<<grid, STEP_BLOCK, 0, st>>>(A, S);
+            launch_force(h, A, S, all);
+            launch_integrate(h, A, S);
             k_dt_rotate<<<blocks_for(h->replicas, 128), 128, 0, st>>>(h->dt_bits.p, h->dt_prev.p, h->dt_last.p,
                                                                       cfg->timestep, h->replicas);
             h->launches += 3;
@@ -894,7 +1051,7 @@ extern "C" int bd_compute_forces(bd_engine *h, int32_t replica, int32_t ff_class
     StepScalars S;
     std::memset(&S, 0, sizeof S);
     Select const sel = {ff_class, ff};
-    k_force<<<dim3(h->chunks, h->replicas), STEP_BLOCK, 0, h->stream>>>(A, S, sel);
+    launch_force(h, A, S, sel);
     k_gather_forces<<<blocks_for(h->n, 256), 256, 0, h->stream>>>(h->force.p, h->slot_of.p, h->xyz_stage.p,
                                                                   (uint32_t) replica * h->n, h->n);
     h->launches += 2;
@@ -1010,6 +1167,15 @@ extern "C" int bd_set_option(bd_engine *h, const char *name, double value)
         h->params_dirty = true;
         return request_rebuild(h);
     }
+    if (key == "specialize") {
+        h->specialize = value != 0;
+        h->params_dirty = true;
+        return 0;
+    }
+    if (key == "time_kernel") {
+        h->time_kernel = value != 0;
+        return 0;
+    }
     if (key == "list_capacity") {
         if (!(value >= 1 && value <= 4096)) return fail("bd_set_option: list_capacity out of range");
         CK(cudaStreamSynchronize(h->stream));
@@ -1028,6 +1194,25 @@ extern "C" int bd_get_option(bd_engine *h, const char *name, double *value)
     if (key == "verlet_factor") *value = h->hp.verlet_factor;
     else if (key == "list_capacity") *value = h->cap;
     else if (key == "block_size") *value = STEP_BLOCK;
+    else if (key == "specialize") *value = h->specialize;
+    else if (key == "pair_program") {
+        if (upload_params(h)) return 1;
+        *value = h->prog;
+    }
+    else if (key == "kernel_ms_avg") {
+        // mean duration of the fused step kernel over the launches recorded since the last query
+        CK(cudaStreamSynchronize(h->stream));
+        double total = 0;
+        for (auto &ev : h->kernel_events) {
+            float ms = 0;
+            CK(cudaEventElapsedTime(&ms, ev.first, ev.second));
+            total += ms;
+            cudaEventDestroy(ev.first);
+            cudaEventDestroy(ev.second);
+        }
+        *value = h->kernel_events.empty() ? 0.0 : total / (double) h->kernel_events.size();
+        h->kernel_events.clear();
+    }
     else return fail("bd_get_option: unknown option '" + key + "'");
     return 0;
 }

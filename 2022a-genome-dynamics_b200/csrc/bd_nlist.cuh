@@ -64,6 +64,7 @@ __global__ void k_rebuild_begin(DControl *ctl, const DParams *params)
     if (need) {
         ctl->rebuilds += 1;
         ctl->listed_entries = 0;
+        ctl->max_row = 0;
         ctl->max_disp2_bits = 0;
         for (int d = 0; d < 3; d++) {
             ctl->bbox_lo[d] = ~0ull;
@@ -363,8 +364,15 @@ __global__ void __launch_bounds__(NL_BLOCK) k_rows(NlistArrays A)
     }
     // listed entries (2 x listed pairs)
     unsigned long long tot = count;
-    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
-    if ((threadIdx.x & 31) == 0 && tot) atomicAdd(&A.ctl->listed_entries, tot);
+    uint32_t longest = count;
+    for (int o = 16; o > 0; o >>= 1) {
+        tot += __shfl_xor_sync(0xffffffffu, tot, o);
+        longest = max(longest, __shfl_xor_sync(0xffffffffu, longest, o));
+    }
+    if ((threadIdx.x & 31) == 0 && tot) {
+        atomicAdd(&A.ctl->listed_entries, tot);
+        atomicMax(&A.ctl->max_row, longest);
+    }
 }
 
 /* Verlet list as unordered pairs of original indices (validation, get_neighbor_list) */

@@ -48,6 +48,9 @@ struct StepArrays {
     double *wprev;                // [Ntot][3] by original global index (replay mode)
     unsigned long long *dt_bits;  // [replicas] adaptive: min timestep of the current step
     const double *dt_prev;        // [replicas] adaptive: timestep of the previous step
+    const struct PairRow *pair_rows;    // compiled table of the specialised pair program
+    uint32_t ntypes2;             // rows in pair_rows
+    int32_t fast_ff;              // the pair forcefield the specialised program evaluates
     uint32_t n, replicas, ntot, chunks;
 };
 
@@ -81,43 +84,117 @@ __device__ inline void store_bead(bead4 *p, double x, double y, double z, uint64
     q[1] = make_double2(z, __longlong_as_double((long long) w));
 }
 
-/* forces of all selected forcefields on the bead at slot s; wall statistics into ws[][4] */
-__device__ inline d3 bead_force(const StepArrays &A, const DParams &P, Select sel, uint32_t s,
-                                uint32_t replica, const bead4 &me, double ws[BD_MAX_WALL_FF][WALL_STATS],
-                                uint32_t &interactions)
+// ---- compile-time specialisations -----------------------------------------------------------------
+//
+// The reference builds its pair potential from expression templates, so the compiler sees
+// `a*softcore<2,3> + b*softcore<8,3>` as straight-line code (MD/potential/sum_potential.hpp:32-40,
+// softcore_potential.hpp:49-61).  The engine gets the same effect by recognising the flattened
+// table's program on the host and launching a kernel instantiated for it; every other table runs
+// through the run-time interpreter (pot_force_scalar).
+
+enum PairProgram {
+    PROG_GENERIC = 0,     // interpreter: any terms, several pair forcefields, target subsets
+    PROG_SC23_SC83 = 1,   // f0*softcore<2,3> + f1*softcore<8,3>   (4-sim-ab, 5-sim-genome 100kb, 3-sim-1kb)
+    PROG_SC23 = 2,        // f0*softcore<2,3>                      (5-sim-genome 10Mb)
+    PROG_COUNT = 3
+};
+
+/* one row of a compiled pair table: c = factor * P * Q * energy * k2, k2 = 1 / diameter^2 */
+struct __align__(16) PairRow {
+    double k2a, ca, k2b, cb;
+};
+
+template <int BOX>
+__device__ __forceinline__ d3 displacement_t(const DParams &P, double ax, double ay, double az, double bx,
+                                             double by, double bz)
 {
-    d3 F = {0.0, 0.0, 0.0};
+    d3 r;
+    r.x = __dsub_rn(ax, bx);
+    r.y = __dsub_rn(ay, by);
+    r.z = __dsub_rn(az, bz);
+    if (BOX == BD_BOX_PERIODIC) {
+        r.x = round_mod_exact(r.x, P.period[0], P.inv_period[0]);
+        r.y = round_mod_exact(r.y, P.period[1], P.inv_period[1]);
+        r.z = round_mod_exact(r.z, P.period[2], P.inv_period[2]);
+    }
+    return r;
+}
+
+/* softcore<P,3> force scalar without the factor: c * g^2 * (u2)^((P-2)/2), g = 1 - (u2)^(P/2) */
+template <int PROG>
+__device__ __forceinline__ double compiled_pair_scalar(const PairRow &row, double r2)
+{
+    double const ua = row.k2a * r2;
+    double const ga = 1.0 - ua;
+    double s = ga >= 0.0 ? row.ca * ga * ga : 0.0;
+    if (PROG == PROG_SC23_SC83) {
+        double const ub = row.k2b * r2;
+        double const vb = ub * ub * ub;
+        double const gb = 1.0 - vb * ub;
+        s += gb >= 0.0 ? row.cb * gb * gb * vb : 0.0;
+    }
+    return s;
+}
+
+/* non-bonded forces on the bead at slot s from its Verlet row */
+template <int BOX, int PROG>
+__device__ __forceinline__ void pair_forces(const StepArrays &A, const DParams &P, const PairRow *rows,
+                                            Select sel, uint32_t s, const bead4 &me, d3 &F,
+                                            uint32_t &interactions)
+{
+    uint32_t const oi = w_orig(me.w), ti = w_type(me.w);
+    int const T = P.ntypes;
+    uint32_t const m = A.nnbr[s];
+    const uint32_t *col = A.nbr + s;
+    if (PROG != PROG_GENERIC) {
+        double const dcut2 = P.pair[A.fast_ff].dcut2;
+        const PairRow *mine = rows + ti * T;
+        for (uint32_t k = 0; k < m; k++) {
+            uint32_t const j = col[(size_t) k * A.ntot];
+            bead4 const o = load_bead(A.pos + j);
+            d3 const r = displacement_t<BOX>(P, me.x, me.y, me.z, o.x, o.y, o.z);
+            double const r2 = sqnorm_exact(r.x, r.y, r.z);
+            if (r2 <= dcut2) {
+                double const sc = compiled_pair_scalar<PROG>(mine[w_type(o.w)], r2);
+                F.x += sc * r.x; F.y += sc * r.y; F.z += sc * r.z;
+                interactions += oi < w_orig(o.w) ? 1u : 0u;
+            }
+        }
+        return;
+    }
+    bool any_pair = false;
+    for (int f = 0; f < BD_MAX_PAIR_FF; f++) any_pair |= ff_on(sel, BD_FF_PAIR, f, P.pair[f].enabled);
+    if (!any_pair) return;
+    for (uint32_t k = 0; k < m; k++) {
+        uint32_t const j = col[(size_t) k * A.ntot];
+        bead4 const o = load_bead(A.pos + j);
+        d3 const r = displacement_t<BOX>(P, me.x, me.y, me.z, o.x, o.y, o.z);
+        double const r2 = sqnorm_exact(r.x, r.y, r.z);
+        uint32_t const oj = w_orig(o.w), tj = w_type(o.w);
+        int const cell = oi < oj ? (int) (ti * T + tj) : (int) (tj * T + ti);
+        bool hit = false;
+#pragma unroll
+        for (int f = 0; f < BD_MAX_PAIR_FF; f++) {
+            const DPair &pf = P.pair[f];
+            if (!ff_on(sel, BD_FF_PAIR, f, pf.enabled) || r2 > pf.dcut2) continue;
+            if (pf.has_targets && !((w_pair_mask(me.w) >> f) & (w_pair_mask(o.w) >> f) & 1u)) continue;
+            double const sc = pot_force_scalar(A.terms + pf.term_off + cell * pf.nterms, pf.nterms, r2);
+            F.x += sc * r.x; F.y += sc * r.y; F.z += sc * r.z;
+            hit = true;
+        }
+        interactions += (hit && oi < oj) ? 1u : 0u;
+    }
+}
+
+/* bonded pairs, bending triples and point sources acting on one bead */
+__device__ __forceinline__ void bonded_forces(const StepArrays &A, const DParams &P, Select sel,
+                                              uint32_t replica, const bead4 &me, d3 &F)
+{
     uint32_t const oi = w_orig(me.w), ti = w_type(me.w);
     int const T = P.ntypes;
     uint32_t const base = replica * A.n;
 
-    // ---- non-bonded pairs over the Verlet row ----
-    bool any_pair = false;
-    for (int f = 0; f < BD_MAX_PAIR_FF; f++) any_pair |= ff_on(sel, BD_FF_PAIR, f, P.pair[f].enabled);
-    if (any_pair) {
-        uint32_t const m = A.nnbr[s];
-        for (uint32_t k = 0; k < m; k++) {
-            uint32_t const j = A.nbr[(size_t) k * A.ntot + s];
-            bead4 const o = load_bead(A.pos + j);
-            d3 const r = displacement(P, me.x, me.y, me.z, o.x, o.y, o.z);
-            double const r2 = sqnorm_exact(r.x, r.y, r.z);
-            uint32_t const oj = w_orig(o.w), tj = w_type(o.w);
-            int const cell = oi < oj ? (int) (ti * T + tj) : (int) (tj * T + ti);
-            bool hit = false;
-#pragma unroll
-            for (int f = 0; f < BD_MAX_PAIR_FF; f++) {
-                const DPair &pf = P.pair[f];
-                if (!ff_on(sel, BD_FF_PAIR, f, pf.enabled) || r2 > pf.dcut2) continue;
-                if (pf.has_targets && !((w_pair_mask(me.w) >> f) & (w_pair_mask(o.w) >> f) & 1u)) continue;
-                double const sc = pot_force_scalar(A.terms + pf.term_off + cell * pf.nterms, pf.nterms, r2);
-                F.x += sc * r.x; F.y += sc * r.y; F.z += sc * r.z;
-                hit = true;
-            }
-            interactions += (hit && oi < oj) ? 1u : 0u;
-        }
-    }
-
-    // ---- bonded pairs (no minimum image: bonded_pairwise_forcefield.hpp:64) ----
+    // bonded pairs (no minimum image: bonded_pairwise_forcefield.hpp:64)
     {
         uint32_t const b = A.bond_start[oi], e = A.bond_start[oi + 1];
         for (uint32_t k = b; k < e; k++) {
@@ -128,16 +205,17 @@ __device__ inline d3 bead_force(const StepArrays &A, const DParams &P, Select se
             bead4 const o = load_bead(A.pos + A.slot_of[base + adj.x]);
             uint32_t const tj = w_type(o.w);
             bool const second = (adj.y >> 8) & 1u;
-            // r = x_first - x_second, row (type_first, type_second); this bead gets +f or -f
-            double rx = me.x - o.x, ry = me.y - o.y, rz = me.z - o.z;
+            // the force on this bead is scalar * (x_me - x_partner) whichever end it is; only the
+            // table row depends on the order (type_first, type_second)
+            double const rx = me.x - o.x, ry = me.y - o.y, rz = me.z - o.z;
             int const cell = second ? (int) (tj * T + ti) : (int) (ti * T + tj);
-            double const r2 = rx * rx + ry * ry + rz * rz;
-            double const sc = pot_force_scalar(A.terms + bf.term_off + cell * bf.nterms, bf.nterms, r2);
+            double const sc = pot_force_scalar(A.terms + bf.term_off + cell * bf.nterms, bf.nterms,
+                                               rx * rx + ry * ry + rz * rz);
             F.x += sc * rx; F.y += sc * ry; F.z += sc * rz;
         }
     }
 
-    // ---- bending triples (cosine_bending_potential.hpp:43-60) ----
+    // bending triples (cosine_bending_potential.hpp:43-60)
     {
         uint32_t const b = A.bend_start[oi], e = A.bend_start[oi + 1];
         for (uint32_t k = b; k < e; k++) {
@@ -165,64 +243,7 @@ __device__ inline d3 bead_force(const StepArrays &A, const DParams &P, Select se
         }
     }
 
-    // ---- walls ----
-#pragma unroll 1
-    for (int f = 0; f < BD_MAX_WALL_FF; f++) {
-        const DWall &wf = P.wall[f];
-        ws[f][0] = ws[f][1] = ws[f][2] = ws[f][3] = 0.0;
-        if (!ff_on(sel, BD_FF_WALL, f, wf.enabled)) continue;
-        double const rx = me.x - wf.center[0], ry = me.y - wf.center[1], rz = me.z - wf.center[2];
-        const DTerm *row = A.terms + wf.term_off + ti * wf.nterms;
-        if (wf.shape == BD_WALL_SPHERE) {
-            // sphere_surface_forcefield.hpp:108-143
-            double const radius = wf.semi[0];
-            double const r2 = rx * rx + ry * ry + rz * rz;
-            if (r2 == 0.0) continue;
-            double const r1 = sqrt(r2);
-            double const scale = radius / r1;
-            double const sx = rx - scale * rx, sy = ry - scale * ry, sz = rz - scale * rz;
-            bool const inside = r2 < radius * radius;
-            bool const active = inside ? wf.direction == BD_WALL_INWARD : wf.direction == BD_WALL_OUTWARD;
-            if (!active) continue;
-            double const sc = pot_force_scalar(row, wf.nterms, sx * sx + sy * sy + sz * sz);
-            double const fx = sc * sx, fy = sc * sy, fz = sc * sz;
-            double const pr = (fx * rx + fy * ry + fz * rz) / r2;  // project(force, r)
-            F.x += fx + scale * (pr * rx - fx);
-            F.y += fy + scale * (pr * ry - fy);
-            F.z += fz + scale * (pr * rz - fz);
-            ws[f][0] = -(fx * rx + fy * ry + fz * rz) / r1;
-        } else {
-            // ellipsoid_surface_forcefield.hpp:54-99 (evaluate_point), :167-211
-            double const qx = 1.0 / (wf.semi[0] * wf.semi[0]), qy = 1.0 / (wf.semi[1] * wf.semi[1]),
-                         qz = 1.0 / (wf.semi[2] * wf.semi[2]);
-            double const dx = qx * rx, dy = qy * ry, dz = qz * rz;  // dual
-            double const d2 = dx * dx + dy * dy + dz * dz;
-            if (d2 == 0.0) continue;
-            double const implicit = dx * rx + dy * ry + dz * rz - 1.0;
-            double const scale = implicit / (2.0 * d2);
-            double const ex = scale * dx, ey = scale * dy, ez = scale * dz;  // delta
-            bool const inside = implicit < 0.0;
-            bool const active = inside ? wf.direction == BD_WALL_INWARD : wf.direction == BD_WALL_OUTWARD;
-            if (!active) continue;
-            double const e2 = ex * ex + ey * ey + ez * ez;
-            double const sc = pot_force_scalar(row, wf.nterms, e2);
-            double const bx = sc * ex, by = sc * ey, bz = sc * ez;  // basic force
-            double const pr = e2 != 0.0 ? (bx * ex + by * ey + bz * ez) / e2 : 0.0;
-            double const ix = pr * ex, iy = pr * ey, iz = pr * ez;  // iso = project(basic, delta)
-            double const fx = ix + ((bx - ix) - ix) * (scale * qx);
-            double const fy = iy + ((by - iy) - iy) * (scale * qy);
-            double const fz = iz + ((bz - iz) - iz) * (scale * qz);
-            F.x += fx; F.y += fy; F.z += fz;
-            double const en = e2 != 0.0 ? (inside ? -1.0 : 1.0) / sqrt(e2) : 0.0;
-            double const nx = en * ex, ny = en * ey, nz = en * ez;  // outward normal
-            ws[f][0] = -(fx * nx + fy * ny + fz * nz);
-            ws[f][1] = -(nx > 0 ? fx : -fx);
-            ws[f][2] = -(ny > 0 ? fy : -fy);
-            ws[f][3] = -(nz > 0 ? fz : -fz);
-        }
-    }
-
-    // ---- point sources ----
+    // point sources (point_source_forcefield.hpp:78-103)
 #pragma unroll 1
     for (int f = 0; f < BD_MAX_POINT_FF; f++) {
         const DPoint &pf = P.point[f];
@@ -233,33 +254,122 @@ __device__ inline d3 bead_force(const StepArrays &A, const DParams &P, Select se
                                            rx * rx + ry * ry + rz * rz);
         F.x += sc * rx; F.y += sc * ry; F.z += sc * rz;
     }
-    return F;
 }
 
-/* block-level sums of the wall statistics -> wall_partial[replica][chunk][wall][4] */
-__device__ inline void reduce_wall_stats(const StepArrays &A, const DParams &P, Select sel,
-                                         uint32_t replica, uint32_t chunk,
-                                         double ws[BD_MAX_WALL_FF][WALL_STATS])
+/* one wall forcefield on one bead: adds the force, returns the reaction statistics in st[4] */
+__device__ __forceinline__ void wall_force(const StepArrays &A, const DWall &wf, const bead4 &me, d3 &F,
+                                           double st[WALL_STATS])
 {
-    __shared__ double red[STEP_BLOCK / 32][WALL_STATS];
+    st[0] = st[1] = st[2] = st[3] = 0.0;
+    double const rx = me.x - wf.center[0], ry = me.y - wf.center[1], rz = me.z - wf.center[2];
+    const DTerm *row = A.terms + wf.term_off + w_type(me.w) * wf.nterms;
+    if (wf.shape == BD_WALL_SPHERE) {
+        // sphere_surface_forcefield.hpp:108-143
+        double const radius = wf.semi[0];
+        double const r2 = rx * rx + ry * ry + rz * rz;
+        if (r2 == 0.0) return;
+        bool const inside = r2 < radius * radius;
+        if (inside ? wf.direction != BD_WALL_INWARD : wf.direction != BD_WALL_OUTWARD) return;
+        double const r1 = sqrt(r2);
+        double const scale = radius / r1;
+        double const sx = rx - scale * rx, sy = ry - scale * ry, sz = rz - scale * rz;
+        double const sc = pot_force_scalar(row, wf.nterms, sx * sx + sy * sy + sz * sz);
+        double const fx = sc * sx, fy = sc * sy, fz = sc * sz;
+        double const fr = fx * rx + fy * ry + fz * rz;
+        double const pr = fr / r2;  // project(force, r)
+        F.x += fx + scale * (pr * rx - fx);
+        F.y += fy + scale * (pr * ry - fy);
+        F.z += fz + scale * (pr * rz - fz);
+        st[0] = -fr / r1;
+    } else {
+        // ellipsoid_surface_forcefield.hpp:54-99 (evaluate_point), :167-211
+        double const qx = 1.0 / (wf.semi[0] * wf.semi[0]), qy = 1.0 / (wf.semi[1] * wf.semi[1]),
+                     qz = 1.0 / (wf.semi[2] * wf.semi[2]);
+        double const dx = qx * rx, dy = qy * ry, dz = qz * rz;  // dual
+        double const d2 = dx * dx + dy * dy + dz * dz;
+        if (d2 == 0.0) return;
+        double const implicit = dx * rx + dy * ry + dz * rz - 1.0;
+        bool const inside = implicit < 0.0;
+        if (inside ? wf.direction != BD_WALL_INWARD : wf.direction != BD_WALL_OUTWARD) return;
+        double const scale = implicit / (2.0 * d2);
+        double const ex = scale * dx, ey = scale * dy, ez = scale * dz;  // delta
+        double const e2 = ex * ex + ey * ey + ez * ez;
+        double const sc = pot_force_scalar(row, wf.nterms, e2);
+        double const bx = sc * ex, by = sc * ey, bz = sc * ez;  // basic force
+        double const pr = e2 != 0.0 ? (bx * ex + by * ey + bz * ez) / e2 : 0.0;
+        double const ix = pr * ex, iy = pr * ey, iz = pr * ez;  // iso = project(basic, delta)
+        double const fx = ix + ((bx - ix) - ix) * (scale * qx);
+        double const fy = iy + ((by - iy) - iy) * (scale * qy);
+        double const fz = iz + ((bz - iz) - iz) * (scale * qz);
+        F.x += fx; F.y += fy; F.z += fz;
+        double const en = e2 != 0.0 ? (inside ? -1.0 : 1.0) / sqrt(e2) : 0.0;
+        double const nx = en * ex, ny = en * ey, nz = en * ez;  // outward normal
+        st[0] = -(fx * nx + fy * ny + fz * nz);
+        st[1] = -(nx > 0 ? fx : -fx);
+        st[2] = -(ny > 0 ? fy : -fy);
+        st[3] = -(nz > 0 ? fz : -fz);
+    }
+}
+
+struct StepShared {
+    DParams P;
+    PairRow rows[BD_MAX_TYPES * BD_MAX_TYPES];
+    double wall_red[STEP_BLOCK / 32][BD_MAX_WALL_FF][WALL_STATS];
+    uint32_t inter[STEP_BLOCK / 32];
+};
+
+template <int PROG>
+__device__ __forceinline__ void load_shared(StepShared &sh, const StepArrays &A)
+{
+    for (uint32_t i = threadIdx.x; i < sizeof(DParams) / 4; i += blockDim.x)
+        ((uint32_t *) &sh.P)[i] = ((const uint32_t *) A.params)[i];
+    if (PROG != PROG_GENERIC) {
+        uint32_t const words = A.ntypes2 * (sizeof(PairRow) / 4);
+        for (uint32_t i = threadIdx.x; i < words; i += blockDim.x)
+            ((uint32_t *) sh.rows)[i] = ((const uint32_t *) A.pair_rows)[i];
+    }
+    __syncthreads();
+}
+
+/* all selected forces on one bead; every thread of the block must call this (walls reduce their
+ * statistics across the block), `live` masks the threads past the end of the replica */
+template <int BOX, int PROG>
+__device__ __forceinline__ d3 block_forces(const StepArrays &A, StepShared &sh, Select sel, bool live,
+                                           uint32_t s, uint32_t replica, uint32_t chunk, const bead4 &me,
+                                           uint32_t &interactions)
+{
+    const DParams &P = sh.P;
+    d3 F = {0.0, 0.0, 0.0};
+    if (live) {
+        pair_forces<BOX, PROG>(A, P, sh.rows, sel, s, me, F, interactions);
+        bonded_forces(A, P, sel, replica, me, F);
+    }
+    bool any_wall = false;
 #pragma unroll 1
     for (int f = 0; f < BD_MAX_WALL_FF; f++) {
-        if (!ff_on(sel, BD_FF_WALL, f, P.wall[f].enabled)) continue;  // block-uniform
-        double v[WALL_STATS] = {ws[f][0], ws[f][1], ws[f][2], ws[f][3]};
+        const DWall &wf = P.wall[f];
+        if (!ff_on(sel, BD_FF_WALL, f, wf.enabled)) continue;  // block-uniform
+        any_wall = true;
+        double st[WALL_STATS] = {0.0, 0.0, 0.0, 0.0};
+        if (live) wall_force(A, wf, me, F, st);
 #pragma unroll
-        for (int c = 0; c < WALL_STATS; c++)
-            for (int o = 16; o > 0; o >>= 1) v[c] += __shfl_xor_sync(0xffffffffu, v[c], o);
-        if ((threadIdx.x & 31) == 0)
-            for (int c = 0; c < WALL_STATS; c++) red[threadIdx.x >> 5][c] = v[c];
-        __syncthreads();
-        if (threadIdx.x < WALL_STATS) {
-            double t = 0.0;
-            for (int w = 0; w < STEP_BLOCK / 32; w++) t += red[w][threadIdx.x];
-            A.wall_partial[(((size_t) replica * A.chunks + chunk) * BD_MAX_WALL_FF + f) * WALL_STATS
-                           + threadIdx.x] = t;
+        for (int c = 0; c < WALL_STATS; c++) {
+            for (int o = 16; o > 0; o >>= 1) st[c] += __shfl_xor_sync(0xffffffffu, st[c], o);
+            if ((threadIdx.x & 31) == 0) sh.wall_red[threadIdx.x >> 5][f][c] = st[c];
         }
-        __syncthreads();
     }
+    if (any_wall) {
+        __syncthreads();
+        if (threadIdx.x < BD_MAX_WALL_FF * WALL_STATS) {
+            int const f = threadIdx.x / WALL_STATS, c = threadIdx.x % WALL_STATS;
+            if (ff_on(sel, BD_FF_WALL, f, P.wall[f].enabled)) {
+                double t = 0.0;
+                for (int w = 0; w < STEP_BLOCK / 32; w++) t += sh.wall_red[w][f][c];
+                A.wall_partial[(((size_t) replica * A.chunks + chunk) * BD_MAX_WALL_FF + f) * WALL_STATS + c] = t;
+            }
+        }
+    }
+    return F;
 }
 
 __device__ inline void load_params(DParams &P, const DParams *src)
@@ -269,10 +379,13 @@ __device__ inline void load_params(DParams &P, const DParams *src)
     __syncthreads();
 }
 
-/* MD/simulation/detail/brownian_simulator.hpp:57-75 + neighbor_list.hpp:132-158 for one bead */
-__device__ inline double integrate_bead(const StepArrays &A, const DParams &P, const StepScalars &S,
-                                        uint32_t s, uint32_t replica, const bead4 &me, d3 F, double dt,
-                                        double dt_prev)
+
+/* MD/simulation/detail/brownian_simulator.hpp:57-75 for one bead; returns the squared distance
+ * from the bead's position at the last list build (neighbor_list.hpp:138-157) */
+template <int BOX>
+__device__ __forceinline__ double integrate_bead(const StepArrays &A, const DParams &P, const StepScalars &S,
+                                                 uint32_t s, uint32_t replica, const bead4 &me, d3 F,
+                                                 double dt, double dt_prev)
 {
     uint32_t const oi = w_orig(me.w);
     double const mu = P.mobility[w_type(me.w)];
@@ -300,15 +413,14 @@ __device__ inline double integrate_bead(const StepArrays &A, const DParams &P, c
     x += 0.5 * (wx + px); y += 0.5 * (wy + py); z2 += 0.5 * (wz + pz);
     store_bead(A.pos_out + s, x, y, z2, me.w);
 
-    // distance from the build position, for the Verlet-list skin test
     bead4 const b0 = load_bead(A.bpos + s);
-    d3 const d = displacement(P, x, y, z2, b0.x, b0.y, b0.z);
+    d3 const d = displacement_t<BOX>(P, x, y, z2, b0.x, b0.y, b0.z);
     return sqnorm_exact(d.x, d.y, d.z);
 }
 
 /* fold the block's largest displacement^2 into the control block; the rebuild decision itself is
  * taken by k_rebuild_begin before the next force evaluation (neighbor_list.hpp:132-158) */
-__device__ inline void publish_displacement(const StepArrays &A, double moved2, double known)
+__device__ __forceinline__ void publish_displacement(const StepArrays &A, double moved2, double known)
 {
     for (int o = 16; o > 0; o >>= 1) moved2 = fmax(moved2, __shfl_xor_sync(0xffffffffu, moved2, o));
     if ((threadIdx.x & 31) == 0 && moved2 > known)
@@ -316,60 +428,54 @@ __device__ inline void publish_displacement(const StepArrays &A, double moved2, 
 }
 
 /* the hot kernel: forces + Brownian update + skin test, fixed timestep */
+template <int BOX, int PROG>
 __global__ void __launch_bounds__(STEP_BLOCK) k_step_fused(StepArrays A, StepScalars S)
 {
-    __shared__ DParams P;
-    load_params(P, A.params);
+    __shared__ StepShared sh;
+    load_shared<PROG>(sh, A);
     uint32_t const replica = blockIdx.y, chunk = blockIdx.x;
     uint32_t const local = chunk * STEP_BLOCK + threadIdx.x;
-    uint32_t const s = replica * A.n + local;
     bool const live = local < A.n;
+    uint32_t const s = replica * A.n + (live ? local : 0u);
     Select const all = {BD_FF_ALL, -1};
-    double ws[BD_MAX_WALL_FF][WALL_STATS];
     uint32_t inter = 0;
     double const known = __longlong_as_double((long long) A.ctl->max_disp2_bits);
+    bead4 const me = load_bead(A.pos + s);
+    d3 const F = block_forces<BOX, PROG>(A, sh, all, live, s, replica, chunk, me, inter);
     double moved2 = 0.0;
-    if (live) {
-        bead4 const me = load_bead(A.pos + s);
-        d3 const F = bead_force(A, P, all, s, replica, me, ws, inter);
-        moved2 = integrate_bead(A, P, S, s, replica, me, F, S.dt, S.dt_prev);
-    } else {
-        for (int f = 0; f < BD_MAX_WALL_FF; f++) ws[f][0] = ws[f][1] = ws[f][2] = ws[f][3] = 0.0;
-    }
+    if (live) moved2 = integrate_bead<BOX>(A, sh.P, S, s, replica, me, F, S.dt, S.dt_prev);
     publish_displacement(A, moved2, known);
-    reduce_wall_stats(A, P, all, replica, chunk, ws);
     for (int o = 16; o > 0; o >>= 1) inter += __shfl_xor_sync(0xffffffffu, inter, o);
-    __shared__ uint32_t inter_s[STEP_BLOCK / 32];
-    if ((threadIdx.x & 31) == 0) inter_s[threadIdx.x >> 5] = inter;
+    if ((threadIdx.x & 31) == 0) sh.inter[threadIdx.x >> 5] = inter;
     __syncthreads();
     if (threadIdx.x == 0) {
         uint32_t t = 0;
-        for (int w = 0; w < STEP_BLOCK / 32; w++) t += inter_s[w];
+        for (int w = 0; w < STEP_BLOCK / 32; w++) t += sh.inter[w];
         A.inter_partial[(size_t) replica * A.chunks + chunk] += t;
     }
 }
 
 /* forces only (compute_forces, and the first pass of an adaptive-timestep step) */
+template <int BOX, int PROG>
 __global__ void __launch_bounds__(STEP_BLOCK) k_force(StepArrays A, StepScalars S, Select sel)
 {
-    __shared__ DParams P;
-    load_params(P, A.params);
+    __shared__ StepShared sh;
+    load_shared<PROG>(sh, A);
     uint32_t const replica = blockIdx.y, chunk = blockIdx.x;
     uint32_t const local = chunk * STEP_BLOCK + threadIdx.x;
-    uint32_t const s = replica * A.n + local;
     bool const live = local < A.n;
-    double ws[BD_MAX_WALL_FF][WALL_STATS];
+    uint32_t const s = replica * A.n + (live ? local : 0u);
     uint32_t inter = 0;
     double dt = S.dt;
+    bead4 const me = load_bead(A.pos + s);
+    d3 const F = block_forces<BOX, PROG>(A, sh, sel, live, s, replica, chunk, me, inter);
     if (live) {
-        bead4 const me = load_bead(A.pos + s);
-        d3 const F = bead_force(A, P, sel, s, replica, me, ws, inter);
         A.force[3 * (size_t) s] = F.x;
         A.force[3 * (size_t) s + 1] = F.y;
         A.force[3 * (size_t) s + 2] = F.z;
         if (S.adaptive) {
             // brownian_timestepper.hpp:72-91,109-136
-            double const mu = P.mobility[w_type(me.w)];
+            double const mu = sh.P.mobility[w_type(me.w)];
             double const f2 = F.x * F.x + F.y * F.y + F.z * F.z;
             if (mu != 0.0 || f2 != 0.0) {
                 double const a = mu * mu * f2, b = 2.55 * mu * S.kT, c = S.spacestep * S.spacestep;
@@ -377,10 +483,7 @@ __global__ void __launch_bounds__(STEP_BLOCK) k_force(StepArrays A, StepScalars 
             }
             dt = fmin(dt, S.dt);
         }
-    } else {
-        for (int f = 0; f < BD_MAX_WALL_FF; f++) ws[f][0] = ws[f][1] = ws[f][2] = ws[f][3] = 0.0;
     }
-    reduce_wall_stats(A, P, sel, replica, chunk, ws);
     if (S.adaptive) {
         for (int o = 16; o > 0; o >>= 1) dt = fmin(dt, __shfl_xor_sync(0xffffffffu, dt, o));
         if ((threadIdx.x & 31) == 0)
@@ -389,6 +492,7 @@ __global__ void __launch_bounds__(STEP_BLOCK) k_force(StepArrays A, StepScalars 
 }
 
 /* second pass of an adaptive step: update from the stored forces */
+template <int BOX>
 __global__ void __launch_bounds__(STEP_BLOCK) k_integrate(StepArrays A, StepScalars S)
 {
     __shared__ DParams P;
@@ -402,7 +506,7 @@ __global__ void __launch_bounds__(STEP_BLOCK) k_integrate(StepArrays A, StepScal
         bead4 const me = load_bead(A.pos + s);
         d3 const F = {A.force[3 * (size_t) s], A.force[3 * (size_t) s + 1], A.force[3 * (size_t) s + 2]};
         double const dt = __longlong_as_double((long long) A.dt_bits[replica]);
-        moved2 = integrate_bead(A, P, S, s, replica, me, F, dt, A.dt_prev[replica]);
+        moved2 = integrate_bead<BOX>(A, P, S, s, replica, me, F, dt, A.dt_prev[replica]);
     }
     publish_displacement(A, moved2, known);
 }

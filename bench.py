@@ -1,0 +1,334 @@
+#!/usr/bin/env python
+"""Benchmark of the Brownian-dynamics hot path (force evaluation + BAOAB-limit update).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]            the B200 engine
+    python bench.py --impl reference [...]                          the reference CPU code (oracle/_ref)
+    torchrun --nproc-per-node N ... bench.py --gpus N ...           one rank per GPU (weak scaling)
+
+Workload (BASELINE.json configs[3], the one north_star's roofline target is quoted on): the
+5-sim-genome 100kb interphase model -- 62 000 chromatin beads in 46 chains + 600 nucleolar
+side-beads, A/B/u classes, mixed softcore<2,3>+softcore<8,3> non-bonded pairs, three bonded
+forcefields, inward + outward ellipsoid walls -- as an ensemble of R independent replicas per GPU in
+one launch (a single 2.5 MB system sits in L2 and is launch-bound).  A "step"
+is one BD step of every replica.  Inputs are synthetic (scenarios.py, fixed seeds).
+
+One JSON line on stdout (rank 0).  `value` is device-resident throughput; `e2e` goes through the
+C ABI with pinned HOST buffers every step (upload all positions, one step, download all positions).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "2022a-genome-dynamics_b200"))
+
+import numpy as np  # noqa: E402
+
+ALGO_BYTES_PER_BEAD_STEP = 64  # fp64: 32 B record read + 32 B record written
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--replicas", type=int, default=64, help="replicas per GPU")
+    ap.add_argument("--beads", type=int, default=62000, help="chromatin beads per replica")
+    ap.add_argument("--relax", type=int, default=400, help="untimed relaxation steps before warm-up")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def scenario(args, distinct, seed):
+    import scenarios as sc
+
+    return sc.genome_100kb(total=args.beads, n_nor=300, seed=seed, replicas=distinct)
+
+
+def workload_name(args, scen):
+    return f"5-sim-genome 100kb interphase, {scen.n} beads x {args.replicas} replicas per GPU"
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons DURING the timed region (B200_PROFILING.md)."""
+
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "50",
+                 "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.12)
+        self.proc.terminate()
+        out, _ = self.proc.communicate(timeout=10)
+        sm, smax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                smax.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---- reference arm -------------------------------------------------------------------------------
+
+def cpu_backend():
+    import bdb200 as bd
+
+    if bd.have_reference():
+        return bd.load_reference(), "reference"
+    subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "liboracle.so"], check=True)
+    return bd.load_oracle(), "port"
+
+
+def cpu_time_steps(backend, scen, start_positions, steps, threads, warm):
+    """`threads` independent replicas, each advanced `steps` BD steps by the single-threaded
+    reference code; returns wall seconds (ctypes releases the GIL, so replicas run in parallel)."""
+    import bdb200 as bd
+
+    systems = []
+    for t in range(threads):
+        s = bd.System(backend, scen.n)
+        scen.apply(s, replicas=[0])
+        s.set_positions(start_positions[t % len(start_positions)])
+        systems.append(s)
+
+    def run(s, k, first):
+        if k > 0:
+            s.step(k, scen.timestep, scen.temperature, seed=1, first_step=first)
+
+    def fan(k, first):
+        th = [threading.Thread(target=run, args=(s, k, first)) for s in systems]
+        t0 = time.perf_counter()
+        for x in th:
+            x.start()
+        for x in th:
+            x.join()
+        return time.perf_counter() - t0
+
+    fan(warm, 1)
+    dt = fan(steps, warm + 1)
+    for s in systems:
+        s.close()
+    return dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    backend, kind = cpu_backend()
+    scen = scenario(args, 1, 4)
+    threads = os.cpu_count() or 1
+    K, W = max(args.steps, 1), max(args.warmup, 0)
+    # size the per-step sample from a short probe so that the whole run stays within ~2 minutes
+    probe = cpu_time_steps(backend, scen, scen.positions, 3, threads, 1) / 3
+    inner = max(1, int(100.0 / max(probe, 1e-6) / (K + W)))
+    inner = min(inner, 50)
+    wall = cpu_time_steps(backend, scen, scen.positions, K * inner, threads, W * inner)
+    units = threads * scen.n * inner * K
+    value = units / wall
+    line = {
+        "impl": "reference", "metric": "bead_steps_per_s", "value": value, "unit": "bead-steps/s",
+        "n_gpus": args.gpus, "steps": K, "warmup": W, "ms_per_step": 1e3 * wall / K,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(args, scen),
+                   "sample": f"{threads} replicas (one per host thread), {inner} BD steps of each per bench step"},
+        "cpu_baseline": {"value": value, "unit": "bead-steps/s", "cores": threads, "kind": kind,
+                         "sample": f"{threads} independent replicas x {inner * K} BD steps, micromd single-threaded per replica"},
+        "e2e": {"value": value, "unit": "bead-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---- B200 arm ------------------------------------------------------------------------------------
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    import bdb200 as bd
+
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the engine has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    eng = bd.load_engine()
+    R = args.replicas
+    distinct = min(R, 4)
+    scen = scenario(args, distinct, 4 + rank)  # every rank simulates its own replicas (weak scaling)
+    n, ntot = scen.n, scen.n * R
+    sysm = bd.System(eng, n, R, device=local)
+    scen.apply(sysm, replicas=[])
+    stream = torch.cuda.Stream()
+    sysm.set_stream(stream.cuda_stream)
+    host = torch.empty((R, n, 3), dtype=torch.float64).pin_memory()
+    host.numpy()[:] = scen.positions[np.arange(R) % distinct]
+    sysm.set_all_positions(host.data_ptr())
+    dt, kT = scen.timestep, scen.temperature
+
+    step_no = [1]
+
+    def advance(k):
+        sysm.step(k, dt, kT, seed=1234 + rank, first_step=step_no[0])
+        step_no[0] += k
+
+    advance(args.relax)
+    advance(max(args.warmup, 3))
+    sysm.sync()
+    c0 = sysm.get_counters()
+    l0 = sysm.get_launch_count()
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    with torch.cuda.stream(stream):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        advance(args.steps)
+        e1.record(stream)
+    barrier()
+    clocks = sampler.stop()
+    ms = e0.elapsed_time(e1)
+    launches = sysm.get_launch_count() - l0
+    c1 = sysm.get_counters()
+    inter = c1.pair_interactions - c0.pair_interactions
+    rebuilds = c1.list_rebuilds - c0.list_rebuilds
+
+    # the dominant kernel alone, CUDA events around every launch
+    sysm.set_option("time_kernel", 1)
+    advance(min(args.steps, 50))
+    kernel_ms = sysm.get_option("kernel_ms_avg")
+    sysm.set_option("time_kernel", 0)
+
+    # end to end through the C ABI with pinned host buffers, every step
+    e2e = None
+    if not args.no_e2e:
+        ke = max(3, min(args.steps, 20))
+        sysm.get_all_positions(host.data_ptr())
+        barrier()
+        with torch.cuda.stream(stream):
+            f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            f0.record(stream)
+            for _ in range(ke):
+                sysm.set_all_positions(host.data_ptr())
+                advance(1)
+                sysm.get_all_positions(host.data_ptr())
+            f1.record(stream)
+        barrier()
+        e2e_ms = f0.elapsed_time(f1)
+        e2e = (ke, e2e_ms)
+
+    t = torch.tensor([ms, e2e[1] if e2e else 0.0, float(inter), kernel_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        tmax = t.clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone()
+        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        ms, e2e_ms_max, kernel_ms = tmax[0].item(), tmax[1].item(), tmax[3].item()
+        inter = tsum[2].item()
+    else:
+        e2e_ms_max = t[1].item()
+
+    if rank == 0:
+        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(peaks_path):
+            peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)"
+        else:
+            peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+        if os.path.exists(tp):
+            traffic = json.load(open(tp)).get("k_step_fused_dram_bytes_per_launch")
+        achieved = ALGO_BYTES_PER_BEAD_STEP * ntot / (kernel_ms * 1e-3) / 1e9 if kernel_ms > 0 else 0.0
+        value = world * ntot * args.steps / (ms * 1e-3)
+        line = {
+            "metric": "bead_steps_per_s", "value": value, "unit": "bead-steps/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": workload_name(args, scen), "beads_per_replica": n, "replicas_per_gpu": R,
+                       "timestep": dt, "temperature": kT, "noise": "philox4x32-10",
+                       "l2": "working set %.2f GB per GPU > 126 MB L2 (no flush needed)" % (ntot * 32 * 3 / 1e9 + ntot * 4 * 8 / 1e9),
+                       "relax_steps": args.relax, "list_rebuilds_in_timed_region": rebuilds,
+                       "parallelism": f"replica shards, {world} GPU(s), no data-path collective"},
+            "pair_interactions_per_s": inter / (ms * 1e-3),
+            "pair_interactions_per_step": inter / args.steps,
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": traffic, "kernel": "k_step_fused",
+                         "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": ALGO_BYTES_PER_BEAD_STEP * ntot,
+                         "peak_source": peak_src},
+        }
+        if e2e:
+            line["e2e"] = {"value": world * ntot * e2e[0] / (e2e_ms_max * 1e-3), "unit": "bead-steps/s",
+                           "h2d_bytes_per_step": ntot * 24, "d2h_bytes_per_step": ntot * 24,
+                           "steps": e2e[0], "ms_per_step": e2e_ms_max / e2e[0],
+                           "path": "bd_set_all_positions -> bd_step(1) -> bd_get_all_positions, pinned host buffers"}
+        if world == 1 and not args.no_cpu_baseline:
+            backend, kind = cpu_backend()
+            start = host.numpy()[:1].copy()  # GPU-relaxed configuration: the same work per step
+            probe = cpu_time_steps(backend, scen, start, 3, 1, 1) / 3
+            s = max(5, int(args.cpu_seconds / max(probe, 1e-6)))
+            wall = cpu_time_steps(backend, scen, start, s, 1, 2)
+            line["cpu_baseline"] = {"value": n * s / wall, "unit": "bead-steps/s", "cores": 1, "kind": kind,
+                                    "sample": f"1 replica ({n} beads) x {s} BD steps from the GPU-relaxed state, single thread"}
+        print(json.dumps(line), flush=True)
+    sysm.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

