@@ -477,6 +477,10 @@ _cache = {}
 def load_engine() -> Backend:
     """The product library.  Fails loudly when it has not been built: no CPU fallback exists."""
     if "bd_" not in _cache:
+        lib = os.environ.get("BD_B200_LIB", ENGINE_LIB)  # developer override: A/B builds of the engine
+        if lib != ENGINE_LIB:
+            _cache["bd_"] = Backend(lib, "bd_")
+            return _cache["bd_"]
         if not os.path.exists(ENGINE_LIB):
             raise BackendError(
                 f"{ENGINE_LIB} is missing: build it with `python __graft_entry__.py build` "

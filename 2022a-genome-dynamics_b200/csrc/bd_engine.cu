@@ -396,7 +396,7 @@ extern "C" int bd_create(int64_t n_beads, int32_t n_replicas, int32_t device, bd
         && h->wall_out.alloc((size_t) h->replicas * BD_MAX_WALL_FF * WALL_STATS) == cudaSuccess
         && h->energy_partial.alloc((size_t) h->replicas * h->chunks) == cudaSuccess
         && h->energy_out.alloc(h->replicas) == cudaSuccess
-        && h->inter_partial.alloc((size_t) h->replicas * h->chunks) == cudaSuccess
+        && h->inter_partial.alloc((size_t) h->replicas * h->chunks * (STEP_BLOCK / 32)) == cudaSuccess
         && h->dt_bits.alloc(h->replicas) == cudaSuccess && h->dt_prev.alloc(h->replicas) == cudaSuccess
         && h->dt_last.alloc(h->replicas) == cudaSuccess && h->pair_count.alloc(1) == cudaSuccess
         && h->d_type.alloc(h->n) == cudaSuccess && h->d_pair_mask.alloc(h->n) == cudaSuccess
@@ -981,6 +981,7 @@ extern "C" int bd_step(bd_engine *h, const bd_step_config *cfg)
         S.dt = cfg->timestep;
         S.dt_prev = h->last_dt;
         S.kT_prev = h->last_kT;
+        S.want_stats = k == cfg->steps - 1;
         if (replay) S.replay = h->replay.p + ((size_t) k - staged_from) * per_step;
         if (!adaptive) {
             cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -1135,7 +1136,7 @@ extern "C" int bd_get_counters(bd_engine *h, bd_counters *out)
     for (unsigned long long v : part) inter += v;
     out->steps_done = h->steps_done;
     out->list_rebuilds = (int64_t) c.rebuilds;
-    out->pair_interactions = (int64_t) inter;
+    out->pair_interactions = (int64_t) (inter / 2);  // every pair is counted from both of its beads
     out->listed_pairs = (int64_t) (c.listed_entries / 2);
     out->overflow_beads = c.overflow;
     return 0;

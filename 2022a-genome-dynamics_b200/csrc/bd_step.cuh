@@ -43,7 +43,7 @@ struct StepArrays {
     const DParams *params;
     DControl *ctl;
     double *wall_partial;         // [replicas][chunks][BD_MAX_WALL_FF][4]
-    unsigned long long *inter_partial;  // [replicas*chunks] running count of interacting pairs
+    unsigned long long *inter_partial;  // [replicas*chunks*warps] interacting (bead, neighbour) entries so far
     double *force;                // [Ntot][3] by slot (two-pass path and compute_forces)
     double *wprev;                // [Ntot][3] by original global index (replay mode)
     unsigned long long *dt_bits;  // [replicas] adaptive: min timestep of the current step
@@ -62,6 +62,7 @@ struct StepScalars {
     long long step;          // 1-based index of this step within the run
     const double *replay;    // device, [replicas][n][3] standard normals of this step, or null
     int adaptive;
+    int want_stats;          // reduce the wall reaction statistics in this step
 };
 
 template <typename T>
@@ -146,20 +147,35 @@ __device__ __forceinline__ void pair_forces(const StepArrays &A, const DParams &
     int const T = P.ntypes;
     uint32_t const m = A.nnbr[s];
     const uint32_t *col = A.nbr + s;
+    (void) oi;
     if (PROG != PROG_GENERIC) {
         double const dcut2 = P.pair[A.fast_ff].dcut2;
         const PairRow *mine = rows + ti * T;
-        for (uint32_t k = 0; k < m; k++) {
-            uint32_t const j = col[(size_t) k * A.ntot];
-            bead4 const o = load_bead(A.pos + j);
+        size_t const stride = A.ntot;
+        auto interact = [&](const bead4 &o) {
             d3 const r = displacement_t<BOX>(P, me.x, me.y, me.z, o.x, o.y, o.z);
             double const r2 = sqnorm_exact(r.x, r.y, r.z);
             if (r2 <= dcut2) {
                 double const sc = compiled_pair_scalar<PROG>(mine[w_type(o.w)], r2);
                 F.x += sc * r.x; F.y += sc * r.y; F.z += sc * r.z;
-                interactions += oi < w_orig(o.w) ? 1u : 0u;
+                interactions += 1u;  // every pair is seen from both ends: halved when read out
             }
+        };
+        // four gathers in flight per thread: the row indices are independent loads, and so are
+        // the records they point at
+        uint32_t k = 0;
+        for (; k + 4 <= m; k += 4, col += 4 * stride) {
+            uint32_t const j0 = col[0], j1 = col[stride], j2 = col[2 * stride], j3 = col[3 * stride];
+            bead4 const o0 = load_bead(A.pos + j0);
+            bead4 const o1 = load_bead(A.pos + j1);
+            bead4 const o2 = load_bead(A.pos + j2);
+            bead4 const o3 = load_bead(A.pos + j3);
+            interact(o0);
+            interact(o1);
+            interact(o2);
+            interact(o3);
         }
+        for (; k < m; k++, col += stride) interact(load_bead(A.pos + col[0]));
         return;
     }
     bool any_pair = false;
@@ -182,7 +198,7 @@ __device__ __forceinline__ void pair_forces(const StepArrays &A, const DParams &
             F.x += sc * r.x; F.y += sc * r.y; F.z += sc * r.z;
             hit = true;
         }
-        interactions += (hit && oi < oj) ? 1u : 0u;
+        interactions += hit ? 1u : 0u;
     }
 }
 
@@ -315,7 +331,6 @@ struct StepShared {
     DParams P;
     PairRow rows[BD_MAX_TYPES * BD_MAX_TYPES];
     double wall_red[STEP_BLOCK / 32][BD_MAX_WALL_FF][WALL_STATS];
-    uint32_t inter[STEP_BLOCK / 32];
 };
 
 template <int PROG>
@@ -335,8 +350,8 @@ __device__ __forceinline__ void load_shared(StepShared &sh, const StepArrays &A)
  * statistics across the block), `live` masks the threads past the end of the replica */
 template <int BOX, int PROG>
 __device__ __forceinline__ d3 block_forces(const StepArrays &A, StepShared &sh, Select sel, bool live,
-                                           uint32_t s, uint32_t replica, uint32_t chunk, const bead4 &me,
-                                           uint32_t &interactions)
+                                           bool want_stats, uint32_t s, uint32_t replica, uint32_t chunk,
+                                           const bead4 &me, uint32_t &interactions)
 {
     const DParams &P = sh.P;
     d3 F = {0.0, 0.0, 0.0};
@@ -352,13 +367,14 @@ __device__ __forceinline__ d3 block_forces(const StepArrays &A, StepShared &sh, 
         any_wall = true;
         double st[WALL_STATS] = {0.0, 0.0, 0.0, 0.0};
         if (live) wall_force(A, wf, me, F, st);
+        if (!want_stats) continue;  // block-uniform: only the last step of a call is observable
 #pragma unroll
         for (int c = 0; c < WALL_STATS; c++) {
             for (int o = 16; o > 0; o >>= 1) st[c] += __shfl_xor_sync(0xffffffffu, st[c], o);
             if ((threadIdx.x & 31) == 0) sh.wall_red[threadIdx.x >> 5][f][c] = st[c];
         }
     }
-    if (any_wall) {
+    if (any_wall && want_stats) {
         __syncthreads();
         if (threadIdx.x < BD_MAX_WALL_FF * WALL_STATS) {
             int const f = threadIdx.x / WALL_STATS, c = threadIdx.x % WALL_STATS;
@@ -429,7 +445,7 @@ __device__ __forceinline__ void publish_displacement(const StepArrays &A, double
 
 /* the hot kernel: forces + Brownian update + skin test, fixed timestep */
 template <int BOX, int PROG>
-__global__ void __launch_bounds__(STEP_BLOCK) k_step_fused(StepArrays A, StepScalars S)
+__global__ void __launch_bounds__(STEP_BLOCK, 8) k_step_fused(StepArrays A, StepScalars S)
 {
     __shared__ StepShared sh;
     load_shared<PROG>(sh, A);
@@ -441,18 +457,13 @@ __global__ void __launch_bounds__(STEP_BLOCK) k_step_fused(StepArrays A, StepSca
     uint32_t inter = 0;
     double const known = __longlong_as_double((long long) A.ctl->max_disp2_bits);
     bead4 const me = load_bead(A.pos + s);
-    d3 const F = block_forces<BOX, PROG>(A, sh, all, live, s, replica, chunk, me, inter);
+    d3 const F = block_forces<BOX, PROG>(A, sh, all, live, S.want_stats != 0, s, replica, chunk, me, inter);
     double moved2 = 0.0;
     if (live) moved2 = integrate_bead<BOX>(A, sh.P, S, s, replica, me, F, S.dt, S.dt_prev);
     publish_displacement(A, moved2, known);
     for (int o = 16; o > 0; o >>= 1) inter += __shfl_xor_sync(0xffffffffu, inter, o);
-    if ((threadIdx.x & 31) == 0) sh.inter[threadIdx.x >> 5] = inter;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t t = 0;
-        for (int w = 0; w < STEP_BLOCK / 32; w++) t += sh.inter[w];
-        A.inter_partial[(size_t) replica * A.chunks + chunk] += t;
-    }
+    if ((threadIdx.x & 31) == 0)  // one private counter per warp: no barrier, no atomics
+        A.inter_partial[((size_t) replica * A.chunks + chunk) * (STEP_BLOCK / 32) + (threadIdx.x >> 5)] += inter;
 }
 
 /* forces only (compute_forces, and the first pass of an adaptive-timestep step) */
@@ -468,7 +479,7 @@ __global__ void __launch_bounds__(STEP_BLOCK) k_force(StepArrays A, StepScalars 
     uint32_t inter = 0;
     double dt = S.dt;
     bead4 const me = load_bead(A.pos + s);
-    d3 const F = block_forces<BOX, PROG>(A, sh, sel, live, s, replica, chunk, me, inter);
+    d3 const F = block_forces<BOX, PROG>(A, sh, sel, live, true, s, replica, chunk, me, inter);
     if (live) {
         A.force[3 * (size_t) s] = F.x;
         A.force[3 * (size_t) s + 1] = F.y;

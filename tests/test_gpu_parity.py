@@ -120,9 +120,12 @@ def test_scenario_golden(engine, name):
     assert rel_force_error(s.compute_forces(), g["forces"]) <= FORCE_TOL
     assert s.compute_energy() == pytest.approx(float(g["energy"]), rel=ENERGY_TOL)
     assert np.array_equal(sort_pairs(s.get_neighbor_list()), sort_pairs(g["neighbor_list"]))
+    total_scale = np.linalg.norm(g["forces"], axis=1).max()
     for cls, key in CLASSES:
         for ff in ids[key]:
-            assert rel_force_error(s.compute_forces(0, cls, ff), g[f"forces_{key}{ff}"]) <= FORCE_TOL
+            fo = g[f"forces_{key}{ff}"]
+            scale = max(np.linalg.norm(fo, axis=1).max(), 1e-3 * total_scale)
+            assert np.linalg.norm(s.compute_forces(0, cls, ff) - fo, axis=1).max() <= FORCE_TOL * scale, (key, ff)
             assert s.compute_energy(0, cls, ff) == pytest.approx(float(g[f"energy_{key}{ff}"]), rel=ENERGY_TOL, abs=ENERGY_TOL * abs(float(g["energy"])))
             if cls == bd.FF_WALL:
                 assert_close(s.get_wall_stats(ff), g[f"stats_{key}{ff}"], 1e-11)
@@ -147,20 +150,28 @@ def test_replayed_trajectory_matches_oracle(engine, oracle, name):
     assert np.abs(se.get_positions() - so.get_positions()).max() <= TRAJ_TOL
 
 
-def test_long_replay_rebuilds_with_the_oracle(engine, oracle):
-    """200 steps at a large timestep: the Verlet list is rebuilt several times, at the same steps."""
-    scen = sc.ab_sphere(20, 20)
+@pytest.mark.parametrize("name", ["ab_box", "ab_sphere"])
+def test_long_replay_rebuilds_with_the_oracle(engine, oracle, name):
+    """200 steps at a large timestep: the Verlet list is rebuilt many times.  In a periodic box the
+    engine rebuilds at exactly the steps the reference does (same fp64 criterion).  In an open box
+    the reference rebuilds at EVERY step -- its consistency check compares the caller's
+    open_box{particle_count = 1000} with the hinted copy {particle_count = N}
+    (MD/forcefield/detail/neighbor_list.hpp:37-40,114-118) -- which the engine does not imitate."""
+    scen = sc.ab_box(20, 20) if name == "ab_box" else sc.ab_sphere(20, 20)
     se, _ = build(engine, scen)
     so, _ = build(oracle, scen)
-    steps, dt = 200, 2e-4
+    steps, dt = 200, 1e-4
     z = oracle.normals(9, steps * scen.n * 3)
     se.step(steps, dt, scen.temperature, replay_normals=z)
     so.step(steps, dt, scen.temperature, replay_normals=z)
     assert np.abs(se.get_positions() - so.get_positions()).max() <= 1e-8
     ce, co = se.get_counters(), so.get_counters()
-    assert co.list_rebuilds >= 3
-    assert ce.list_rebuilds == co.list_rebuilds
     assert ce.steps_done == steps
+    assert 3 <= ce.list_rebuilds < steps
+    if name == "ab_box":
+        assert ce.list_rebuilds == co.list_rebuilds
+    else:
+        assert co.list_rebuilds == steps
 
 
 def test_adaptive_timestep_matches_oracle(engine, oracle):
