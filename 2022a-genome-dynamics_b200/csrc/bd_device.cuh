@@ -26,6 +26,10 @@ namespace bd {
 
 // ---- records -----------------------------------------------------------------------------------
 
+/* Slot Ntot of every per-bead array is a sentinel: NaN coordinates that fail every distance test.
+ * Verlet rows are padded with it to a multiple of ROW_PAD entries. */
+constexpr uint32_t ROW_PAD = 4;
+
 struct __align__(32) bead4 {
     double x, y, z;
     uint64_t w;  // bits 0..31 original index within the replica, 32..39 class,
@@ -56,7 +60,12 @@ static_assert(sizeof(DTerm) == 64, "DTerm is one 64-byte record");
 struct DPair { int32_t enabled, nterms, term_off, has_targets; double dcut, dcut2; };
 struct DBond { int32_t enabled, nterms, term_off, pad; };
 struct DBend { int32_t enabled, pad[3]; };
-struct DWall { int32_t enabled, nterms, term_off, shape, direction, pad[3]; double center[3]; double semi[3]; };
+struct DWall {
+    int32_t enabled, nterms, term_off, shape, direction, pad[3];
+    double center[3];
+    double semi[3];
+    double quad[3];  // 1 / (semi * semi), rounded exactly as ellipsoid_surface_forcefield.hpp:72-76 does
+};
 struct DPoint { int32_t enabled, nterms, term_off, has_targets; double source[3]; double pad; };
 
 /* everything the host may change between steps; uploaded as one block when dirty */
@@ -83,6 +92,10 @@ struct DGrid {
     int32_t totalbits;
     int32_t pad;
     double radius;  // list radius the rows were built with
+    // single-precision shadow coordinates of the pre-filter (bd_step.cuh): |r_shadow - r| <= shadow_eps / 4
+    double shadow_eps;
+    float shadow_scale[3];  // periodic: period * 2^-32 (fixed-point fraction -> length)
+    float pad2;
 };
 
 /* device-resident control block: kernels decide on rebuilds without returning to the host */
@@ -287,6 +300,56 @@ __device__ inline void cell_coords(const DParams &P, const DGrid &G, double x, d
         ci = ci >= G.n[d] ? G.n[d] - 1 : ci;
         c[d] = ci;
     }
+}
+
+// ---- single-precision shadow coordinates --------------------------------------------------------
+//
+// The step kernel walks ~26 listed neighbours per bead of which ~8 interact.  The walk tests a
+// 16-byte single-precision shadow of each neighbour against a widened cutoff; only survivors are
+// loaded as 32-byte fp64 records and evaluated exactly, so the fp64 result does not depend on the
+// shadow.  Open box: float offsets from the grid origin.  Periodic box: 32-bit fixed-point
+// fractions of the period, whose wrapping difference IS the minimum image.
+
+template <int BOX>
+__device__ __forceinline__ float4 make_shadow(const DParams &P, const DGrid &G, double x, double y, double z)
+{
+    float4 q;
+    if (BOX == BD_BOX_PERIODIC) {
+        double const v[3] = {x, y, z};
+        uint32_t u[3];
+#pragma unroll
+        for (int d = 0; d < 3; d++) {
+            double t = v[d] * P.inv_period[d];
+            t -= floor(t);
+            u[d] = (uint32_t) (unsigned long long) (t * 4294967296.0);
+        }
+        q.x = __uint_as_float(u[0]);
+        q.y = __uint_as_float(u[1]);
+        q.z = __uint_as_float(u[2]);
+    } else {
+        q.x = (float) (x - G.origin[0]);
+        q.y = (float) (y - G.origin[1]);
+        q.z = (float) (z - G.origin[2]);
+    }
+    q.w = 0.0f;
+    return q;
+}
+
+/* squared shadow distance between two beads */
+template <int BOX>
+__device__ __forceinline__ float shadow_dist2(const float4 &a, const float4 &b, const float scale[3])
+{
+    float dx, dy, dz;
+    if (BOX == BD_BOX_PERIODIC) {
+        dx = (float) (int32_t) (__float_as_uint(a.x) - __float_as_uint(b.x)) * scale[0];
+        dy = (float) (int32_t) (__float_as_uint(a.y) - __float_as_uint(b.y)) * scale[1];
+        dz = (float) (int32_t) (__float_as_uint(a.z) - __float_as_uint(b.z)) * scale[2];
+    } else {
+        dx = a.x - b.x;
+        dy = a.y - b.y;
+        dz = a.z - b.z;
+    }
+    return fmaf(dx, dx, fmaf(dy, dy, dz * dz));
 }
 
 /* order-preserving map double -> u64 (for atomicMin/Max bounding boxes) */

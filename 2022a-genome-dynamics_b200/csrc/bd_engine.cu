@@ -21,6 +21,8 @@
 
 using namespace bd;
 
+static_assert(BAL_TILE == STEP_BLOCK, "k_balance ranks the beads of one step-kernel block");
+
 // ---- errors --------------------------------------------------------------------------------------
 
 static thread_local std::string g_error;
@@ -78,8 +80,16 @@ struct bd_engine {
 
     // per-bead device state
     DevBuf<bead4> pos[2], bpos;
+    DevBuf<float4> shadow[2];  // single-precision shadow of pos[] (slot Ntot of pos/shadow is the NaN sentinel)
     int cur = 0;
-    DevBuf<uint32_t> slot_of, cellkey, rank, stage, cell_count, cell_start, block_sum, nbr, nnbr;
+    DevBuf<uint32_t> slot_of, cellkey, rank, stage, cell_count, cell_start, block_sum, nnbr, plen;
+    DevBuf<uint4> nbr4;       // Verlet rows by thread position, ROW_PAD indices per group
+    DevBuf<uint2> bondrow;    // bonded partners by thread position, resolved to slots at every rebuild
+    DevBuf<BondRow> d_bond_rows;
+    uint32_t npad = 0, pstride = 0, bond_deg = 0;
+    bool bonds_compiled = false;
+    int nbond_rows = 0;
+    uint8_t bond_slot[BD_MAX_BOND_FF] = {};
     uint32_t cell_cap = 0, max_bits = 0, cap = 32;
     DevBuf<DControl> ctl;
     DevBuf<DParams> d_params;
@@ -90,7 +100,7 @@ struct bd_engine {
     bool specialize = true;
     DevBuf<double> force, wprev, xyz_stage, wall_partial, wall_out, energy_partial, energy_out, dt_prev, dt_last;
     DevBuf<unsigned long long> inter_partial, dt_bits, pair_count;
-    DevBuf<uint8_t> d_type, d_pair_mask, d_point_mask;
+    DevBuf<uint8_t> d_type, d_pair_mask, d_point_mask, order;
     DevBuf<double> replay, xyz_all;
 
     // topology (device CSR by original index)
@@ -233,10 +243,52 @@ static int compile_pair_program(bd_engine *h, std::vector<PairRow> &rows)
     return 0;
 }
 
+/* Bond tables whose cells are one harmonic / spring / semispring term (every reference driver) are
+ * compiled into BondRow blocks that the step kernel keeps in shared memory; anything else keeps the
+ * interpreter. */
+static void compile_bond_rows(bd_engine *h, std::vector<BondRow> &rows)
+{
+    h->bonds_compiled = false;
+    h->nbond_rows = 0;
+    rows.clear();
+    if (!h->specialize) return;
+    int const T2 = h->hp.ntypes * h->hp.ntypes;
+    int used = 0;
+    for (int f = 0; f < BD_MAX_BOND_FF; f++) {
+        if (!h->bond[f].used) continue;
+        h->bond_slot[f] = (uint8_t) used++;
+        const DTerm *tab = h->hterms.data() + h->bond[f].term_off;
+        int const nterms = h->bond[f].nterms;
+        for (int c = 0; c < T2; c++) {
+            BondRow row = {0.0, 0.0, 1.0, BD_TERM_NONE, 0};
+            int live = 0;
+            for (int k = 0; k < nterms; k++) {
+                const DTerm &t = tab[c * nterms + k];
+                if (t.kind == BD_TERM_NONE) continue;
+                if (++live > 1 || t.cutoff2 != 0.0) return;
+                if (t.kind != BD_TERM_HARMONIC && t.kind != BD_TERM_SPRING && t.kind != BD_TERM_SEMISPRING) return;
+                row.k = t.energy;
+                row.b = t.length;
+                row.factor = t.factor;
+                row.kind = t.kind;
+            }
+            rows.push_back(row);
+        }
+    }
+    if (used == 0 || rows.size() > (size_t) BD_MAX_TYPES * BD_MAX_TYPES) return;
+    h->bonds_compiled = true;
+    h->nbond_rows = (int) rows.size();
+}
+
 static int upload_params(bd_engine *h)
 {
     if (!h->params_dirty) return 0;
     refresh_dcut_max(h);
+    std::vector<BondRow> brows;
+    compile_bond_rows(h, brows);
+    if (h->bonds_compiled)
+        CK(cudaMemcpyAsync(h->d_bond_rows.p, brows.data(), brows.size() * sizeof(BondRow), cudaMemcpyHostToDevice,
+                           h->stream));
     std::vector<PairRow> rows;
     compile_pair_program(h, rows);
     if (h->prog != PROG_GENERIC)
@@ -294,7 +346,12 @@ static int upload_topology(bd_engine *h)
             adj[fill[j]++] = make_uint2(i, (uint32_t) f | 0x100u);
         }
     }
+    uint32_t deg = 0;
+    for (uint32_t i = 0; i < n; i++) deg = std::max(deg, start[i + 1] - start[i]);
     CK(cudaStreamSynchronize(h->stream));
+    h->bond_deg = deg;
+    CK(h->bondrow.alloc((size_t) deg * h->pstride));
+    h->list_verified = false;
     CK(h->bond_start.alloc(n + 1));
     CK(h->bond_adj.alloc(adj.size()));
     CK(cudaMemcpy(h->bond_start.p, start.data(), (n + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice));
@@ -327,14 +384,14 @@ static int upload_topology(bd_engine *h)
         CK(cudaMemcpy(h->bend_energy.p, ten.data(), ten.size() * sizeof(double), cudaMemcpyHostToDevice));
         CK(cudaMemcpy(h->bend_ff.p, tff.data(), tff.size(), cudaMemcpyHostToDevice));
     }
-    return 0;
+    return request_rebuild(h);  // the slot-space bond rows are refilled by the rebuild chain
 }
 
 // ---- lifetime ------------------------------------------------------------------------------------
 
 static int alloc_rows(bd_engine *h)
 {
-    CK(h->nbr.alloc((size_t) h->cap * h->ntot));
+    CK(h->nbr4.alloc((size_t) (h->cap / ROW_PAD) * h->pstride));
     return 0;
 }
 
@@ -357,6 +414,8 @@ extern "C" int bd_create(int64_t n_beads, int32_t n_replicas, int32_t device, bd
     h->replicas = (uint32_t) n_replicas;
     h->ntot = h->n * h->replicas;
     h->chunks = blocks_for(h->n, STEP_BLOCK);
+    h->npad = h->chunks * STEP_BLOCK;
+    h->pstride = h->npad * h->replicas;
     if (cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
         delete h;
         return fail("bd_create: cannot create a stream");
@@ -383,7 +442,8 @@ extern "C" int bd_create(int64_t n_beads, int32_t n_replicas, int32_t device, bd
     h->h_point_mask.assign(h->n, 0);
 
     size_t const nt = h->ntot;
-    bool ok = h->pos[0].alloc(nt) == cudaSuccess && h->pos[1].alloc(nt) == cudaSuccess
+    bool ok = h->pos[0].alloc(nt + 1) == cudaSuccess && h->pos[1].alloc(nt + 1) == cudaSuccess
+        && h->shadow[0].alloc(nt + 1) == cudaSuccess && h->shadow[1].alloc(nt + 1) == cudaSuccess
         && h->bpos.alloc(nt) == cudaSuccess && h->slot_of.alloc(nt) == cudaSuccess
         && h->cellkey.alloc(nt) == cudaSuccess && h->rank.alloc(nt) == cudaSuccess
         && h->stage.alloc(nt) == cudaSuccess && h->nnbr.alloc(nt) == cudaSuccess
@@ -401,21 +461,22 @@ extern "C" int bd_create(int64_t n_beads, int32_t n_replicas, int32_t device, bd
         && h->dt_bits.alloc(h->replicas) == cudaSuccess && h->dt_prev.alloc(h->replicas) == cudaSuccess
         && h->dt_last.alloc(h->replicas) == cudaSuccess && h->pair_count.alloc(1) == cudaSuccess
         && h->d_type.alloc(h->n) == cudaSuccess && h->d_pair_mask.alloc(h->n) == cudaSuccess
-        && h->d_point_mask.alloc(h->n) == cudaSuccess && h->nbr.alloc((size_t) h->cap * nt) == cudaSuccess;
+        && h->d_point_mask.alloc(h->n) == cudaSuccess && h->order.alloc(nt) == cudaSuccess && h->plen.alloc(h->pstride) == cudaSuccess
+        && h->d_bond_rows.alloc(BD_MAX_TYPES * BD_MAX_TYPES) == cudaSuccess
+        && h->nbr4.alloc((size_t) (h->cap / ROW_PAD) * h->pstride) == cudaSuccess;
     if (!ok) {
         bd_destroy(h);
         return fail(std::string("bd_create: device allocation failed: ") + cudaGetErrorString(cudaGetLastError()));
     }
     cudaMemsetAsync(h->ctl.p, 0, sizeof(DControl), h->stream);
+    cudaMemsetAsync(h->plen.p, 0, std::max<size_t>(h->pstride, 1) * sizeof(uint32_t), h->stream);
     cudaMemsetAsync(h->wall_partial.p, 0, h->wall_partial.count * sizeof(double), h->stream);
     cudaMemsetAsync(h->inter_partial.p, 0, h->inter_partial.count * sizeof(unsigned long long), h->stream);
     cudaMemsetAsync(h->dt_last.p, 0, h->replicas * sizeof(double), h->stream);
     cudaMemsetAsync(h->dt_prev.p, 0, h->replicas * sizeof(double), h->stream);
-    if (h->ntot) {
-        k_init_identity<<<blocks_for(h->ntot, 256), 256, 0, h->stream>>>(h->slot_of.p, h->pos[0].p, h->pos[1].p,
-                                                                         h->bpos.p, h->n, h->ntot);
-        h->launches++;
-    }
+    k_init_identity<<<blocks_for(h->ntot + 1, 256), 256, 0, h->stream>>>(
+        h->slot_of.p, h->pos[0].p, h->pos[1].p, h->bpos.p, h->shadow[0].p, h->shadow[1].p, h->order.p, h->n, h->ntot);
+    h->launches++;
     if (upload_topology(h) || request_rebuild(h)) {
         bd_destroy(h);
         return 1;
@@ -434,19 +495,23 @@ extern "C" int bd_destroy(bd_engine *h)
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     for (auto *b : {&h->pos[0], &h->pos[1], &h->bpos}) b->release();
+    for (auto *b : {&h->shadow[0], &h->shadow[1]}) b->release();
     for (auto *b : {&h->slot_of, &h->cellkey, &h->rank, &h->stage, &h->cell_count, &h->cell_start,
-                    &h->block_sum, &h->nbr, &h->nnbr, &h->bond_start, &h->bend_start, &h->bend_adj, &h->triples})
+                    &h->block_sum, &h->plen, &h->nnbr, &h->bond_start, &h->bend_start, &h->bend_adj, &h->triples})
         b->release();
     for (auto *b : {&h->force, &h->wprev, &h->xyz_stage, &h->wall_partial, &h->wall_out, &h->energy_partial,
                     &h->energy_out, &h->dt_prev, &h->dt_last, &h->bend_energy, &h->replay, &h->xyz_all})
         b->release();
     for (auto *b : {&h->inter_partial, &h->dt_bits, &h->pair_count}) b->release();
-    for (auto *b : {&h->d_type, &h->d_pair_mask, &h->d_point_mask, &h->bend_ff}) b->release();
+    for (auto *b : {&h->d_type, &h->d_pair_mask, &h->d_point_mask, &h->bend_ff, &h->order}) b->release();
     h->ctl.release();
     h->d_params.release();
     h->d_terms.release();
     h->d_pair_rows.release();
     h->bond_adj.release();
+    h->nbr4.release();
+    h->bondrow.release();
+    h->d_bond_rows.release();
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     delete h;
     return 0;
@@ -673,6 +738,7 @@ extern "C" int bd_add_wall_ff(bd_engine *h, int32_t shape, int32_t direction, in
         for (int d = 0; d < 3; d++) {
             w.center[d] = center[d];
             w.semi[d] = semiaxes[d];
+            w.quad[d] = 1.0 / (semiaxes[d] * semiaxes[d]);
         }
         *ff_out = k;
         return 0;
@@ -689,6 +755,7 @@ extern "C" int bd_update_wall_ff(bd_engine *h, int32_t ff, const bd_term *table,
     for (int d = 0; d < 3; d++) {
         h->hp.wall[ff].center[d] = center[d];
         h->hp.wall[ff].semi[d] = semiaxes[d];
+        h->hp.wall[ff].quad[d] = 1.0 / (semiaxes[d] * semiaxes[d]);
     }
     h->params_dirty = true;
     return 0;
@@ -740,6 +807,7 @@ static NlistArrays nlist_arrays(bd_engine *h)
     A.pos = h->pos[h->cur].p;
     A.pos_out = h->pos[h->cur].p;
     A.bpos = h->bpos.p;
+    A.shadow = h->shadow[h->cur].p;
     A.slot_of = h->slot_of.p;
     A.cellkey = h->cellkey.p;
     A.rank = h->rank.p;
@@ -747,8 +815,16 @@ static NlistArrays nlist_arrays(bd_engine *h)
     A.cell_count = h->cell_count.p;
     A.cell_start = h->cell_start.p;
     A.block_sum = h->block_sum.p;
-    A.nbr = h->nbr.p;
+    A.nbr4 = h->nbr4.p;
+    A.plen = h->plen.p;
     A.nnbr = h->nnbr.p;
+    A.order = h->order.p;
+    A.bondrow = h->bondrow.p;
+    A.bond_start = h->bond_start.p;
+    A.bond_adj = h->bond_adj.p;
+    A.bond_deg = h->bond_deg;
+    A.npad = h->npad;
+    A.pstride = h->pstride;
     A.ctl = h->ctl.p;
     A.params = h->d_params.p;
     A.n = h->n;
@@ -765,10 +841,23 @@ static StepArrays step_arrays(bd_engine *h)
     StepArrays A;
     A.pos = h->pos[h->cur].p;
     A.pos_out = h->pos[h->cur ^ 1].p;
+    A.shadow = h->shadow[h->cur].p;
+    A.shadow_out = h->shadow[h->cur ^ 1].p;
     A.bpos = h->bpos.p;
     A.slot_of = h->slot_of.p;
-    A.nbr = h->nbr.p;
-    A.nnbr = h->nnbr.p;
+    A.nbr4 = h->nbr4.p;
+    A.plen = h->plen.p;
+    A.bondrow = h->bondrow.p;
+    A.bond_deg = h->bond_deg;
+    A.npad = h->npad;
+    A.pstride = h->pstride;
+    A.bond_rows = h->d_bond_rows.p;
+    for (int f = 0; f < BD_MAX_BOND_FF; f++) A.bond_slot[f] = h->bond_slot[f];
+    A.bonds_compiled = h->bonds_compiled;
+    A.nbond_rows = h->nbond_rows;
+    A.any_bend = 0;
+    for (int f = 0; f < BD_MAX_BEND_FF; f++) A.any_bend |= h->bend_used[f];
+    A.order = h->order.p;
     A.bond_start = h->bond_start.p;
     A.bond_adj = h->bond_adj.p;
     A.bend_start = h->bend_start.p;
@@ -798,10 +887,11 @@ static StepArrays step_arrays(bd_engine *h)
 template <int BOX>
 static void launch_step_box(int prog, dim3 grid, cudaStream_t st, const StepArrays &A, const StepScalars &S)
 {
+    size_t const rows_bytes = (size_t) A.ntypes2 * sizeof(PairRow) + (size_t) A.nbond_rows * sizeof(BondRow);
     switch (prog) {
-    case PROG_SC23_SC83: k_step_fused<BOX, PROG_SC23_SC83><<<grid, STEP_BLOCK, 0, st>>>(A, S); break;
-    case PROG_SC23: k_step_fused<BOX, PROG_SC23><<<grid, STEP_BLOCK, 0, st>>>(A, S); break;
-    default: k_step_fused<BOX, PROG_GENERIC><<<grid, STEP_BLOCK, 0, st>>>(A, S); break;
+    case PROG_SC23_SC83: k_step_fused<BOX, PROG_SC23_SC83><<<grid, STEP_BLOCK, rows_bytes, st>>>(A, S); break;
+    case PROG_SC23: k_step_fused<BOX, PROG_SC23><<<grid, STEP_BLOCK, rows_bytes, st>>>(A, S); break;
+    default: k_step_fused<BOX, PROG_GENERIC><<<grid, STEP_BLOCK, rows_bytes, st>>>(A, S); break;
     }
 }
 
@@ -809,10 +899,11 @@ template <int BOX>
 static void launch_force_box(int prog, dim3 grid, cudaStream_t st, const StepArrays &A, const StepScalars &S,
                              Select sel)
 {
+    size_t const rows_bytes = (size_t) A.ntypes2 * sizeof(PairRow) + (size_t) A.nbond_rows * sizeof(BondRow);
     switch (prog) {
-    case PROG_SC23_SC83: k_force<BOX, PROG_SC23_SC83><<<grid, STEP_BLOCK, 0, st>>>(A, S, sel); break;
-    case PROG_SC23: k_force<BOX, PROG_SC23><<<grid, STEP_BLOCK, 0, st>>>(A, S, sel); break;
-    default: k_force<BOX, PROG_GENERIC><<<grid, STEP_BLOCK, 0, st>>>(A, S, sel); break;
+    case PROG_SC23_SC83: k_force<BOX, PROG_SC23_SC83><<<grid, STEP_BLOCK, rows_bytes, st>>>(A, S, sel); break;
+    case PROG_SC23: k_force<BOX, PROG_SC23><<<grid, STEP_BLOCK, rows_bytes, st>>>(A, S, sel); break;
+    default: k_force<BOX, PROG_GENERIC><<<grid, STEP_BLOCK, rows_bytes, st>>>(A, S, sel); break;
     }
 }
 
@@ -848,7 +939,10 @@ static int enqueue_rebuild_chain(bd_engine *h)
     if (upload_params(h)) return 1;
     NlistArrays const A = nlist_arrays(h);
     cudaStream_t const st = h->stream;
-    unsigned const bead_blocks = blocks_for(h->ntot, NL_BLOCK);
+    // per-bead kernels run grid-stride: a few waves of blocks when a rebuild is due, one wave of
+    // returning blocks when it is not
+    unsigned const bead_blocks = std::min(blocks_for(h->ntot, NL_BLOCK), 148u * 8u);
+    unsigned const row_blocks = std::min(blocks_for(h->ntot, NL_BLOCK), 148u * 32u);
     unsigned const tile_blocks = blocks_for(h->cell_cap, SCAN_TILE);
     k_rebuild_begin<<<1, 32, 0, st>>>(h->ctl.p, h->d_params.p);
     k_bbox_zero<<<std::min(bead_blocks + tile_blocks, 148u * 8u), NL_BLOCK, 0, st>>>(A);
@@ -859,8 +953,9 @@ static int enqueue_rebuild_chain(bd_engine *h)
     k_scan_down<<<tile_blocks, NL_BLOCK, 0, st>>>(A);
     k_group<<<bead_blocks, NL_BLOCK, 0, st>>>(A);
     k_place<<<bead_blocks, NL_BLOCK, 0, st>>>(A);
-    k_rows<<<bead_blocks, NL_BLOCK, 0, st>>>(A);
-    h->launches += 10;
+    k_rows<<<row_blocks, NL_BLOCK, 0, st>>>(A);
+    k_balance<<<std::min(h->chunks * h->replicas, 148u * 16u), BAL_TILE, 0, st>>>(A);
+    h->launches += 11;
     CK(cudaGetLastError());
     return 0;
 }
@@ -897,6 +992,7 @@ static int prepare_list(bd_engine *h)
         } else if (2 * c.max_row > h->cap && h->cap < limit) {
             want = std::min<uint32_t>((2 * c.max_row + 15u) & ~15u, limit);
         }
+        want = (want + ROW_PAD - 1) & ~(ROW_PAD - 1);
         if (want == h->cap) {
             h->list_verified = true;
             return 0;
@@ -1182,7 +1278,7 @@ extern "C" int bd_set_option(bd_engine *h, const char *name, double value)
     if (key == "list_capacity") {
         if (!(value >= 1 && value <= 4096)) return fail("bd_set_option: list_capacity out of range");
         CK(cudaStreamSynchronize(h->stream));
-        h->cap = (uint32_t) value;
+        h->cap = ((uint32_t) value + ROW_PAD - 1) & ~(ROW_PAD - 1);
         if (alloc_rows(h)) return 1;
         CK(cudaMemset(&h->ctl.p->overflow, 0, sizeof(uint32_t)));
         return request_rebuild(h);

@@ -20,6 +20,8 @@
 namespace bd {
 
 constexpr int NL_BLOCK = 256;
+constexpr int BAL_TILE = 128;                       // == STEP_BLOCK (checked in bd_engine.cu)
+static_assert(ROW_PAD == 4, "Verlet rows are stored in uint4 groups");
 constexpr int SCAN_ITEMS = 8;                       // counts per thread in the scan kernels
 constexpr int SCAN_TILE = NL_BLOCK * SCAN_ITEMS;    // 2048 counts per block
 
@@ -27,6 +29,7 @@ struct NlistArrays {
     const bead4 *pos;        // current positions (slot order of the previous build)
     bead4 *pos_out;          // == pos buffer, rewritten in the new slot order by k_rows
     bead4 *bpos;             // build positions, new slot order
+    float4 *shadow;          // single-precision shadow of pos_out (bd_device.cuh: make_shadow)
     uint32_t *slot_of;       // [Ntot]
     uint32_t *cellkey;       // [Ntot] key of the bead at OLD slot
     uint32_t *rank;          // [Ntot] arrival rank within the cell
@@ -34,8 +37,17 @@ struct NlistArrays {
     uint32_t *cell_count;    // [cell_cap]
     uint32_t *cell_start;    // [cell_cap + 1]
     uint32_t *block_sum;     // [cell_cap / SCAN_TILE + 1]
-    uint32_t *nbr;           // [cap][Ntot]
-    uint32_t *nnbr;          // [Ntot]
+    // Verlet rows are stored by THREAD POSITION P = replica * npad + chunk * BAL_TILE + t (npad = N
+    // rounded up to whole tiles), in groups of ROW_PAD indices: nbr4[g * pstride + P]
+    uint4 *nbr4;             // [cap / ROW_PAD][pstride]
+    uint32_t *plen;          // [pstride] row length of the bead at position P
+    uint32_t *nnbr;          // [Ntot] row length by slot
+    uint8_t *order;          // [Ntot] position -> bead offset within its BAL_TILE-slot tile, by row length
+    uint2 *bondrow;          // [bond_deg][pstride] {partner slot, ff | second << 8}, 0xffffffff slot = none
+    const uint32_t *bond_start;  // CSR of all bond forcefields by original index (bd_engine.cu: upload_topology)
+    const uint2 *bond_adj;
+    uint32_t bond_deg;       // largest number of bonds on one bead
+    uint32_t npad, pstride;
     DControl *ctl;
     const DParams *params;
     uint32_t n;              // beads per replica
@@ -148,6 +160,18 @@ __global__ void k_make_grid(NlistArrays A)
     }
     G.totalbits = G.bits[0] + G.bits[1] + G.bits[2];
     for (int d = 0; d < 3; d++) G.inv_cell[d] = (double) G.n[d] / extent[d];
+    // error bound of the shadow coordinates (bd_device.cuh: make_shadow).  Open box: two float
+    // roundings of offsets no larger than E = extent + 2 radius (a bead further than (radius-dcut)/2
+    // from its build position forces a rebuild before the next force evaluation) give
+    // |r_shadow - r| <= sqrt(3) 2^-23 E < 2^-22 E.  Periodic: two 2^-32 L quantisations.
+    double const big = fmax(extent[0], fmax(extent[1], extent[2]));
+    if (P.box_kind == BD_BOX_PERIODIC) {
+        G.shadow_eps = big * 3.725290298461914e-09;  // 2^-28
+        for (int d = 0; d < 3; d++) G.shadow_scale[d] = (float) (P.period[d] * 2.3283064365386963e-10);
+    } else {
+        G.shadow_eps = (big + 2.0 * radius) * 9.5367431640625e-07;  // 2^-20
+        for (int d = 0; d < 3; d++) G.shadow_scale[d] = 1.0f;
+    }
 }
 
 __device__ inline uint32_t bead_cell_key(const DParams &P, const DGrid &G, const bead4 &b,
@@ -158,14 +182,17 @@ __device__ inline uint32_t bead_cell_key(const DParams &P, const DGrid &G, const
     return (replica << G.totalbits) | morton_key(c[0], c[1], c[2], G.bits);
 }
 
+/* The per-bead kernels of the chain run grid-stride on a fixed, small grid (bd_engine.cu:
+ * chain_blocks): when no rebuild is due -- nine steps out of ten -- each costs one wave of
+ * immediately returning blocks instead of Ntot/256 of them. */
 __global__ void __launch_bounds__(NL_BLOCK) k_cell_count(NlistArrays A)
 {
     if (!A.ctl->doing_rebuild) return;
-    uint32_t const s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= A.ntot) return;
-    uint32_t const key = bead_cell_key(*A.params, A.ctl->grid, A.pos[s], s / A.n);
-    A.cellkey[s] = key;
-    A.rank[s] = atomicAdd(&A.cell_count[key], 1u);
+    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < A.ntot; s += gridDim.x * blockDim.x) {
+        uint32_t const key = bead_cell_key(*A.params, A.ctl->grid, A.pos[s], s / A.n);
+        A.cellkey[s] = key;
+        A.rank[s] = atomicAdd(&A.cell_count[key], 1u);
+    }
 }
 
 /* ---- exclusive scan of cell_count[0 .. replicas << totalbits) -> cell_start --------------- */
@@ -271,33 +298,40 @@ __global__ void __launch_bounds__(NL_BLOCK) k_scan_down(NlistArrays A)
 __global__ void __launch_bounds__(NL_BLOCK) k_group(NlistArrays A)
 {
     if (!A.ctl->doing_rebuild) return;
-    uint32_t const s = blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= A.ntot) return;
-    A.stage[A.cell_start[A.cellkey[s]] + A.rank[s]] = s;
+    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < A.ntot; s += gridDim.x * blockDim.x)
+        A.stage[A.cell_start[A.cellkey[s]] + A.rank[s]] = s;
 }
 
 /* deterministic order inside each cell (ascending original index), then move the records */
 __global__ void __launch_bounds__(NL_BLOCK) k_place(NlistArrays A)
 {
     if (!A.ctl->doing_rebuild) return;
-    uint32_t const t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= A.ntot) return;
-    uint32_t const old = A.stage[t];
-    uint32_t const key = A.cellkey[old];
-    uint32_t const b = A.cell_start[key], e = A.cell_start[key + 1];
-    bead4 const rec = A.pos[old];
-    uint32_t const mine = w_orig(rec.w);
-    uint32_t rnk = 0;
-    for (uint32_t u = b; u < e; u++) {
-        uint32_t const other = w_orig(A.pos[A.stage[u]].w);
-        rnk += other < mine;
+    const DParams &P = *A.params;
+    const DGrid &G = A.ctl->grid;
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < A.ntot; t += gridDim.x * blockDim.x) {
+        uint32_t const old = A.stage[t];
+        uint32_t const key = A.cellkey[old];
+        uint32_t const b = A.cell_start[key], e = A.cell_start[key + 1];
+        bead4 const rec = A.pos[old];
+        uint32_t const mine = w_orig(rec.w);
+        uint32_t rnk = 0;
+        for (uint32_t u = b; u < e; u++) {
+            uint32_t const other = w_orig(A.pos[A.stage[u]].w);
+            rnk += other < mine;
+        }
+        uint32_t const slot = b + rnk;
+        A.bpos[slot] = rec;
+        // nobody reads the shadow buffer during a rebuild: it can be rewritten in the new order here
+        A.shadow[slot] = P.box_kind == BD_BOX_PERIODIC ? make_shadow<BD_BOX_PERIODIC>(P, G, rec.x, rec.y, rec.z)
+                                                       : make_shadow<BD_BOX_OPEN>(P, G, rec.x, rec.y, rec.z);
+        A.slot_of[(old / A.n) * A.n + mine] = slot;
     }
-    uint32_t const slot = b + rnk;
-    A.bpos[slot] = rec;
-    A.slot_of[(old / A.n) * A.n + mine] = slot;
 }
 
-/* ELL rows: every bead lists all beads of its replica within the list radius at build time */
+/* ELL rows: every bead lists all beads of its replica within the list radius at build time.
+ * The scan of the 27 surrounding cells (about 165 candidates for 26 listed) tests the 16-byte
+ * single-precision shadows first; the reference's fp64 test (neighbor_searcher.hpp:81-92) decides
+ * on the survivors, so the listed SET is exactly the reference's. */
 __global__ void __launch_bounds__(NL_BLOCK) k_rows(NlistArrays A)
 {
     if (!A.ctl->doing_rebuild) return;
@@ -307,22 +341,37 @@ __global__ void __launch_bounds__(NL_BLOCK) k_rows(NlistArrays A)
         ((uint32_t *) &P)[i] = ((const uint32_t *) A.params)[i];
     for (uint32_t i = threadIdx.x; i < sizeof(DGrid) / 4; i += blockDim.x)
         ((uint32_t *) &G)[i] = ((const uint32_t *) &A.ctl->grid)[i];
+    __shared__ uint8_t bitpos[3][32];  // position of bit i of axis d inside morton_key()
+    if (threadIdx.x == 0) {
+        const int32_t *bits = A.ctl->grid.bits;
+        int pos = 0;
+        int const maxb = max(bits[0], max(bits[1], bits[2]));
+        for (int i = 0; i < maxb; i++)
+            for (int d = 0; d < 3; d++)
+                if (i < bits[d]) bitpos[d][i] = (uint8_t) pos++;
+    }
     __syncthreads();
+    double const r2max = __dmul_rn(G.radius, G.radius);
+    double const wide = G.radius + G.shadow_eps;
+    float const filter2 = __double2float_ru(wide * wide * (1.0 + 4e-6));
+    float const scale[3] = {G.shadow_scale[0], G.shadow_scale[1], G.shadow_scale[2]};
+    bool const periodic = P.box_kind == BD_BOX_PERIODIC;
 
-    uint32_t const s = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t count = 0;
-    if (s < A.ntot) {
+    unsigned long long tot = 0;
+    uint32_t longest = 0, overflowed = 0;
+    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < A.ntot; s += gridDim.x * blockDim.x) {
+        uint32_t count = 0;
         bead4 const me = A.bpos[s];
+        float4 const ms = A.shadow[s];
         A.pos_out[s] = me;
         uint32_t const replica = s / A.n;
-        double const r2max = __dmul_rn(G.radius, G.radius);
         int c[3];
         cell_coords(P, G, me.x, me.y, me.z, c);
         int lst[3][3], cnt[3];
         for (int d = 0; d < 3; d++) {
             int const n = G.n[d];
             cnt[d] = 0;
-            if (P.box_kind == BD_BOX_PERIODIC) {
+            if (periodic) {
                 if (n == 1) {
                     lst[d][cnt[d]++] = c[d];
                 } else if (n == 2) {
@@ -339,39 +388,122 @@ __global__ void __launch_bounds__(NL_BLOCK) k_rows(NlistArrays A)
                 if (c[d] < n - 1) lst[d][cnt[d]++] = c[d] + 1;
             }
         }
+        // the Morton key is separable: dilate each of the (at most) nine axis coordinates once
+        uint32_t dil[3][3];
+        for (int d = 0; d < 3; d++)
+            for (int i = 0; i < cnt[d]; i++) {
+                uint32_t v = 0;
+                for (int bit = 0; bit < G.bits[d]; bit++) v |= (((uint32_t) lst[d][i] >> bit) & 1u) << bitpos[d][bit];
+                dil[d][i] = v;
+            }
         bool over = false;
+        uint32_t grp[ROW_PAD];
+        uint4 *mine = A.nbr4 + (size_t) replica * A.npad + (s - replica * A.n);  // natural position; k_balance permutes
         for (int iz = 0; iz < cnt[2]; iz++)
             for (int iy = 0; iy < cnt[1]; iy++)
                 for (int ix = 0; ix < cnt[0]; ix++) {
-                    uint32_t const key = (replica << G.totalbits)
-                        | morton_key(lst[0][ix], lst[1][iy], lst[2][iz], G.bits);
+                    uint32_t const key = (replica << G.totalbits) | dil[0][ix] | dil[1][iy] | dil[2][iz];
                     uint32_t const b = A.cell_start[key], e = A.cell_start[key + 1];
                     for (uint32_t j = b; j < e; j++) {
-                        if (j == s) continue;
+                        float4 const q = A.shadow[j];
+                        float const d2 = periodic ? shadow_dist2<BD_BOX_PERIODIC>(ms, q, scale)
+                                                  : shadow_dist2<BD_BOX_OPEN>(ms, q, scale);
+                        if (!(d2 <= filter2) || j == s) continue;
                         bead4 const o = A.bpos[j];
                         d3 const r = displacement(P, me.x, me.y, me.z, o.x, o.y, o.z);
                         if (sqnorm_exact(r.x, r.y, r.z) > r2max) continue;
                         if (count < A.cap) {
-                            A.nbr[(size_t) count * A.ntot + s] = j;
+                            grp[count % ROW_PAD] = j;
                             count++;
+                            if (count % ROW_PAD == 0)
+                                mine[(size_t) (count / ROW_PAD - 1) * A.pstride] = make_uint4(grp[0], grp[1], grp[2], grp[3]);
                         } else {
                             over = true;
                         }
                     }
                 }
         A.nnbr[s] = count;
-        if (over) atomicAdd(&A.ctl->overflow, 1u);
+        // the last group is padded with the sentinel slot: the step kernel reads whole groups
+        if (count % ROW_PAD) {
+            for (uint32_t k = count % ROW_PAD; k < ROW_PAD; k++) grp[k] = A.ntot;
+            mine[(size_t) (count / ROW_PAD) * A.pstride] = make_uint4(grp[0], grp[1], grp[2], grp[3]);
+        }
+        overflowed += over;
+        tot += count;
+        longest = max(longest, count);
     }
-    // listed entries (2 x listed pairs)
-    unsigned long long tot = count;
-    uint32_t longest = count;
+    // listed entries (2 x listed pairs), longest row, overflowed rows
     for (int o = 16; o > 0; o >>= 1) {
         tot += __shfl_xor_sync(0xffffffffu, tot, o);
         longest = max(longest, __shfl_xor_sync(0xffffffffu, longest, o));
+        overflowed += __shfl_xor_sync(0xffffffffu, overflowed, o);
     }
     if ((threadIdx.x & 31) == 0 && tot) {
         atomicAdd(&A.ctl->listed_entries, tot);
         atomicMax(&A.ctl->max_row, longest);
+        if (overflowed) atomicAdd(&A.ctl->overflow, overflowed);
+    }
+}
+
+/* Thread -> bead assignment of the step kernels.  Inside every tile of BAL_TILE consecutive slots
+ * the beads are ranked by row length, so that the 32 rows a warp walks in lockstep end together (row
+ * lengths inside one tile of a polymer melt differ by 4x; unranked, half of the lanes idle).  The
+ * tile's Verlet rows are then moved to their thread positions, so that the step kernel reads them
+ * with one coalesced 16-byte load per lane and group, and the bonded partners of every bead are
+ * resolved to slots (the step kernel then needs neither the CSR nor slot_of).
+ * One tile per block iteration, BAL_TILE threads. */
+__global__ void __launch_bounds__(BAL_TILE) k_balance(NlistArrays A)
+{
+    if (!A.ctl->doing_rebuild) return;
+    __shared__ uint32_t len[BAL_TILE];
+    __shared__ uint8_t src[BAL_TILE];
+    __shared__ uint32_t longest;
+    uint32_t const chunks = A.npad / BAL_TILE;
+    for (uint32_t tile = blockIdx.x; tile < chunks * A.replicas; tile += gridDim.x) {
+        uint32_t const chunk = tile % chunks, replica = tile / chunks;
+        uint32_t const local = chunk * BAL_TILE + threadIdx.x;
+        uint32_t const base = replica * A.n + chunk * BAL_TILE;     // slot of the tile's first bead
+        uint32_t const pbase = replica * A.npad + chunk * BAL_TILE;  // position of the tile's first thread
+        bool const live = local < A.n;
+        uint32_t const mine = live ? A.nnbr[base + threadIdx.x] : 0xffffffffu;  // dead lanes rank last
+        __syncthreads();
+        if (threadIdx.x == 0) longest = 0;
+        len[threadIdx.x] = mine;
+        __syncthreads();
+        uint32_t rnk = 0;
+        for (uint32_t t = 0; t < BAL_TILE; t++) {
+            uint32_t const other = len[t];
+            rnk += (other < mine) || (other == mine && t < threadIdx.x);
+        }
+        src[rnk] = (uint8_t) threadIdx.x;
+        if (live) {
+            A.order[base + rnk] = (uint8_t) threadIdx.x;
+            atomicMax(&longest, mine);
+        }
+        __syncthreads();
+        // thread t now owns the bead at offset src[t]: move that bead's row to column pbase + t
+        uint32_t const from = src[threadIdx.x];
+        bool const owner = chunk * BAL_TILE + from < A.n;  // dead offsets were ranked last
+        uint32_t const groups = (longest + ROW_PAD - 1) / ROW_PAD;
+        for (uint32_t g = 0; g < groups; g++) {
+            uint4 const v = A.nbr4[(size_t) g * A.pstride + pbase + from];
+            __syncthreads();
+            A.nbr4[(size_t) g * A.pstride + pbase + threadIdx.x] = v;
+        }
+        A.plen[pbase + threadIdx.x] = owner ? len[from] : 0u;
+        if (A.bond_deg) {
+            uint32_t k = 0;
+            if (owner) {
+                uint32_t const oi = w_orig(A.bpos[base + from].w);
+                for (uint32_t c = A.bond_start[oi]; c < A.bond_start[oi + 1] && k < A.bond_deg; c++, k++) {
+                    uint2 const adj = A.bond_adj[c];
+                    A.bondrow[(size_t) k * A.pstride + pbase + threadIdx.x] =
+                        make_uint2(A.slot_of[replica * A.n + adj.x], adj.y);
+                }
+            }
+            for (; k < A.bond_deg; k++)
+                A.bondrow[(size_t) k * A.pstride + pbase + threadIdx.x] = make_uint2(0xffffffffu, 0u);
+        }
     }
 }
 
@@ -383,11 +515,14 @@ __global__ void __launch_bounds__(NL_BLOCK) k_export_pairs(NlistArrays A, uint32
 {
     uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= A.n) return;
-    uint32_t const s = replica * A.n + i;
+    uint32_t const tile = i / BAL_TILE * BAL_TILE;
+    uint32_t const s = replica * A.n + tile + A.order[replica * A.n + i];
+    uint32_t const p = replica * A.npad + i;
     uint32_t const oi = w_orig(A.bpos[s].w);
-    uint32_t const m = A.nnbr[s];
+    uint32_t const m = A.plen[p];
     for (uint32_t k = 0; k < m; k++) {
-        uint32_t const j = A.nbr[(size_t) k * A.ntot + s];
+        uint4 const grp = A.nbr4[(size_t) (k / ROW_PAD) * A.pstride + p];
+        uint32_t const j = k % ROW_PAD == 0 ? grp.x : k % ROW_PAD == 1 ? grp.y : k % ROW_PAD == 2 ? grp.z : grp.w;
         uint32_t const oj = w_orig(A.bpos[j].w);
         if (oi < oj) {
             unsigned long long const at = atomicAdd(count, 1ull);

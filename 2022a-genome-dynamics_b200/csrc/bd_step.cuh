@@ -23,15 +23,23 @@
 namespace bd {
 
 constexpr int STEP_BLOCK = 128;
+#ifndef STEP_MIN_BLOCKS
+#define STEP_MIN_BLOCKS 8  // resident CTAs per SM the fused kernel is compiled for (register budget)
+#endif
 constexpr int WALL_STATS = 4;
 
 struct StepArrays {
     const bead4 *pos;
     bead4 *pos_out;
     const bead4 *bpos;
+    const float4 *shadow;         // single-precision shadow of pos (pre-filter of the pair walk)
+    float4 *shadow_out;           // ... of pos_out
     const uint32_t *slot_of;
-    const uint32_t *nbr;
-    const uint32_t *nnbr;
+    const uint4 *nbr4;            // [cap / ROW_PAD][pstride] Verlet rows by thread position (bd_nlist.cuh)
+    const uint32_t *plen;         // [pstride] row length at a position
+    const uint2 *bondrow;         // [bond_deg][pstride] {partner slot, ff | second << 8}
+    uint32_t bond_deg, npad, pstride;
+    const uint8_t *order;         // [Ntot] thread -> bead offset within its 128-slot tile (bd_nlist.cuh: k_balance)
     const uint32_t *bond_start;   // [n+1] CSR by original index
     const uint2 *bond_adj;        // {partner original index, ff | second<<8}
     const uint32_t *bend_start;   // [n+1]
@@ -49,6 +57,10 @@ struct StepArrays {
     unsigned long long *dt_bits;  // [replicas] adaptive: min timestep of the current step
     const double *dt_prev;        // [replicas] adaptive: timestep of the previous step
     const struct PairRow *pair_rows;    // compiled table of the specialised pair program
+    const struct BondRow *bond_rows;    // compiled bond tables [used bond ff][ntypes^2], or unused
+    uint8_t bond_slot[BD_MAX_BOND_FF];  // bond forcefield -> block of bond_rows
+    int32_t bonds_compiled, nbond_rows; // all enabled bond tables are single simple terms
+    int32_t any_bend;                   // some bending forcefield exists
     uint32_t ntypes2;             // rows in pair_rows
     int32_t fast_ff;              // the pair forcefield the specialised program evaluates
     uint32_t n, replicas, ntot, chunks;
@@ -68,21 +80,18 @@ struct StepScalars {
 template <typename T>
 __device__ inline T ldg(const T *p) { return __ldg(p); }
 
-__device__ inline bead4 load_bead(const bead4 *p)
+/* one 32-byte record = one 256-bit access (sm_100: LDG.E.256 / STG.E.256) */
+__device__ __forceinline__ bead4 load_bead(const bead4 *p)
 {
     bead4 b;
-    const double2 *q = reinterpret_cast<const double2 *>(p);
-    double2 const a = q[0];
-    double2 const c = q[1];
-    b.x = a.x; b.y = a.y; b.z = c.x; b.w = (uint64_t) __double_as_longlong(c.y);
+    // .nc: the step kernels only read the buffer they gather from
+    asm("ld.global.nc.v4.b64 {%0, %1, %2, %3}, [%4];" : "=d"(b.x), "=d"(b.y), "=d"(b.z), "=l"(b.w) : "l"(p));
     return b;
 }
 
-__device__ inline void store_bead(bead4 *p, double x, double y, double z, uint64_t w)
+__device__ __forceinline__ void store_bead(bead4 *p, double x, double y, double z, uint64_t w)
 {
-    double2 *q = reinterpret_cast<double2 *>(p);
-    q[0] = make_double2(x, y);
-    q[1] = make_double2(z, __longlong_as_double((long long) w));
+    asm volatile("st.global.v4.b64 [%0], {%1, %2, %3, %4};" :: "l"(p), "d"(x), "d"(y), "d"(z), "l"(w) : "memory");
 }
 
 // ---- compile-time specialisations -----------------------------------------------------------------
@@ -103,6 +112,12 @@ enum PairProgram {
 /* one row of a compiled pair table: c = factor * P * Q * energy * k2, k2 = 1 / diameter^2 */
 struct __align__(16) PairRow {
     double k2a, ca, k2b, cb;
+};
+
+/* one row of a compiled bond table: a single harmonic / spring / semispring term (or none) */
+struct __align__(16) BondRow {
+    double k, b, factor;
+    int32_t kind, pad;
 };
 
 template <int BOX>
@@ -137,102 +152,170 @@ __device__ __forceinline__ double compiled_pair_scalar(const PairRow &row, doubl
     return s;
 }
 
-/* non-bonded forces on the bead at slot s from its Verlet row */
+constexpr int HIT_CAP = 16;  // near-hits buffered per bead between the two phases of the pair walk
+
+struct StepShared {
+    DParams P;
+    DGrid G;
+    float filter2;  // widened cutoff^2 of the shadow pre-filter
+    uint32_t hits[HIT_CAP][STEP_BLOCK];
+    double wall_red[STEP_BLOCK / 32][BD_MAX_WALL_FF][WALL_STATS];
+};
+
+extern __shared__ __align__(16) unsigned char dyn_smem[];  // PairRow[ntypes^2] of the compiled program
+
+/* Non-bonded forces on the bead at slot s from its Verlet row, in two phases:
+ *   1. walk the row (groups of ROW_PAD coalesced indices), test the 16-byte shadow of each listed
+ *      neighbour against the widened cutoff in single precision and queue the survivors;
+ *   2. load the queued neighbours' fp64 records and evaluate them exactly -- the reference's
+ *      arithmetic, in row order, so the result does not depend on the shadows at all.
+ * About 26 neighbours are listed per bead and 8 interact: phase 1 is cheap per entry and fully
+ * convergent, phase 2 runs on a third of the entries. */
 template <int BOX, int PROG>
-__device__ __forceinline__ void pair_forces(const StepArrays &A, const DParams &P, const PairRow *rows,
-                                            Select sel, uint32_t s, const bead4 &me, d3 &F,
-                                            uint32_t &interactions)
+__device__ __forceinline__ void pair_forces(const StepArrays &A, StepShared &sh, Select sel, uint32_t s,
+                                            uint32_t pos, const bead4 &me, d3 &F, uint32_t &interactions)
 {
+    const DParams &P = sh.P;
     uint32_t const oi = w_orig(me.w), ti = w_type(me.w);
     int const T = P.ntypes;
-    uint32_t const m = A.nnbr[s];
-    const uint32_t *col = A.nbr + s;
     (void) oi;
-    if (PROG != PROG_GENERIC) {
-        double const dcut2 = P.pair[A.fast_ff].dcut2;
-        const PairRow *mine = rows + ti * T;
-        size_t const stride = A.ntot;
-        auto interact = [&](const bead4 &o) {
-            d3 const r = displacement_t<BOX>(P, me.x, me.y, me.z, o.x, o.y, o.z);
-            double const r2 = sqnorm_exact(r.x, r.y, r.z);
-            if (r2 <= dcut2) {
-                double const sc = compiled_pair_scalar<PROG>(mine[w_type(o.w)], r2);
-                F.x += sc * r.x; F.y += sc * r.y; F.z += sc * r.z;
-                interactions += 1u;  // every pair is seen from both ends: halved when read out
+    if (PROG == PROG_GENERIC) {
+        bool any_pair = false;
+        for (int f = 0; f < BD_MAX_PAIR_FF; f++) any_pair |= ff_on(sel, BD_FF_PAIR, f, P.pair[f].enabled);
+        if (!any_pair) return;
+    }
+    const PairRow *mine = reinterpret_cast<const PairRow *>(dyn_smem) + ti * T;
+    double const dcut2 = PROG != PROG_GENERIC ? P.pair[A.fast_ff].dcut2 : 0.0;
+    float const filter2 = sh.filter2;
+    float const scale[3] = {sh.G.shadow_scale[0], sh.G.shadow_scale[1], sh.G.shadow_scale[2]};
+    size_t const stride = A.pstride;
+    uint32_t const m = (A.plen[pos] + ROW_PAD - 1) & ~(ROW_PAD - 1);  // rows are padded with the sentinel
+    float4 const ms = A.shadow[s];
+    const uint4 *col = A.nbr4 + pos;
+    uint32_t *queue = &sh.hits[0][threadIdx.x];
+
+    uint32_t k = 0;
+    uint32_t j[ROW_PAD], jn[ROW_PAD];
+    if (m) {
+        uint4 const g = *col;
+        j[0] = g.x; j[1] = g.y; j[2] = g.z; j[3] = g.w;
+    }
+    while (k < m) {
+        // ---- phase 1: single-precision filter ------------------------------------------------
+        // the indices of the next group are requested together with the shadows of this one, so
+        // only the gather itself is on the dependent path
+        uint32_t *qp = queue;
+        uint32_t *const qfull = queue + (HIT_CAP - ROW_PAD) * STEP_BLOCK;
+        while (k < m && qp <= qfull) {
+            float4 q[ROW_PAD];
+#pragma unroll
+            for (int u = 0; u < (int) ROW_PAD; u++) q[u] = __ldg(A.shadow + j[u]);
+            col += stride;
+            k += ROW_PAD;
+            if (k < m) {
+                uint4 const g = *col;
+                jn[0] = g.x; jn[1] = g.y; jn[2] = g.z; jn[3] = g.w;
             }
-        };
-        // four gathers in flight per thread: the row indices are independent loads, and so are
-        // the records they point at
-        uint32_t k = 0;
-        for (; k + 4 <= m; k += 4, col += 4 * stride) {
-            uint32_t const j0 = col[0], j1 = col[stride], j2 = col[2 * stride], j3 = col[3 * stride];
+#pragma unroll
+            for (int u = 0; u < (int) ROW_PAD; u++) {
+                bool near = shadow_dist2<BOX>(ms, q[u], scale) <= filter2;
+                if (BOX == BD_BOX_PERIODIC) near = near && j[u] < A.ntot;  // fixed point has no NaN
+                if (near) {
+                    *qp = j[u];
+                    qp += STEP_BLOCK;
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < (int) ROW_PAD; u++) j[u] = jn[u];
+        }
+        uint32_t const cnt = (uint32_t) (qp - queue) / STEP_BLOCK;
+        if (cnt & 1u) queue[cnt * STEP_BLOCK] = A.ntot;  // phase 2 takes the queue two at a time
+
+        // ---- phase 2: exact evaluation -------------------------------------------------------
+        for (uint32_t c = 0; c < cnt; c += 2) {
+            uint32_t const j0 = queue[c * STEP_BLOCK], j1 = queue[(c + 1) * STEP_BLOCK];
             bead4 const o0 = load_bead(A.pos + j0);
             bead4 const o1 = load_bead(A.pos + j1);
-            bead4 const o2 = load_bead(A.pos + j2);
-            bead4 const o3 = load_bead(A.pos + j3);
-            interact(o0);
-            interact(o1);
-            interact(o2);
-            interact(o3);
-        }
-        for (; k < m; k++, col += stride) interact(load_bead(A.pos + col[0]));
-        return;
-    }
-    bool any_pair = false;
-    for (int f = 0; f < BD_MAX_PAIR_FF; f++) any_pair |= ff_on(sel, BD_FF_PAIR, f, P.pair[f].enabled);
-    if (!any_pair) return;
-    for (uint32_t k = 0; k < m; k++) {
-        uint32_t const j = col[(size_t) k * A.ntot];
-        bead4 const o = load_bead(A.pos + j);
-        d3 const r = displacement_t<BOX>(P, me.x, me.y, me.z, o.x, o.y, o.z);
-        double const r2 = sqnorm_exact(r.x, r.y, r.z);
-        uint32_t const oj = w_orig(o.w), tj = w_type(o.w);
-        int const cell = oi < oj ? (int) (ti * T + tj) : (int) (tj * T + ti);
-        bool hit = false;
 #pragma unroll
-        for (int f = 0; f < BD_MAX_PAIR_FF; f++) {
-            const DPair &pf = P.pair[f];
-            if (!ff_on(sel, BD_FF_PAIR, f, pf.enabled) || r2 > pf.dcut2) continue;
-            if (pf.has_targets && !((w_pair_mask(me.w) >> f) & (w_pair_mask(o.w) >> f) & 1u)) continue;
-            double const sc = pot_force_scalar(A.terms + pf.term_off + cell * pf.nterms, pf.nterms, r2);
-            F.x += sc * r.x; F.y += sc * r.y; F.z += sc * r.z;
-            hit = true;
+            for (int u = 0; u < 2; u++) {
+                const bead4 &o = u == 0 ? o0 : o1;
+                d3 const r = displacement_t<BOX>(P, me.x, me.y, me.z, o.x, o.y, o.z);
+                double const r2 = sqnorm_exact(r.x, r.y, r.z);  // NaN for the sentinel: every test fails
+                if (PROG != PROG_GENERIC) {
+                    if (r2 <= dcut2) {
+                        double const sc = compiled_pair_scalar<PROG>(mine[w_type(o.w)], r2);
+                        F.x += sc * r.x; F.y += sc * r.y; F.z += sc * r.z;
+                        interactions += 1u;  // every pair is seen from both ends: halved when read out
+                    }
+                } else {
+                    uint32_t const oj = w_orig(o.w), tj = w_type(o.w);
+                    int const cell = oi < oj ? (int) (ti * T + tj) : (int) (tj * T + ti);
+                    bool hit = false;
+#pragma unroll
+                    for (int f = 0; f < BD_MAX_PAIR_FF; f++) {
+                        const DPair &pf = P.pair[f];
+                        if (!ff_on(sel, BD_FF_PAIR, f, pf.enabled) || !(r2 <= pf.dcut2)) continue;
+                        if (pf.has_targets && !((w_pair_mask(me.w) >> f) & (w_pair_mask(o.w) >> f) & 1u)) continue;
+                        double const sc = pot_force_scalar(A.terms + pf.term_off + cell * pf.nterms, pf.nterms, r2);
+                        F.x += sc * r.x; F.y += sc * r.y; F.z += sc * r.z;
+                        hit = true;
+                    }
+                    interactions += hit ? 1u : 0u;
+                }
+            }
         }
-        interactions += hit ? 1u : 0u;
     }
 }
 
 /* bonded pairs, bending triples and point sources acting on one bead */
 __device__ __forceinline__ void bonded_forces(const StepArrays &A, const DParams &P, Select sel,
-                                              uint32_t replica, const bead4 &me, d3 &F)
+                                              uint32_t replica, uint32_t pos, const bead4 &me, d3 &F)
 {
     uint32_t const oi = w_orig(me.w), ti = w_type(me.w);
     int const T = P.ntypes;
     uint32_t const base = replica * A.n;
 
-    // bonded pairs (no minimum image: bonded_pairwise_forcefield.hpp:64)
+    // bonded pairs (no minimum image: bonded_pairwise_forcefield.hpp:64); the partners were resolved
+    // to slots at the last rebuild (bd_nlist.cuh: k_balance)
     {
-        uint32_t const b = A.bond_start[oi], e = A.bond_start[oi + 1];
-        for (uint32_t k = b; k < e; k++) {
-            uint2 const adj = A.bond_adj[k];
+        const BondRow *brows = reinterpret_cast<const BondRow *>(dyn_smem + A.ntypes2 * sizeof(PairRow));
+        const uint2 *col = A.bondrow + pos;
+        for (uint32_t k = 0; k < A.bond_deg; k++, col += A.pstride) {
+            uint2 const adj = *col;
+            if (adj.x == 0xffffffffu) break;
             int const f = adj.y & 0xff;
             const DBond &bf = P.bond[f];
             if (!ff_on(sel, BD_FF_BOND, f, bf.enabled)) continue;
-            bead4 const o = load_bead(A.pos + A.slot_of[base + adj.x]);
+            bead4 const o = load_bead(A.pos + adj.x);
             uint32_t const tj = w_type(o.w);
             bool const second = (adj.y >> 8) & 1u;
             // the force on this bead is scalar * (x_me - x_partner) whichever end it is; only the
             // table row depends on the order (type_first, type_second)
             double const rx = me.x - o.x, ry = me.y - o.y, rz = me.z - o.z;
+            double const r2 = rx * rx + ry * ry + rz * rz;
             int const cell = second ? (int) (tj * T + ti) : (int) (ti * T + tj);
-            double const sc = pot_force_scalar(A.terms + bf.term_off + cell * bf.nterms, bf.nterms,
-                                               rx * rx + ry * ry + rz * rz);
+            double sc;
+            if (A.bonds_compiled) {
+                // single-term tables compiled on the host; same arithmetic as term_force_scalar
+                BondRow const row = brows[A.bond_slot[f] * A.ntypes2 + cell];
+                double v = 0.0;
+                if (row.kind == BD_TERM_HARMONIC) {
+                    v = -row.k;
+                } else if (row.kind != BD_TERM_NONE) {
+                    double const r1 = sqrt(r2);
+                    bool const on = row.kind == BD_TERM_SPRING ? r1 != 0.0 : r1 > row.b;
+                    if (on) v = row.k * row.b / r1 - row.k;
+                }
+                sc = row.factor * v;
+            } else {
+                sc = pot_force_scalar(A.terms + bf.term_off + cell * bf.nterms, bf.nterms, r2);
+            }
             F.x += sc * rx; F.y += sc * ry; F.z += sc * rz;
         }
     }
 
     // bending triples (cosine_bending_potential.hpp:43-60)
-    {
+    if (A.any_bend) {
         uint32_t const b = A.bend_start[oi], e = A.bend_start[oi + 1];
         for (uint32_t k = b; k < e; k++) {
             uint32_t const adj = A.bend_adj[k];
@@ -299,8 +382,7 @@ __device__ __forceinline__ void wall_force(const StepArrays &A, const DWall &wf,
         st[0] = -fr / r1;
     } else {
         // ellipsoid_surface_forcefield.hpp:54-99 (evaluate_point), :167-211
-        double const qx = 1.0 / (wf.semi[0] * wf.semi[0]), qy = 1.0 / (wf.semi[1] * wf.semi[1]),
-                     qz = 1.0 / (wf.semi[2] * wf.semi[2]);
+        double const qx = wf.quad[0], qy = wf.quad[1], qz = wf.quad[2];  // 1 / semiaxis^2 (host)
         double const dx = qx * rx, dy = qy * ry, dz = qz * rz;  // dual
         double const d2 = dx * dx + dy * dy + dz * dz;
         if (d2 == 0.0) return;
@@ -327,21 +409,32 @@ __device__ __forceinline__ void wall_force(const StepArrays &A, const DWall &wf,
     }
 }
 
-struct StepShared {
-    DParams P;
-    PairRow rows[BD_MAX_TYPES * BD_MAX_TYPES];
-    double wall_red[STEP_BLOCK / 32][BD_MAX_WALL_FF][WALL_STATS];
-};
-
 template <int PROG>
-__device__ __forceinline__ void load_shared(StepShared &sh, const StepArrays &A)
+__device__ __forceinline__ void load_shared(StepShared &sh, const StepArrays &A, Select sel)
 {
     for (uint32_t i = threadIdx.x; i < sizeof(DParams) / 4; i += blockDim.x)
         ((uint32_t *) &sh.P)[i] = ((const uint32_t *) A.params)[i];
+    for (uint32_t i = threadIdx.x; i < sizeof(DGrid) / 4; i += blockDim.x)
+        ((uint32_t *) &sh.G)[i] = ((const uint32_t *) &A.ctl->grid)[i];
     if (PROG != PROG_GENERIC) {
         uint32_t const words = A.ntypes2 * (sizeof(PairRow) / 4);
         for (uint32_t i = threadIdx.x; i < words; i += blockDim.x)
-            ((uint32_t *) sh.rows)[i] = ((const uint32_t *) A.pair_rows)[i];
+            ((uint32_t *) dyn_smem)[i] = ((const uint32_t *) A.pair_rows)[i];
+    }
+    if (A.bonds_compiled) {
+        uint32_t *dst = (uint32_t *) (dyn_smem + A.ntypes2 * sizeof(PairRow));
+        uint32_t const words = (uint32_t) A.nbond_rows * (sizeof(BondRow) / 4);
+        for (uint32_t i = threadIdx.x; i < words; i += blockDim.x) dst[i] = ((const uint32_t *) A.bond_rows)[i];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        // widened cutoff of the pre-filter: r <= dcut implies r_shadow <= dcut + shadow_eps / 4, and the
+        // factor covers the single-precision rounding of the squared distance itself
+        double dcut = 0.0;
+        for (int f = 0; f < BD_MAX_PAIR_FF; f++)
+            if (ff_on(sel, BD_FF_PAIR, f, sh.P.pair[f].enabled)) dcut = fmax(dcut, sh.P.pair[f].dcut);
+        double const wide = dcut + sh.G.shadow_eps;
+        sh.filter2 = __double2float_ru(wide * wide * (1.0 + 4e-6));
     }
     __syncthreads();
 }
@@ -355,9 +448,10 @@ __device__ __forceinline__ d3 block_forces(const StepArrays &A, StepShared &sh, 
 {
     const DParams &P = sh.P;
     d3 F = {0.0, 0.0, 0.0};
+    uint32_t const pos = replica * A.npad + chunk * STEP_BLOCK + threadIdx.x;
     if (live) {
-        pair_forces<BOX, PROG>(A, P, sh.rows, sel, s, me, F, interactions);
-        bonded_forces(A, P, sel, replica, me, F);
+        pair_forces<BOX, PROG>(A, sh, sel, s, pos, me, F, interactions);
+        bonded_forces(A, P, sel, replica, pos, me, F);
     }
     bool any_wall = false;
 #pragma unroll 1
@@ -399,7 +493,8 @@ __device__ inline void load_params(DParams &P, const DParams *src)
 /* MD/simulation/detail/brownian_simulator.hpp:57-75 for one bead; returns the squared distance
  * from the bead's position at the last list build (neighbor_list.hpp:138-157) */
 template <int BOX>
-__device__ __forceinline__ double integrate_bead(const StepArrays &A, const DParams &P, const StepScalars &S,
+__device__ __forceinline__ double integrate_bead(const StepArrays &A, const DParams &P, const DGrid &G,
+                                                 const StepScalars &S,
                                                  uint32_t s, uint32_t replica, const bead4 &me, d3 F,
                                                  double dt, double dt_prev)
 {
@@ -428,6 +523,7 @@ __device__ __forceinline__ double integrate_bead(const StepArrays &A, const DPar
     double x = me.x + mu_dt * F.x, y = me.y + mu_dt * F.y, z2 = me.z + mu_dt * F.z;
     x += 0.5 * (wx + px); y += 0.5 * (wy + py); z2 += 0.5 * (wz + pz);
     store_bead(A.pos_out + s, x, y, z2, me.w);
+    A.shadow_out[s] = make_shadow<BOX>(P, G, x, y, z2);
 
     bead4 const b0 = load_bead(A.bpos + s);
     d3 const d = displacement_t<BOX>(P, x, y, z2, b0.x, b0.y, b0.z);
@@ -445,21 +541,22 @@ __device__ __forceinline__ void publish_displacement(const StepArrays &A, double
 
 /* the hot kernel: forces + Brownian update + skin test, fixed timestep */
 template <int BOX, int PROG>
-__global__ void __launch_bounds__(STEP_BLOCK, 8) k_step_fused(StepArrays A, StepScalars S)
+__global__ void __launch_bounds__(STEP_BLOCK, STEP_MIN_BLOCKS) k_step_fused(StepArrays A, StepScalars S)
 {
     __shared__ StepShared sh;
-    load_shared<PROG>(sh, A);
-    uint32_t const replica = blockIdx.y, chunk = blockIdx.x;
-    uint32_t const local = chunk * STEP_BLOCK + threadIdx.x;
-    bool const live = local < A.n;
-    uint32_t const s = replica * A.n + (live ? local : 0u);
     Select const all = {BD_FF_ALL, -1};
+    load_shared<PROG>(sh, A, all);
+    uint32_t const replica = blockIdx.y, chunk = blockIdx.x;
+    bool const live = chunk * STEP_BLOCK + threadIdx.x < A.n;
+    // threads take the tile's beads in order of row length, so that the rows of a warp end together
+    uint32_t const s = replica * A.n
+        + (live ? chunk * STEP_BLOCK + A.order[replica * A.n + chunk * STEP_BLOCK + threadIdx.x] : 0u);
     uint32_t inter = 0;
     double const known = __longlong_as_double((long long) A.ctl->max_disp2_bits);
     bead4 const me = load_bead(A.pos + s);
     d3 const F = block_forces<BOX, PROG>(A, sh, all, live, S.want_stats != 0, s, replica, chunk, me, inter);
     double moved2 = 0.0;
-    if (live) moved2 = integrate_bead<BOX>(A, sh.P, S, s, replica, me, F, S.dt, S.dt_prev);
+    if (live) moved2 = integrate_bead<BOX>(A, sh.P, sh.G, S, s, replica, me, F, S.dt, S.dt_prev);
     publish_displacement(A, moved2, known);
     for (int o = 16; o > 0; o >>= 1) inter += __shfl_xor_sync(0xffffffffu, inter, o);
     if ((threadIdx.x & 31) == 0)  // one private counter per warp: no barrier, no atomics
@@ -471,11 +568,11 @@ template <int BOX, int PROG>
 __global__ void __launch_bounds__(STEP_BLOCK) k_force(StepArrays A, StepScalars S, Select sel)
 {
     __shared__ StepShared sh;
-    load_shared<PROG>(sh, A);
+    load_shared<PROG>(sh, A, sel);
     uint32_t const replica = blockIdx.y, chunk = blockIdx.x;
-    uint32_t const local = chunk * STEP_BLOCK + threadIdx.x;
-    bool const live = local < A.n;
-    uint32_t const s = replica * A.n + (live ? local : 0u);
+    bool const live = chunk * STEP_BLOCK + threadIdx.x < A.n;
+    uint32_t const s = replica * A.n
+        + (live ? chunk * STEP_BLOCK + A.order[replica * A.n + chunk * STEP_BLOCK + threadIdx.x] : 0u);
     uint32_t inter = 0;
     double dt = S.dt;
     bead4 const me = load_bead(A.pos + s);
@@ -507,6 +604,9 @@ template <int BOX>
 __global__ void __launch_bounds__(STEP_BLOCK) k_integrate(StepArrays A, StepScalars S)
 {
     __shared__ DParams P;
+    __shared__ DGrid G;
+    for (uint32_t i = threadIdx.x; i < sizeof(DGrid) / 4; i += blockDim.x)
+        ((uint32_t *) &G)[i] = ((const uint32_t *) &A.ctl->grid)[i];
     load_params(P, A.params);
     uint32_t const replica = blockIdx.y;
     uint32_t const local = blockIdx.x * STEP_BLOCK + threadIdx.x;
@@ -517,7 +617,7 @@ __global__ void __launch_bounds__(STEP_BLOCK) k_integrate(StepArrays A, StepScal
         bead4 const me = load_bead(A.pos + s);
         d3 const F = {A.force[3 * (size_t) s], A.force[3 * (size_t) s + 1], A.force[3 * (size_t) s + 2]};
         double const dt = __longlong_as_double((long long) A.dt_bits[replica]);
-        moved2 = integrate_bead<BOX>(A, P, S, s, replica, me, F, dt, A.dt_prev[replica]);
+        moved2 = integrate_bead<BOX>(A, P, G, S, s, replica, me, F, dt, A.dt_prev[replica]);
     }
     publish_displacement(A, moved2, known);
 }
@@ -541,16 +641,18 @@ __global__ void __launch_bounds__(STEP_BLOCK) k_energy(StepArrays A, Select sel,
     load_params(P, A.params);
     uint32_t const replica = blockIdx.y, chunk = blockIdx.x;
     uint32_t const local = chunk * STEP_BLOCK + threadIdx.x;
-    uint32_t const s = replica * A.n + local;
+    uint32_t const pos = replica * A.npad + local;
+    uint32_t const s = replica * A.n + (local < A.n ? chunk * STEP_BLOCK + A.order[replica * A.n + local] : 0u);
     double E = 0.0;
     if (local < A.n) {
         bead4 const me = load_bead(A.pos + s);
         uint32_t const oi = w_orig(me.w), ti = w_type(me.w);
         int const T = P.ntypes;
         uint32_t const base = replica * A.n;
-        uint32_t const m = A.nnbr[s];
+        uint32_t const m = A.plen[pos];
         for (uint32_t k = 0; k < m; k++) {
-            uint32_t const j = A.nbr[(size_t) k * A.ntot + s];
+            uint4 const grp = A.nbr4[(size_t) (k / ROW_PAD) * A.pstride + pos];
+            uint32_t const j = k % ROW_PAD == 0 ? grp.x : k % ROW_PAD == 1 ? grp.y : k % ROW_PAD == 2 ? grp.z : grp.w;
             bead4 const o = load_bead(A.pos + j);
             uint32_t const oj = w_orig(o.w), tj = w_type(o.w);
             if (oi >= oj) continue;
@@ -604,8 +706,7 @@ __global__ void __launch_bounds__(STEP_BLOCK) k_energy(StepArrays A, Select sel,
                 if (inside ? wf.direction == BD_WALL_INWARD : wf.direction == BD_WALL_OUTWARD)
                     E += pot_energy(row, wf.nterms, sx * sx + sy * sy + sz * sz);
             } else {
-                double const qx = 1.0 / (wf.semi[0] * wf.semi[0]), qy = 1.0 / (wf.semi[1] * wf.semi[1]),
-                             qz = 1.0 / (wf.semi[2] * wf.semi[2]);
+                double const qx = wf.quad[0], qy = wf.quad[1], qz = wf.quad[2];
                 double const dx = qx * rx, dy = qy * ry, dz = qz * rz;
                 double const d2 = dx * dx + dy * dy + dz * dz;
                 if (d2 == 0.0) continue;
@@ -698,18 +799,34 @@ __global__ void k_set_words(bead4 *pos0, bead4 *pos1, bead4 *bpos, const uint32_
     bpos[s].w = w;
 }
 
-__global__ void k_init_identity(uint32_t *slot_of, bead4 *pos0, bead4 *pos1, bead4 *bpos, uint32_t n,
-                                uint32_t ntot)
+__global__ void k_init_identity(uint32_t *slot_of, bead4 *pos0, bead4 *pos1, bead4 *bpos, float4 *shadow0,
+                                float4 *shadow1, uint8_t *order, uint32_t n, uint32_t ntot)
 {
     uint32_t const g = blockIdx.x * blockDim.x + threadIdx.x;
-    if (g >= ntot) return;
+    if (g > ntot) return;
+    if (g == ntot) {
+        // the sentinel slot: NaN coordinates fail every distance test
+        double const qnan = __longlong_as_double(0x7ff8000000000000ll);
+        float const fnan = __uint_as_float(0x7fc00000u);
+        bead4 b;
+        b.x = b.y = b.z = qnan;
+        b.w = pack_w(0xffffffffu, 0, 0, 0);
+        pos0[g] = b;
+        pos1[g] = b;
+        shadow0[g] = make_float4(fnan, fnan, fnan, 0.0f);
+        shadow1[g] = make_float4(fnan, fnan, fnan, 0.0f);
+        return;
+    }
     slot_of[g] = g;
+    order[g] = (uint8_t) ((g % n) % STEP_BLOCK);
     bead4 b;
     b.x = b.y = b.z = 0.0;
     b.w = pack_w(g % n, 0, 0, 0);
     pos0[g] = b;
     pos1[g] = b;
     bpos[g] = b;
+    shadow0[g] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    shadow1[g] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
 }
 
 }  // namespace bd
