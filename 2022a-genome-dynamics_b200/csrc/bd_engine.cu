@@ -942,7 +942,7 @@ static int enqueue_rebuild_chain(bd_engine *h)
     // per-bead kernels run grid-stride: a few waves of blocks when a rebuild is due, one wave of
     // returning blocks when it is not
     unsigned const bead_blocks = std::min(blocks_for(h->ntot, NL_BLOCK), 148u * 8u);
-    unsigned const row_blocks = std::min(blocks_for(h->ntot, NL_BLOCK), 148u * 32u);
+    unsigned const row_blocks = std::min(blocks_for(h->ntot, ROWS_BLOCK), 148u * 56u);
     unsigned const tile_blocks = blocks_for(h->cell_cap, SCAN_TILE);
     k_rebuild_begin<<<1, 32, 0, st>>>(h->ctl.p, h->d_params.p);
     k_bbox_zero<<<std::min(bead_blocks + tile_blocks, 148u * 8u), NL_BLOCK, 0, st>>>(A);
@@ -953,7 +953,7 @@ static int enqueue_rebuild_chain(bd_engine *h)
     k_scan_down<<<tile_blocks, NL_BLOCK, 0, st>>>(A);
     k_group<<<bead_blocks, NL_BLOCK, 0, st>>>(A);
     k_place<<<bead_blocks, NL_BLOCK, 0, st>>>(A);
-    k_rows<<<row_blocks, NL_BLOCK, 0, st>>>(A);
+    k_rows<<<row_blocks, ROWS_BLOCK, 0, st>>>(A);
     k_balance<<<std::min(h->chunks * h->replicas, 148u * 16u), BAL_TILE, 0, st>>>(A);
     h->launches += 11;
     CK(cudaGetLastError());

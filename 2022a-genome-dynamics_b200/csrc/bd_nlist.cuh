@@ -328,20 +328,29 @@ __global__ void __launch_bounds__(NL_BLOCK) k_place(NlistArrays A)
     }
 }
 
-/* ELL rows: every bead lists all beads of its replica within the list radius at build time.
- * The scan of the 27 surrounding cells (about 165 candidates for 26 listed) tests the 16-byte
- * single-precision shadows first; the reference's fp64 test (neighbor_searcher.hpp:81-92) decides
- * on the survivors, so the listed SET is exactly the reference's. */
-__global__ void __launch_bounds__(NL_BLOCK) k_rows(NlistArrays A)
+constexpr int ROWS_BLOCK = 128;
+
+/* ELL rows: every bead lists the beads of its replica within the list radius at build time.
+ *
+ * One thread per bead.  The (at most) 27 surrounding cells are looked up first, in lockstep, into
+ * shared memory; the candidates are then walked in ONE flat loop per thread, so a lane does not wait
+ * at every cell boundary for the fullest cell of its warp.  Candidates are tested on their 16-byte
+ * single-precision shadows against the widened radius: the stored rows are a superset of the
+ * reference's list (neighbor_searcher.hpp:81-92) by at most the shadow error bound.  That changes no
+ * result -- the step kernel decides every interaction with the exact fp64 test -- and the exported
+ * list (k_export_pairs) applies the reference's fp64 test to the build positions. */
+__global__ void __launch_bounds__(ROWS_BLOCK) k_rows(NlistArrays A)
 {
     if (!A.ctl->doing_rebuild) return;
     __shared__ DParams P;
     __shared__ DGrid G;
+    __shared__ uint2 runs[27][ROWS_BLOCK];      // [cell][thread] {first slot, end slot}, empty cells dropped
+    __shared__ uint32_t stage[ROW_PAD][ROWS_BLOCK];  // the group of the row being filled
+    __shared__ uint8_t bitpos[3][32];            // position of bit i of axis d inside morton_key()
     for (uint32_t i = threadIdx.x; i < sizeof(DParams) / 4; i += blockDim.x)
         ((uint32_t *) &P)[i] = ((const uint32_t *) A.params)[i];
     for (uint32_t i = threadIdx.x; i < sizeof(DGrid) / 4; i += blockDim.x)
         ((uint32_t *) &G)[i] = ((const uint32_t *) &A.ctl->grid)[i];
-    __shared__ uint8_t bitpos[3][32];  // position of bit i of axis d inside morton_key()
     if (threadIdx.x == 0) {
         const int32_t *bits = A.ctl->grid.bits;
         int pos = 0;
@@ -351,82 +360,107 @@ __global__ void __launch_bounds__(NL_BLOCK) k_rows(NlistArrays A)
                 if (i < bits[d]) bitpos[d][i] = (uint8_t) pos++;
     }
     __syncthreads();
-    double const r2max = __dmul_rn(G.radius, G.radius);
     double const wide = G.radius + G.shadow_eps;
     float const filter2 = __double2float_ru(wide * wide * (1.0 + 4e-6));
     float const scale[3] = {G.shadow_scale[0], G.shadow_scale[1], G.shadow_scale[2]};
     bool const periodic = P.box_kind == BD_BOX_PERIODIC;
+    uint32_t const tid = threadIdx.x;
 
     unsigned long long tot = 0;
     uint32_t longest = 0, overflowed = 0;
-    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < A.ntot; s += gridDim.x * blockDim.x) {
-        uint32_t count = 0;
+    // every thread of the block runs the same number of outer iterations (the loop has no barrier,
+    // but the warp reductions below want whole warps)
+    for (uint32_t s0 = blockIdx.x * blockDim.x; s0 < A.ntot; s0 += gridDim.x * blockDim.x) {
+        uint32_t const s = s0 + tid;
+        if (s >= A.ntot) continue;
         bead4 const me = A.bpos[s];
         float4 const ms = A.shadow[s];
         A.pos_out[s] = me;
         uint32_t const replica = s / A.n;
         int c[3];
         cell_coords(P, G, me.x, me.y, me.z, c);
-        int lst[3][3], cnt[3];
+
+        // per axis: up to three neighbouring cell coordinates, already dilated to Morton bits
+        uint32_t dil[3][3];
+        int cnt[3];
+#pragma unroll
         for (int d = 0; d < 3; d++) {
             int const n = G.n[d];
-            cnt[d] = 0;
+            int v[3];
+            int m = 0;
             if (periodic) {
                 if (n == 1) {
-                    lst[d][cnt[d]++] = c[d];
+                    v[m++] = c[d];
                 } else if (n == 2) {
-                    lst[d][cnt[d]++] = c[d];
-                    lst[d][cnt[d]++] = c[d] ^ 1;
+                    v[m++] = c[d];
+                    v[m++] = c[d] ^ 1;
                 } else {
-                    lst[d][cnt[d]++] = c[d] == 0 ? n - 1 : c[d] - 1;
-                    lst[d][cnt[d]++] = c[d];
-                    lst[d][cnt[d]++] = c[d] == n - 1 ? 0 : c[d] + 1;
+                    v[m++] = c[d] == 0 ? n - 1 : c[d] - 1;
+                    v[m++] = c[d];
+                    v[m++] = c[d] == n - 1 ? 0 : c[d] + 1;
                 }
             } else {
-                if (c[d] > 0) lst[d][cnt[d]++] = c[d] - 1;
-                lst[d][cnt[d]++] = c[d];
-                if (c[d] < n - 1) lst[d][cnt[d]++] = c[d] + 1;
+                if (c[d] > 0) v[m++] = c[d] - 1;
+                v[m++] = c[d];
+                if (c[d] < n - 1) v[m++] = c[d] + 1;
+            }
+            cnt[d] = m;
+#pragma unroll
+            for (int i = 0; i < 3; i++) {
+                uint32_t key = 0;
+                if (i < m)
+                    for (int bit = 0; bit < G.bits[d]; bit++) key |= (((uint32_t) v[i] >> bit) & 1u) << bitpos[d][bit];
+                dil[d][i] = key;
             }
         }
-        // the Morton key is separable: dilate each of the (at most) nine axis coordinates once
-        uint32_t dil[3][3];
-        for (int d = 0; d < 3; d++)
-            for (int i = 0; i < cnt[d]; i++) {
-                uint32_t v = 0;
-                for (int bit = 0; bit < G.bits[d]; bit++) v |= (((uint32_t) lst[d][i] >> bit) & 1u) << bitpos[d][bit];
-                dil[d][i] = v;
-            }
-        bool over = false;
-        uint32_t grp[ROW_PAD];
-        uint4 *mine = A.nbr4 + (size_t) replica * A.npad + (s - replica * A.n);  // natural position; k_balance permutes
-        for (int iz = 0; iz < cnt[2]; iz++)
-            for (int iy = 0; iy < cnt[1]; iy++)
-                for (int ix = 0; ix < cnt[0]; ix++) {
-                    uint32_t const key = (replica << G.totalbits) | dil[0][ix] | dil[1][iy] | dil[2][iz];
-                    uint32_t const b = A.cell_start[key], e = A.cell_start[key + 1];
-                    for (uint32_t j = b; j < e; j++) {
-                        float4 const q = A.shadow[j];
-                        float const d2 = periodic ? shadow_dist2<BD_BOX_PERIODIC>(ms, q, scale)
-                                                  : shadow_dist2<BD_BOX_OPEN>(ms, q, scale);
-                        if (!(d2 <= filter2) || j == s) continue;
-                        bead4 const o = A.bpos[j];
-                        d3 const r = displacement(P, me.x, me.y, me.z, o.x, o.y, o.z);
-                        if (sqnorm_exact(r.x, r.y, r.z) > r2max) continue;
-                        if (count < A.cap) {
-                            grp[count % ROW_PAD] = j;
-                            count++;
-                            if (count % ROW_PAD == 0)
-                                mine[(size_t) (count / ROW_PAD - 1) * A.pstride] = make_uint4(grp[0], grp[1], grp[2], grp[3]);
-                        } else {
-                            over = true;
-                        }
+        // look the cells up (lockstep: no divergence), keep the non-empty ones
+        uint32_t nruns = 0;
+#pragma unroll
+        for (int iz = 0; iz < 3; iz++)
+#pragma unroll
+            for (int iy = 0; iy < 3; iy++)
+#pragma unroll
+                for (int ix = 0; ix < 3; ix++) {
+                    if (ix < cnt[0] && iy < cnt[1] && iz < cnt[2]) {
+                        uint32_t const key = (replica << G.totalbits) | dil[0][ix] | dil[1][iy] | dil[2][iz];
+                        uint32_t const b = A.cell_start[key], e = A.cell_start[key + 1];
+                        if (b < e) runs[nruns++][tid] = make_uint2(b, e);
                     }
                 }
+
+        // one flat walk over all candidates
+        uint4 *dst = A.nbr4 + (size_t) replica * A.npad + (s - replica * A.n);  // natural position; k_balance permutes
+        uint32_t count = 0, run = 0, j = 0, e = 0;
+        bool over = false;
+        while (true) {
+            if (j >= e) {
+                if (run == nruns) break;
+                uint2 const r = runs[run++][tid];
+                j = r.x;
+                e = r.y;
+            }
+            float4 const q = A.shadow[j];
+            float const d2 = periodic ? shadow_dist2<BD_BOX_PERIODIC>(ms, q, scale)
+                                      : shadow_dist2<BD_BOX_OPEN>(ms, q, scale);
+            if (d2 <= filter2 && j != s) {
+                if (count < A.cap) {
+                    stage[count % ROW_PAD][tid] = j;
+                    count++;
+                    if (count % ROW_PAD == 0) {
+                        *dst = make_uint4(stage[0][tid], stage[1][tid], stage[2][tid], stage[3][tid]);
+                        dst += A.pstride;
+                    }
+                } else {
+                    over = true;
+                }
+            }
+            j++;
+        }
         A.nnbr[s] = count;
         // the last group is padded with the sentinel slot: the step kernel reads whole groups
         if (count % ROW_PAD) {
-            for (uint32_t k = count % ROW_PAD; k < ROW_PAD; k++) grp[k] = A.ntot;
-            mine[(size_t) (count / ROW_PAD) * A.pstride] = make_uint4(grp[0], grp[1], grp[2], grp[3]);
+            for (uint32_t k = count % ROW_PAD; k < ROW_PAD; k++) stage[k][tid] = A.ntot;
+            *dst = make_uint4(stage[0][tid], stage[1][tid], stage[2][tid], stage[3][tid]);
         }
         overflowed += over;
         tot += count;
@@ -518,12 +552,19 @@ __global__ void __launch_bounds__(NL_BLOCK) k_export_pairs(NlistArrays A, uint32
     uint32_t const tile = i / BAL_TILE * BAL_TILE;
     uint32_t const s = replica * A.n + tile + A.order[replica * A.n + i];
     uint32_t const p = replica * A.npad + i;
-    uint32_t const oi = w_orig(A.bpos[s].w);
+    bead4 const me = A.bpos[s];
+    uint32_t const oi = w_orig(me.w);
+    double const radius = A.ctl->grid.radius;
+    double const r2max = __dmul_rn(radius, radius);
     uint32_t const m = A.plen[p];
     for (uint32_t k = 0; k < m; k++) {
         uint4 const grp = A.nbr4[(size_t) (k / ROW_PAD) * A.pstride + p];
         uint32_t const j = k % ROW_PAD == 0 ? grp.x : k % ROW_PAD == 1 ? grp.y : k % ROW_PAD == 2 ? grp.z : grp.w;
-        uint32_t const oj = w_orig(A.bpos[j].w);
+        bead4 const o = A.bpos[j];
+        uint32_t const oj = w_orig(o.w);
+        // the stored rows are a superset by the shadow error bound: apply the reference's test
+        d3 const r = displacement(*A.params, me.x, me.y, me.z, o.x, o.y, o.z);
+        if (sqnorm_exact(r.x, r.y, r.z) > r2max) continue;
         if (oi < oj) {
             unsigned long long const at = atomicAdd(count, 1ull);
             if (at < cap) {
