@@ -132,6 +132,7 @@ struct bd_engine {
 
     // optional CUDA-event timing of the step kernel alone (bench.py roofline)
     bool time_kernel = false;
+    uint32_t replica_base = 0, replica_stride = 1;  // noise key of local replica r (bd_set_option)
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> kernel_events;
 };
 
@@ -1059,6 +1060,8 @@ extern "C" int bd_step(bd_engine *h, const bd_step_config *cfg)
     S.seed = cfg->seed;
     S.adaptive = adaptive;
     S.replay = nullptr;
+    S.replica_base = h->replica_base;
+    S.replica_stride = h->replica_stride;
     Select const all = {BD_FF_ALL, -1};
 
     for (int64_t k = 0; k < cfg->steps; k++) {
@@ -1275,6 +1278,11 @@ extern "C" int bd_set_option(bd_engine *h, const char *name, double value)
         h->time_kernel = value != 0;
         return 0;
     }
+    if (key == "replica_id_base" || key == "replica_id_stride") {
+        if (!(value >= 0 && value < 4294967296.0)) return fail("bd_set_option: replica id out of range");
+        (key == "replica_id_base" ? h->replica_base : h->replica_stride) = (uint32_t) value;
+        return 0;
+    }
     if (key == "list_capacity") {
         if (!(value >= 1 && value <= 4096)) return fail("bd_set_option: list_capacity out of range");
         CK(cudaStreamSynchronize(h->stream));
@@ -1293,6 +1301,8 @@ extern "C" int bd_get_option(bd_engine *h, const char *name, double *value)
     if (key == "verlet_factor") *value = h->hp.verlet_factor;
     else if (key == "list_capacity") *value = h->cap;
     else if (key == "block_size") *value = STEP_BLOCK;
+    else if (key == "replica_id_base") *value = h->replica_base;
+    else if (key == "replica_id_stride") *value = h->replica_stride;
     else if (key == "specialize") *value = h->specialize;
     else if (key == "pair_program") {
         if (upload_params(h)) return 1;

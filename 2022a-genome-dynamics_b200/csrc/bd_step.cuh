@@ -75,6 +75,9 @@ struct StepScalars {
     const double *replay;    // device, [replicas][n][3] standard normals of this step, or null
     int adaptive;
     int want_stats;          // reduce the wall reaction statistics in this step
+    // noise key of local replica r is replica_base + r * replica_stride: an ensemble sharded over
+    // GPUs draws the same noise for a replica wherever it runs (ensemble.py)
+    uint32_t replica_base, replica_stride;
 };
 
 template <typename T>
@@ -510,11 +513,11 @@ __device__ __forceinline__ double integrate_bead(const StepArrays &A, const DPar
         A.wprev[3 * g] = wx; A.wprev[3 * g + 1] = wy; A.wprev[3 * g + 2] = wz;
     } else {
         double z[3];
-        philox_normals(S.seed, (uint64_t) S.step, replica, oi, z);
+        philox_normals(S.seed, (uint64_t) S.step, S.replica_base + replica * S.replica_stride, oi, z);
         wx = sigma * z[0]; wy = sigma * z[1]; wz = sigma * z[2];
         if (S.step > 1) {
             double const sp = sqrt(2.0 * S.kT_prev * (dt_prev * mu));
-            philox_normals(S.seed, (uint64_t) (S.step - 1), replica, oi, z);
+            philox_normals(S.seed, (uint64_t) (S.step - 1), S.replica_base + replica * S.replica_stride, oi, z);
             px = sp * z[0]; py = sp * z[1]; pz = sp * z[2];
         } else {
             px = py = pz = 0.0;

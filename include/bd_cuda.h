@@ -36,7 +36,8 @@ int bd_sync(bd_engine *h);
 
 /* Tunables.  Names: "verlet_factor" (list radius / dcut, reference value 1.5,
  * MD/forcefield/detail/neighbor_list.hpp:182), "list_capacity" (ELL row length),
- * "time_kernel" (0/1: bracket every fused step kernel with CUDA events), and read-only
+ * "time_kernel" (0/1: bracket every fused step kernel with CUDA events), "replica_id_base" /
+ * "replica_id_stride" (noise key of local replica r = base + r * stride, for sharded ensembles), and read-only
  * "block_size", "kernel_ms_avg" (mean event-timed duration of the step kernel since last read). */
 int bd_set_option(bd_engine *h, const char *name, double value);
 int bd_get_option(bd_engine *h, const char *name, double *value);
