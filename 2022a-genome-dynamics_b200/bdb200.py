@@ -166,6 +166,9 @@ ENGINE_ONLY = {
     "get_launch_count": [C.c_void_p, _P(C.c_int64)],
     "set_all_positions": [C.c_void_p, C.c_void_p],
     "get_all_positions": [C.c_void_p, C.c_void_p],
+    "set_owned": [C.c_void_p, _u8_p],
+    "gather_positions_indexed": [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p],
+    "scatter_positions_indexed": [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p],
 }
 
 
@@ -460,6 +463,22 @@ class System:
 
     def get_all_positions(self, host_ptr: int):
         self.b.call("get_all_positions", self.h, C.c_void_p(host_ptr))
+
+    def set_owned(self, owned):
+        """slab decomposition: 0/1 per bead, None = every bead is advanced by this engine"""
+        if owned is None:
+            self.b.call("set_owned", self.h, None)
+            return
+        m = np.ascontiguousarray(owned, dtype=np.uint8)
+        assert m.shape == (self.n,)
+        self.b.call("set_owned", self.h, m.ctypes.data_as(_u8_p))
+
+    def gather_positions_indexed(self, d_index: int, count: int, d_xyz: int):
+        """device pointers: uint32 original indices, xyz[count][3] doubles"""
+        self.b.call("gather_positions_indexed", self.h, C.c_void_p(d_index), int(count), C.c_void_p(d_xyz))
+
+    def scatter_positions_indexed(self, d_index: int, count: int, d_xyz: int):
+        self.b.call("scatter_positions_indexed", self.h, C.c_void_p(d_index), int(count), C.c_void_p(d_xyz))
 
     def get_launch_count(self) -> int:
         v = C.c_int64(0)

@@ -46,6 +46,11 @@ __host__ __device__ inline uint32_t w_orig(uint64_t w) { return (uint32_t) w; }
 __host__ __device__ inline uint32_t w_type(uint64_t w) { return (uint32_t) (w >> 32) & 0xff; }
 __host__ __device__ inline uint32_t w_pair_mask(uint64_t w) { return (uint32_t) (w >> 40) & 0xff; }
 __host__ __device__ inline uint32_t w_point_mask(uint64_t w) { return (uint32_t) (w >> 48) & 0xff; }
+/* Bit 7 of the point-mask byte marks a GHOST: a bead another engine (another GPU's slab) advances.  Its
+ * position only changes through bd_scatter_positions_device; no force is evaluated for it, but it is a
+ * neighbour and a bonded partner like any other bead. */
+constexpr uint32_t GHOST_BIT = 0x80u;
+__host__ __device__ inline bool w_ghost(uint64_t w) { return ((uint32_t) (w >> 48) & GHOST_BIT) != 0; }
 
 /* flattened potential term with the constants the kernels need precomputed on the host */
 struct __align__(16) DTerm {

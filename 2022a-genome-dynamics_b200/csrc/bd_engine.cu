@@ -629,6 +629,44 @@ extern "C" int bd_get_positions_device(bd_engine *h, double *d_xyz)
     return 0;
 }
 
+/* Slab decomposition (slab.py): beads another engine advances are GHOSTS here. */
+extern "C" int bd_set_owned(bd_engine *h, const uint8_t *owned)
+{
+    NEED(h);
+    if (h->replicas != 1) return fail("bd_set_owned: slab decomposition applies to a single system (1 replica)");
+    for (uint32_t i = 0; i < h->n; i++) {
+        h->h_point_mask[i] = (uint8_t) (h->h_point_mask[i] & ~GHOST_BIT);
+        if (owned && !owned[i]) h->h_point_mask[i] |= (uint8_t) GHOST_BIT;
+    }
+    if (upload_words(h)) return 1;
+    return request_rebuild(h);  // ghosts carry no Verlet row
+}
+
+extern "C" int bd_gather_positions_indexed(bd_engine *h, const uint32_t *d_index, int64_t count, double *d_xyz)
+{
+    NEED(h);
+    if (count < 0 || (count > 0 && (!d_index || !d_xyz))) return fail("bd_gather_positions_indexed: bad arguments");
+    if (count == 0) return 0;
+    k_gather_indexed<<<blocks_for((uint32_t) count, 256), 256, 0, h->stream>>>(h->pos[h->cur].p, h->slot_of.p, d_index,
+                                                                                d_xyz, (uint32_t) count);
+    h->launches++;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int bd_scatter_positions_indexed(bd_engine *h, const uint32_t *d_index, int64_t count, const double *d_xyz)
+{
+    NEED(h);
+    if (count < 0 || (count > 0 && (!d_index || !d_xyz))) return fail("bd_scatter_positions_indexed: bad arguments");
+    if (count == 0) return 0;
+    if (upload_params(h)) return 1;
+    k_scatter_indexed<<<blocks_for((uint32_t) count, 256), 256, 0, h->stream>>>(
+        h->pos[h->cur].p, h->shadow[h->cur].p, h->slot_of.p, d_index, d_xyz, (uint32_t) count, h->d_params.p, h->ctl.p);
+    h->launches++;
+    CK(cudaGetLastError());
+    return 0;
+}
+
 static int set_mask_bit(std::vector<uint8_t> &mask, const uint8_t *targets, uint32_t n, int bit)
 {
     for (uint32_t i = 0; i < n; i++) {

@@ -432,6 +432,7 @@ __global__ void __launch_bounds__(ROWS_BLOCK) k_rows(NlistArrays A)
         uint4 *dst = A.nbr4 + (size_t) replica * A.npad + (s - replica * A.n);  // natural position; k_balance permutes
         uint32_t count = 0, run = 0, j = 0, e = 0;
         bool over = false;
+        if (w_ghost(me.w)) nruns = 0;  // no force is evaluated for a ghost: it needs no row
         while (true) {
             if (j >= e) {
                 if (run == nruns) break;

@@ -533,6 +533,19 @@ __device__ __forceinline__ double integrate_bead(const StepArrays &A, const DPar
     return sqnorm_exact(d.x, d.y, d.z);
 }
 
+/* a ghost keeps the position its owner sent: copy it to the other buffer and report how far it is
+ * from where it was at the last list build */
+template <int BOX>
+__device__ __forceinline__ double carry_ghost(const StepArrays &A, const DParams &P, const DGrid &G, uint32_t s,
+                                              const bead4 &me)
+{
+    store_bead(A.pos_out + s, me.x, me.y, me.z, me.w);
+    A.shadow_out[s] = make_shadow<BOX>(P, G, me.x, me.y, me.z);
+    bead4 const b0 = load_bead(A.bpos + s);
+    d3 const d = displacement_t<BOX>(P, me.x, me.y, me.z, b0.x, b0.y, b0.z);
+    return sqnorm_exact(d.x, d.y, d.z);
+}
+
 /* fold the block's largest displacement^2 into the control block; the rebuild decision itself is
  * taken by k_rebuild_begin before the next force evaluation (neighbor_list.hpp:132-158) */
 __device__ __forceinline__ void publish_displacement(const StepArrays &A, double moved2, double known)
@@ -557,9 +570,11 @@ __global__ void __launch_bounds__(STEP_BLOCK, STEP_MIN_BLOCKS) k_step_fused(Step
     uint32_t inter = 0;
     double const known = __longlong_as_double((long long) A.ctl->max_disp2_bits);
     bead4 const me = load_bead(A.pos + s);
-    d3 const F = block_forces<BOX, PROG>(A, sh, all, live, S.want_stats != 0, s, replica, chunk, me, inter);
+    bool const active = live && !w_ghost(me.w);
+    d3 const F = block_forces<BOX, PROG>(A, sh, all, active, S.want_stats != 0, s, replica, chunk, me, inter);
     double moved2 = 0.0;
-    if (live) moved2 = integrate_bead<BOX>(A, sh.P, sh.G, S, s, replica, me, F, S.dt, S.dt_prev);
+    if (active) moved2 = integrate_bead<BOX>(A, sh.P, sh.G, S, s, replica, me, F, S.dt, S.dt_prev);
+    else if (live) moved2 = carry_ghost<BOX>(A, sh.P, sh.G, s, me);
     publish_displacement(A, moved2, known);
     for (int o = 16; o > 0; o >>= 1) inter += __shfl_xor_sync(0xffffffffu, inter, o);
     if ((threadIdx.x & 31) == 0)  // one private counter per warp: no barrier, no atomics
@@ -579,12 +594,13 @@ __global__ void __launch_bounds__(STEP_BLOCK) k_force(StepArrays A, StepScalars 
     uint32_t inter = 0;
     double dt = S.dt;
     bead4 const me = load_bead(A.pos + s);
-    d3 const F = block_forces<BOX, PROG>(A, sh, sel, live, true, s, replica, chunk, me, inter);
+    bool const active = live && !w_ghost(me.w);
+    d3 const F = block_forces<BOX, PROG>(A, sh, sel, active, true, s, replica, chunk, me, inter);
     if (live) {
         A.force[3 * (size_t) s] = F.x;
         A.force[3 * (size_t) s + 1] = F.y;
         A.force[3 * (size_t) s + 2] = F.z;
-        if (S.adaptive) {
+        if (S.adaptive && active) {
             // brownian_timestepper.hpp:72-91,109-136
             double const mu = sh.P.mobility[w_type(me.w)];
             double const f2 = F.x * F.x + F.y * F.y + F.z * F.z;
@@ -620,7 +636,8 @@ __global__ void __launch_bounds__(STEP_BLOCK) k_integrate(StepArrays A, StepScal
         bead4 const me = load_bead(A.pos + s);
         d3 const F = {A.force[3 * (size_t) s], A.force[3 * (size_t) s + 1], A.force[3 * (size_t) s + 2]};
         double const dt = __longlong_as_double((long long) A.dt_bits[replica]);
-        moved2 = integrate_bead<BOX>(A, P, G, S, s, replica, me, F, dt, A.dt_prev[replica]);
+        if (w_ghost(me.w)) moved2 = carry_ghost<BOX>(A, P, G, s, me);
+        else moved2 = integrate_bead<BOX>(A, P, G, S, s, replica, me, F, dt, A.dt_prev[replica]);
     }
     publish_displacement(A, moved2, known);
 }
@@ -647,7 +664,7 @@ __global__ void __launch_bounds__(STEP_BLOCK) k_energy(StepArrays A, Select sel,
     uint32_t const pos = replica * A.npad + local;
     uint32_t const s = replica * A.n + (local < A.n ? chunk * STEP_BLOCK + A.order[replica * A.n + local] : 0u);
     double E = 0.0;
-    if (local < A.n) {
+    if (local < A.n && !w_ghost(load_bead(A.pos + s).w)) {
         bead4 const me = load_bead(A.pos + s);
         uint32_t const oi = w_orig(me.w), ti = w_type(me.w);
         int const T = P.ntypes;
@@ -785,6 +802,34 @@ __global__ void k_gather_forces(const double *force, const uint32_t *slot_of, do
     out[3 * (size_t) i] = force[3 * s];
     out[3 * (size_t) i + 1] = force[3 * s + 1];
     out[3 * (size_t) i + 2] = force[3 * s + 2];
+}
+
+/* positions of a list of original indices (replica 0) -> xyz[count][3]: what a slab sends to its
+ * neighbours every step (slab.py) */
+__global__ void k_gather_indexed(const bead4 *pos, const uint32_t *slot_of, const uint32_t *idx, double *xyz,
+                                 uint32_t count)
+{
+    uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    bead4 const b = load_bead(pos + slot_of[idx[i]]);
+    xyz[3 * (size_t) i] = b.x;
+    xyz[3 * (size_t) i + 1] = b.y;
+    xyz[3 * (size_t) i + 2] = b.z;
+}
+
+/* xyz[count][3] -> positions (and shadows) of a list of original indices: the ghosts a slab receives */
+__global__ void k_scatter_indexed(bead4 *pos, float4 *shadow, const uint32_t *slot_of, const uint32_t *idx,
+                                  const double *xyz, uint32_t count, const DParams *params, const DControl *ctl)
+{
+    uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    uint32_t const s = slot_of[idx[i]];
+    double const x = xyz[3 * (size_t) i], y = xyz[3 * (size_t) i + 1], z = xyz[3 * (size_t) i + 2];
+    pos[s].x = x;
+    pos[s].y = y;
+    pos[s].z = z;
+    shadow[s] = params->box_kind == BD_BOX_PERIODIC ? make_shadow<BD_BOX_PERIODIC>(*params, ctl->grid, x, y, z)
+                                                    : make_shadow<BD_BOX_OPEN>(*params, ctl->grid, x, y, z);
 }
 
 /* (re)write the packed word of every bead: original index, class, target masks */

@@ -47,6 +47,16 @@ int bd_get_option(bd_engine *h, const char *name, double *value);
 int bd_set_positions_device(bd_engine *h, const double *d_xyz);
 int bd_get_positions_device(bd_engine *h, double *d_xyz);
 
+/* ---- slab decomposition of one large system over several engines (several GPUs) ------------------
+ * The reference has no counterpart (micromd is single-threaded); SURVEY.md 8e / slab.py.  Every engine
+ * holds all beads; `owned[n_beads]` (HOST, 0/1, NULL = all) says which ones this engine advances.  The
+ * others are ghosts: neighbours and bonded partners whose positions arrive from their owner every step.
+ * The indexed gather / scatter take DEVICE pointers (original bead indices, xyz[count][3]) and are
+ * enqueued on the engine's stream, so a halo exchange needs no host synchronisation. */
+int bd_set_owned(bd_engine *h, const uint8_t *owned);
+int bd_gather_positions_indexed(bd_engine *h, const uint32_t *d_index, int64_t count, double *d_xyz);
+int bd_scatter_positions_indexed(bd_engine *h, const uint32_t *d_index, int64_t count, const double *d_xyz);
+
 /* All replicas at once through HOST buffers laid out [n_replicas][n_beads][3] (original bead order);
  * with pinned buffers the copies are asynchronous on the engine's stream.  bd_get_all_positions
  * returns after the data has arrived. */
