@@ -85,13 +85,28 @@ class SlabLayout:
         return d
 
 
+_streams: Dict[str, "torch.cuda.Stream"] = {}
+
+
+def work_stream(device) -> "torch.cuda.Stream":
+    """The one CUDA stream per device on which engines, torch operations and NCCL transfers of this module
+    are ordered.  It becomes torch's current stream (the legacy default stream cannot be handed to the
+    engine: bd_set_stream(NULL) means "the engine's own stream")."""
+    key = str(torch.device(device))
+    if key not in _streams:
+        _streams[key] = torch.cuda.Stream(device=torch.device(device))
+    torch.cuda.set_stream(_streams[key])
+    return _streams[key]
+
+
 class EngineStore:
     """The beads of one rank in a B200 engine (bdb200.System with one replica)."""
 
     def __init__(self, system, device: str):
         self.system, self.device, self.n = system, torch.device(device), system.n
         torch.cuda.set_device(self.device)
-        system.set_stream(torch.cuda.current_stream(self.device).cuda_stream)
+        self.stream = work_stream(self.device)
+        system.set_stream(self.stream.cuda_stream)
         self._xyz = torch.empty((self.n, 3), dtype=torch.float64, device=self.device)
 
     def positions(self) -> torch.Tensor:

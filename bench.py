@@ -46,6 +46,12 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--workload", default="genome100kb", choices=["genome100kb", "slab1kb"],
+                    help="genome100kb: the headline replica ensemble (weak scaling); slab1kb: ONE 1kb chromatin system "
+                         "split into x-slabs with a per-step NCCL halo exchange (strong scaling, BASELINE configs[4])")
+    ap.add_argument("--chains", type=int, default=600, help="slab1kb: chains")
+    ap.add_argument("--chain-len", type=int, default=10000, help="slab1kb: beads per chain")
+    ap.add_argument("--migrate-every", type=int, default=10, help="slab1kb: steps between ownership migrations")
     return ap.parse_args()
 
 
@@ -322,10 +328,107 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
+def run_slab(args):
+    """One large periodic 1kb chromatin system, slab-decomposed over the ranks (slab.py).  A step is one
+    BD step of the whole system: fused force+integrate on every rank's owned beads, then the halo
+    exchange (NCCL send/recv).  Migrations (every --migrate-every steps) are inside the timed region."""
+    import torch
+    import torch.distributed as dist
+
+    import bdb200 as bd
+    import scenarios as sc
+    import slab
+
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the engine has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = f"cuda:{local}"
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    eng = bd.load_engine()
+    scen = sc.chromatin_1kb(args.chains, args.chain_len)
+    dcut = max(ff["dcut"] for ff in scen.pair_ffs)
+    sysm = bd.System(eng, scen.n, 1, device=local)
+    scen.apply(sysm)
+    dt, kT, seed = scen.timestep, scen.temperature, 77
+    sampler = ClockSampler(local)
+    K, W = args.steps, max(args.warmup, 3)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    stream = slab.work_stream(dev)  # torch's current stream from here on: engine, events and NCCL are ordered on it
+    if world == 1:
+        sysm.set_stream(stream.cuda_stream)
+        sysm.step(args.relax + W, dt, kT, seed=seed)
+        done = args.relax + W
+        c0, l0 = sysm.get_counters(), sysm.get_launch_count()
+        barrier()
+        sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        sysm.step(K, dt, kT, seed=seed, first_step=done + 1)
+        e1.record()
+        barrier()
+        halo_bytes = 0
+    else:
+        lay = slab.SlabLayout.balanced(scen.positions[0][:, 0], world, period=scen.period[0])
+        sl = slab.SlabSystem(slab.EngineStore(sysm, dev), lay, rank, halo=3.0 * dcut, margin=dcut,
+                             migrate_every=args.migrate_every, partners=slab.topology_partners(scen))
+        ex = slab.DistExchange(dev)
+        slab.run_distributed(sl, ex, args.relax + W, dt, kT, seed)
+        c0, l0 = sysm.get_counters(), sysm.get_launch_count()
+        b0 = sl.halo_bytes_sent
+        barrier()
+        sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        slab.run_distributed(sl, ex, K, dt, kT, seed)
+        e1.record()
+        barrier()
+        halo_bytes = sl.halo_bytes_sent - b0
+    clocks = sampler.stop()
+    ms = e0.elapsed_time(e1)
+    c1 = sysm.get_counters()
+    t = torch.tensor([ms, float(c1.pair_interactions - c0.pair_interactions), float(halo_bytes),
+                      float(sysm.get_launch_count() - l0)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        tmax, tsum = t.clone(), t.clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        ms, inter, halo_bytes, launches = tmax[0].item(), tsum[1].item(), tsum[2].item(), tsum[3].item()
+    else:
+        inter, launches = t[1].item(), t[3].item()
+    if rank == 0:
+        line = {
+            "metric": "bead_steps_per_s", "value": scen.n * K / (ms * 1e-3), "unit": "bead-steps/s", "n_gpus": world,
+            "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"3-sim-1kb chromatin, one periodic system of {scen.n} beads ({args.chains} chains x {args.chain_len})",
+                       "timestep": dt, "temperature": kT, "noise": "philox4x32-10", "relax_steps": args.relax,
+                       "parallelism": (f"{world} x-slabs, per-step halo exchange over NCCL send/recv, migration every "
+                                       f"{args.migrate_every} steps" if world > 1 else "single GPU, no decomposition"),
+                       "halo_width": 3.0 * dcut, "l2": "working set > 126 MB L2 for >= 2 M beads"},
+            "pair_interactions_per_s": inter / (ms * 1e-3), "gpu_launches": int(launches),
+            "halo_bytes_per_step": halo_bytes / K, "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    sysm.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     args = parse()
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "slab1kb":
+        run_slab(args)
     else:
         run_b200(args)
 
