@@ -371,8 +371,13 @@ def chromatin_1kb(n_chains=6, chain_len=1000, seed=5, replicas=1, volume_fractio
     n_glue, n_loop = n // 20, n // 200
     gi = rng.choice(n - 1, size=n_glue, replace=False)
     glue_pairs = np.stack([gi, np.minimum(n - 1, gi + rng.integers(3, 30, size=n_glue))], axis=1).astype(np.uint32)
-    li = rng.choice(n - 200, size=max(1, n_loop), replace=False)
-    loop_pairs = np.stack([li, li + rng.integers(20, 200, size=len(li))], axis=1).astype(np.uint32)
+    # loops are extruded along one chain (3-sim-1kb/src/simulation/loops/basic_loop_simulator.cpp:165-316):
+    # both anchors stay inside the chain of the first one
+    li = rng.choice(n - 1, size=max(1, n_loop), replace=False)
+    chain_end = chains[np.searchsorted(chains[:, 1], li, side="right"), 1]
+    lj = np.minimum(li + rng.integers(20, 200, size=len(li)), chain_end - 1)
+    keep = lj > li
+    loop_pairs = np.stack([li[keep], lj[keep]], axis=1).astype(np.uint32)
     return Scenario(
         "chromatin_1kb", n, np.zeros(n, np.uint8), np.array([1.0]), pos, bd.BOX_PERIODIC, (L, L, L),
         pair_ffs=[dict(table=one([bd.softcore(2, 3, p["repulsive_energy"], p["repulsive_diameter"]),

@@ -365,8 +365,9 @@ def run_slab(args):
     stream = slab.work_stream(dev)  # torch's current stream from here on: engine, events and NCCL are ordered on it
     if world == 1:
         sysm.set_stream(stream.cuda_stream)
-        sysm.step(args.relax + W, dt, kT, seed=seed)
-        done = args.relax + W
+        sysm.step(args.relax, dt, kT, seed=seed + 1)
+        sysm.step(W, dt, kT, seed=seed)
+        done = W
         c0, l0 = sysm.get_counters(), sysm.get_launch_count()
         barrier()
         sampler.start()
@@ -381,7 +382,14 @@ def run_slab(args):
         sl = slab.SlabSystem(slab.EngineStore(sysm, dev), lay, rank, halo=3.0 * dcut, margin=dcut,
                              migrate_every=args.migrate_every, partners=slab.topology_partners(scen))
         ex = slab.DistExchange(dev)
-        slab.run_distributed(sl, ex, args.relax + W, dt, kT, seed)
+        # The synthetic start (overlapping random walks) relaxes violently: beads would outrun the halo
+        # margin.  Every rank relaxes the whole system first, rank 0's result is broadcast so that all
+        # ranks start the decomposed run from the same bits.
+        sysm.step(args.relax, dt, kT, seed=seed + 1)
+        start = sl.store.positions().clone()
+        dist.broadcast(start, src=0)
+        sysm.set_positions_device(start.data_ptr())
+        slab.run_distributed(sl, ex, W, dt, kT, seed)
         c0, l0 = sysm.get_counters(), sysm.get_launch_count()
         b0 = sl.halo_bytes_sent
         barrier()
