@@ -167,6 +167,7 @@ ENGINE_ONLY = {
     "set_all_positions": [C.c_void_p, C.c_void_p],
     "get_all_positions": [C.c_void_p, C.c_void_p],
     "set_owned": [C.c_void_p, _u8_p],
+    "set_owned_device": [C.c_void_p, C.c_void_p],
     "gather_positions_indexed": [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p],
     "scatter_positions_indexed": [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p],
 }
@@ -472,6 +473,10 @@ class System:
         m = np.ascontiguousarray(owned, dtype=np.uint8)
         assert m.shape == (self.n,)
         self.b.call("set_owned", self.h, m.ctypes.data_as(_u8_p))
+
+    def set_owned_device(self, d_owned: int):
+        """device pointer to n uint8 flags"""
+        self.b.call("set_owned_device", self.h, C.c_void_p(d_owned))
 
     def gather_positions_indexed(self, d_index: int, count: int, d_xyz: int):
         """device pointers: uint32 original indices, xyz[count][3] doubles"""

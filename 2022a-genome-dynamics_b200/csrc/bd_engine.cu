@@ -100,7 +100,7 @@ struct bd_engine {
     bool specialize = true;
     DevBuf<double> force, wprev, xyz_stage, wall_partial, wall_out, energy_partial, energy_out, dt_prev, dt_last;
     DevBuf<unsigned long long> inter_partial, dt_bits, pair_count;
-    DevBuf<uint8_t> d_type, d_pair_mask, d_point_mask, order;
+    DevBuf<uint8_t> d_type, d_pair_mask, d_point_mask, order, d_owned;
     DevBuf<double> replay, xyz_all;
 
     // topology (device CSR by original index)
@@ -504,7 +504,7 @@ extern "C" int bd_destroy(bd_engine *h)
                     &h->energy_out, &h->dt_prev, &h->dt_last, &h->bend_energy, &h->replay, &h->xyz_all})
         b->release();
     for (auto *b : {&h->inter_partial, &h->dt_bits, &h->pair_count}) b->release();
-    for (auto *b : {&h->d_type, &h->d_pair_mask, &h->d_point_mask, &h->bend_ff, &h->order}) b->release();
+    for (auto *b : {&h->d_type, &h->d_pair_mask, &h->d_point_mask, &h->bend_ff, &h->order, &h->d_owned}) b->release();
     h->ctl.release();
     h->d_params.release();
     h->d_terms.release();
@@ -634,11 +634,22 @@ extern "C" int bd_set_owned(bd_engine *h, const uint8_t *owned)
 {
     NEED(h);
     if (h->replicas != 1) return fail("bd_set_owned: slab decomposition applies to a single system (1 replica)");
-    for (uint32_t i = 0; i < h->n; i++) {
-        h->h_point_mask[i] = (uint8_t) (h->h_point_mask[i] & ~GHOST_BIT);
-        if (owned && !owned[i]) h->h_point_mask[i] |= (uint8_t) GHOST_BIT;
-    }
-    if (upload_words(h)) return 1;
+    if (!owned) return bd_set_owned_device(h, nullptr);
+    if (h->d_owned.count < h->n) CK(h->d_owned.alloc(h->n));
+    CK(cudaMemcpyAsync(h->d_owned.p, owned, h->n, cudaMemcpyHostToDevice, h->stream));
+    int const rc = bd_set_owned_device(h, h->d_owned.p);
+    CK(cudaStreamSynchronize(h->stream));  // the caller's mask may go away
+    return rc;
+}
+
+extern "C" int bd_set_owned_device(bd_engine *h, const uint8_t *d_owned)
+{
+    NEED(h);
+    if (h->replicas != 1) return fail("bd_set_owned_device: slab decomposition applies to a single system (1 replica)");
+    if (h->n == 0) return 0;
+    k_set_ghost<<<blocks_for(h->n, 256), 256, 0, h->stream>>>(h->pos[0].p, h->pos[1].p, h->bpos.p, h->slot_of.p, d_owned, h->n);
+    h->launches++;
+    CK(cudaGetLastError());
     return request_rebuild(h);  // ghosts carry no Verlet row
 }
 

@@ -840,8 +840,23 @@ __global__ void k_set_words(bead4 *pos0, bead4 *pos1, bead4 *bpos, const uint32_
     uint32_t const g = blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= ntot) return;
     uint32_t const o = g % n;
-    uint64_t const w = pack_w(o, type[o], pair_mask[o], point_mask[o]);
     uint32_t const s = slot_of[g];
+    // ownership (the ghost bit) is device state: bd_set_owned / bd_set_owned_device
+    uint64_t const w = pack_w(o, type[o], pair_mask[o], point_mask[o]) | (pos0[s].w & ((uint64_t) GHOST_BIT << 48));
+    pos0[s].w = w;
+    pos1[s].w = w;
+    bpos[s].w = w;
+}
+
+/* ownership of every bead (replica 0): owned[original index] != 0, or everything when owned is null */
+__global__ void k_set_ghost(bead4 *pos0, bead4 *pos1, bead4 *bpos, const uint32_t *slot_of, const uint8_t *owned,
+                            uint32_t n)
+{
+    uint32_t const g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n) return;
+    uint32_t const s = slot_of[g];
+    uint64_t const bit = (uint64_t) GHOST_BIT << 48;
+    uint64_t const w = (pos0[s].w & ~bit) | ((owned && !owned[g]) ? bit : 0ull);
     pos0[s].w = w;
     pos1[s].w = w;
     bpos[s].w = w;

@@ -123,7 +123,8 @@ class EngineStore:
         self.system.scatter_positions_indexed(index.data_ptr(), len(index), xyz.data_ptr())
 
     def set_owned(self, owned: torch.Tensor):
-        self.system.set_owned(owned.to(torch.uint8).cpu().numpy())
+        self._owned = owned.to(torch.uint8).contiguous()  # kept alive until the kernel has read it
+        self.system.set_owned_device(self._owned.data_ptr())
 
     def step(self, first_step: int, timestep: float, temperature: float, seed: int):
         self.system.step(1, timestep, temperature, seed=seed, first_step=first_step)

@@ -51,7 +51,7 @@ def parse():
                          "split into x-slabs with a per-step NCCL halo exchange (strong scaling, BASELINE configs[4])")
     ap.add_argument("--chains", type=int, default=600, help="slab1kb: chains")
     ap.add_argument("--chain-len", type=int, default=10000, help="slab1kb: beads per chain")
-    ap.add_argument("--migrate-every", type=int, default=10, help="slab1kb: steps between ownership migrations")
+    ap.add_argument("--migrate-every", type=int, default=40, help="slab1kb: steps between ownership migrations")
     return ap.parse_args()
 
 
@@ -379,7 +379,7 @@ def run_slab(args):
         halo_bytes = 0
     else:
         lay = slab.SlabLayout.balanced(scen.positions[0][:, 0], world, period=scen.period[0])
-        sl = slab.SlabSystem(slab.EngineStore(sysm, dev), lay, rank, halo=3.0 * dcut, margin=dcut,
+        sl = slab.SlabSystem(slab.EngineStore(sysm, dev), lay, rank, halo=4.0 * dcut, margin=2.0 * dcut,
                              migrate_every=args.migrate_every, partners=slab.topology_partners(scen))
         ex = slab.DistExchange(dev)
         # The synthetic start (overlapping random walks) relaxes violently: beads would outrun the halo
@@ -421,7 +421,7 @@ def run_slab(args):
                        "timestep": dt, "temperature": kT, "noise": "philox4x32-10", "relax_steps": args.relax,
                        "parallelism": (f"{world} x-slabs, per-step halo exchange over NCCL send/recv, migration every "
                                        f"{args.migrate_every} steps" if world > 1 else "single GPU, no decomposition"),
-                       "halo_width": 3.0 * dcut, "l2": "working set > 126 MB L2 for >= 2 M beads"},
+                       "halo_width": 4.0 * dcut, "l2": "working set > 126 MB L2 for >= 2 M beads"},
             "pair_interactions_per_s": inter / (ms * 1e-3), "gpu_launches": int(launches),
             "halo_bytes_per_step": halo_bytes / K, "clocks": clocks,
         }

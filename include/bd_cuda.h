@@ -54,6 +54,8 @@ int bd_get_positions_device(bd_engine *h, double *d_xyz);
  * The indexed gather / scatter take DEVICE pointers (original bead indices, xyz[count][3]) and are
  * enqueued on the engine's stream, so a halo exchange needs no host synchronisation. */
 int bd_set_owned(bd_engine *h, const uint8_t *owned);
+/* the same with a DEVICE mask, enqueued on the engine's stream (no host copy of the mask) */
+int bd_set_owned_device(bd_engine *h, const uint8_t *d_owned);
 int bd_gather_positions_indexed(bd_engine *h, const uint32_t *d_index, int64_t count, double *d_xyz);
 int bd_scatter_positions_indexed(bd_engine *h, const uint32_t *d_index, int64_t count, const double *d_xyz);
 
