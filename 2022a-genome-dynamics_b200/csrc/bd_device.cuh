@@ -70,6 +70,8 @@ struct DWall {
     double center[3];
     double semi[3];
     double quad[3];  // 1 / (semi * semi), rounded exactly as ellipsoid_surface_forcefield.hpp:72-76 does
+    double range;    // beyond this distance from the surface every row of the table is exactly zero
+                     // (softcore diameters, cutoffs); 0 = some term has unbounded range.  Host-computed.
 };
 struct DPoint { int32_t enabled, nterms, term_off, has_targets; double source[3]; double pad; };
 

@@ -769,6 +769,22 @@ extern "C" int bd_add_bend_ff(bd_engine *h, const uint32_t *triples, const doubl
     return fail("bd_add_bend_ff: too many bending forcefields");
 }
 
+/* reach of a wall table: the largest distance at which any of its terms is non-zero, 0 if unbounded */
+static double table_range(const bd_term *table, int cells, int nterms)
+{
+    double range = 0;
+    for (int i = 0; i < cells * nterms; i++) {
+        const bd_term &t = table[i];
+        if (t.kind == BD_TERM_NONE || t.factor == 0.0) continue;
+        double reach = 0;
+        if (t.kind == BD_TERM_SOFTCORE) reach = t.length;  // zero force and energy for r >= diameter
+        if (t.cutoff > 0) reach = reach > 0 ? std::min(reach, t.cutoff) : t.cutoff;
+        if (!(reach > 0)) return 0;
+        range = std::max(range, reach);
+    }
+    return range;
+}
+
 extern "C" int bd_add_wall_ff(bd_engine *h, int32_t shape, int32_t direction, int32_t nterms,
                               const bd_term *table, const double center[3], const double semiaxes[3],
                               int32_t *ff_out)
@@ -785,6 +801,7 @@ extern "C" int bd_add_wall_ff(bd_engine *h, int32_t shape, int32_t direction, in
         w.term_off = h->wall[k].term_off;
         w.shape = shape;
         w.direction = direction;
+        w.range = table_range(table, h->hp.ntypes, nterms);
         for (int d = 0; d < 3; d++) {
             w.center[d] = center[d];
             w.semi[d] = semiaxes[d];
@@ -802,6 +819,7 @@ extern "C" int bd_update_wall_ff(bd_engine *h, int32_t ff, const bd_term *table,
     NEED(h);
     if (ff < 0 || ff >= BD_MAX_WALL_FF || !h->wall[ff].used) return fail("bd_update_wall_ff: bad forcefield id");
     if (table && store_table(h, h->wall[ff], h->wall[ff].nterms, table, h->wall[ff].cells)) return 1;
+    if (table) h->hp.wall[ff].range = table_range(table, h->wall[ff].cells, h->wall[ff].nterms);
     for (int d = 0; d < 3; d++) {
         h->hp.wall[ff].center[d] = center[d];
         h->hp.wall[ff].semi[d] = semiaxes[d];

@@ -433,19 +433,13 @@ __global__ void __launch_bounds__(ROWS_BLOCK) k_rows(NlistArrays A)
         uint32_t count = 0, run = 0, j = 0, e = 0;
         bool over = false;
         if (w_ghost(me.w)) nruns = 0;  // no force is evaluated for a ghost: it needs no row
-        while (true) {
-            if (j >= e) {
-                if (run == nruns) break;
-                uint2 const r = runs[run++][tid];
-                j = r.x;
-                e = r.y;
-            }
-            float4 const q = A.shadow[j];
+        // four candidates of a run are requested together: the walk is bound by the latency of these loads
+        auto consider = [&](uint32_t jj, const float4 &q) {
             float const d2 = periodic ? shadow_dist2<BD_BOX_PERIODIC>(ms, q, scale)
                                       : shadow_dist2<BD_BOX_OPEN>(ms, q, scale);
-            if (d2 <= filter2 && j != s) {
+            if (d2 <= filter2 && jj != s) {
                 if (count < A.cap) {
-                    stage[count % ROW_PAD][tid] = j;
+                    stage[count % ROW_PAD][tid] = jj;
                     count++;
                     if (count % ROW_PAD == 0) {
                         *dst = make_uint4(stage[0][tid], stage[1][tid], stage[2][tid], stage[3][tid]);
@@ -455,7 +449,26 @@ __global__ void __launch_bounds__(ROWS_BLOCK) k_rows(NlistArrays A)
                     over = true;
                 }
             }
-            j++;
+        };
+        while (true) {
+            if (j >= e) {
+                if (run == nruns) break;
+                uint2 const r = runs[run++][tid];
+                j = r.x;
+                e = r.y;
+            }
+            if (e - j >= 4) {
+                float4 const q0 = A.shadow[j], q1 = A.shadow[j + 1], q2 = A.shadow[j + 2], q3 = A.shadow[j + 3];
+                consider(j, q0);
+                consider(j + 1, q1);
+                consider(j + 2, q2);
+                consider(j + 3, q3);
+                j += 4;
+            } else {
+                float4 const q = A.shadow[j];
+                consider(j, q);
+                j++;
+            }
         }
         A.nnbr[s] = count;
         // the last group is padded with the sentinel slot: the step kernel reads whole groups

@@ -282,14 +282,22 @@ __device__ __forceinline__ void bonded_forces(const StepArrays &A, const DParams
     // to slots at the last rebuild (bd_nlist.cuh: k_balance)
     {
         const BondRow *brows = reinterpret_cast<const BondRow *>(dyn_smem + A.ntypes2 * sizeof(PairRow));
+        // software pipeline: the next bond's row entry and partner record are requested while this
+        // bond is evaluated (the loop was bound by these two dependent loads)
         const uint2 *col = A.bondrow + pos;
-        for (uint32_t k = 0; k < A.bond_deg; k++, col += A.pstride) {
-            uint2 const adj = *col;
+        uint2 adj_next = A.bond_deg ? *col : make_uint2(0xffffffffu, 0u);
+        bead4 o_next = me;
+        if (adj_next.x != 0xffffffffu) o_next = load_bead(A.pos + adj_next.x);
+        for (uint32_t k = 0; k < A.bond_deg; k++) {
+            uint2 const adj = adj_next;
             if (adj.x == 0xffffffffu) break;
+            bead4 const o = o_next;
+            col += A.pstride;
+            adj_next = k + 1 < A.bond_deg ? *col : make_uint2(0xffffffffu, 0u);
+            if (adj_next.x != 0xffffffffu) o_next = load_bead(A.pos + adj_next.x);
             int const f = adj.y & 0xff;
             const DBond &bf = P.bond[f];
             if (!ff_on(sel, BD_FF_BOND, f, bf.enabled)) continue;
-            bead4 const o = load_bead(A.pos + adj.x);
             uint32_t const tj = w_type(o.w);
             bool const second = (adj.y >> 8) & 1u;
             // the force on this bead is scalar * (x_me - x_partner) whichever end it is; only the
@@ -372,6 +380,12 @@ __device__ __forceinline__ void wall_force(const StepArrays &A, const DWall &wf,
         if (r2 == 0.0) return;
         bool const inside = r2 < radius * radius;
         if (inside ? wf.direction != BD_WALL_INWARD : wf.direction != BD_WALL_OUTWARD) return;
+        if (wf.range > 0.0) {
+            // farther from the surface than any term reaches: force and statistics are exactly zero
+            double const reach = wf.range * (1.0 + 1e-6);
+            double const lim = inside ? radius - reach : radius + reach;
+            if (inside ? (lim > 0.0 && r2 < lim * lim) : r2 > lim * lim) return;
+        }
         double const r1 = sqrt(r2);
         double const scale = radius / r1;
         double const sx = rx - scale * rx, sy = ry - scale * ry, sz = rz - scale * rz;
@@ -392,6 +406,9 @@ __device__ __forceinline__ void wall_force(const StepArrays &A, const DWall &wf,
         double const implicit = dx * rx + dy * ry + dz * rz - 1.0;
         bool const inside = implicit < 0.0;
         if (inside ? wf.direction != BD_WALL_INWARD : wf.direction != BD_WALL_OUTWARD) return;
+        // delta^2 = implicit^2 / (4 d2): farther from the surface than any term reaches (with a margin for
+        // the rounding of this estimate), force and statistics are exactly zero
+        if (wf.range > 0.0 && implicit * implicit > 4.0 * d2 * wf.range * wf.range * (1.0 + 1e-6)) return;
         double const scale = implicit / (2.0 * d2);
         double const ex = scale * dx, ey = scale * dy, ez = scale * dz;  // delta
         double const e2 = ex * ex + ey * ey + ez * ez;
