@@ -145,6 +145,7 @@ def _api(prefix: str):
         "get_wall_stats": [vp, i32, i32, _dbl_p],
         "add_point_ff": [vp, i32, vp, _dbl_p, _u8_p, _P(i32)],
         "set_ff_enabled": [vp, i32, i32, i32],
+        "set_external_forces": [vp, i32, _dbl_p],
         "compute_forces": [vp, i32, i32, i32, _dbl_p],
         "compute_energy": [vp, i32, i32, i32, _dbl_p],
         "step": [vp, _P(StepConfig)],
@@ -384,6 +385,15 @@ class System:
         self.b.call("add_point_ff", self.h, tab.shape[1], tab.ctypes.data, _dp(s),
                     m.ctypes.data_as(_u8_p) if m is not None else None, C.byref(ff))
         return ff.value
+
+    def set_external_forces(self, xyz, replica=0):
+        """force array of host-evaluated user forcefields, added to every whole-system evaluation; None clears"""
+        if xyz is None:
+            self.b.call("set_external_forces", self.h, replica, None)
+            return
+        f = np.ascontiguousarray(xyz, dtype=np.float64)
+        assert f.shape == (self.n, 3)
+        self.b.call("set_external_forces", self.h, replica, _dp(f))
 
     def set_ff_enabled(self, ff_class, ff, enabled):
         self.b.call("set_ff_enabled", self.h, ff_class, ff, int(bool(enabled)))

@@ -101,7 +101,8 @@ struct bd_engine {
     DevBuf<double> force, wprev, xyz_stage, wall_partial, wall_out, energy_partial, energy_out, dt_prev, dt_last;
     DevBuf<unsigned long long> inter_partial, dt_bits, pair_count;
     DevBuf<uint8_t> d_type, d_pair_mask, d_point_mask, order, d_owned;
-    DevBuf<double> replay, xyz_all;
+    DevBuf<double> replay, xyz_all, ext;
+    bool ext_on = false;
 
     // topology (device CSR by original index)
     DevBuf<uint32_t> bond_start, bend_start, bend_adj, triples;
@@ -501,7 +502,7 @@ extern "C" int bd_destroy(bd_engine *h)
                     &h->block_sum, &h->plen, &h->nnbr, &h->bond_start, &h->bend_start, &h->bend_adj, &h->triples})
         b->release();
     for (auto *b : {&h->force, &h->wprev, &h->xyz_stage, &h->wall_partial, &h->wall_out, &h->energy_partial,
-                    &h->energy_out, &h->dt_prev, &h->dt_last, &h->bend_energy, &h->replay, &h->xyz_all})
+                    &h->energy_out, &h->dt_prev, &h->dt_last, &h->bend_energy, &h->replay, &h->xyz_all, &h->ext})
         b->release();
     for (auto *b : {&h->inter_partial, &h->dt_bits, &h->pair_count}) b->release();
     for (auto *b : {&h->d_type, &h->d_pair_mask, &h->d_point_mask, &h->bend_ff, &h->order, &h->d_owned}) b->release();
@@ -626,6 +627,27 @@ extern "C" int bd_get_positions_device(bd_engine *h, double *d_xyz)
     k_gather_positions<<<blocks_for(h->ntot, 256), 256, 0, h->stream>>>(h->pos[h->cur].p, h->slot_of.p, d_xyz, 0, h->ntot);
     h->launches++;
     CK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int bd_set_external_forces(bd_engine *h, int32_t replica, const double *xyz)
+{
+    NEED(h);
+    if (replica < 0 || (uint32_t) replica >= h->replicas) return fail("bd_set_external_forces: bad replica");
+    size_t const per = 3 * (size_t) h->n;
+    if (!xyz) {
+        // cleared for this replica; the array stays in use while any replica may still hold forces
+        if (h->ext_on) CK(cudaMemsetAsync(h->ext.p + (size_t) replica * per, 0, per * sizeof(double), h->stream));
+        if (h->replicas == 1) h->ext_on = false;
+        return 0;
+    }
+    if (h->ext.count < per * h->replicas) {
+        CK(h->ext.alloc(per * h->replicas));
+        CK(cudaMemsetAsync(h->ext.p, 0, per * h->replicas * sizeof(double), h->stream));
+    }
+    CK(cudaMemcpyAsync(h->ext.p + (size_t) replica * per, xyz, per * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));  // the caller's array may change right away
+    h->ext_on = true;
     return 0;
 }
 
@@ -940,6 +962,7 @@ static StepArrays step_arrays(bd_engine *h)
     A.inter_partial = h->inter_partial.p;
     A.force = h->force.p;
     A.wprev = h->wprev.p;
+    A.ext = h->ext_on ? h->ext.p : nullptr;
     A.dt_bits = h->dt_bits.p;
     A.dt_prev = h->dt_prev.p;
     A.pair_rows = h->d_pair_rows.p;

@@ -54,6 +54,7 @@ struct StepArrays {
     unsigned long long *inter_partial;  // [replicas*chunks*warps] interacting (bead, neighbour) entries so far
     double *force;                // [Ntot][3] by slot (two-pass path and compute_forces)
     double *wprev;                // [Ntot][3] by original global index (replay mode)
+    const double *ext;            // [Ntot][3] by original global index: host-evaluated user forcefields, or null
     unsigned long long *dt_bits;  // [replicas] adaptive: min timestep of the current step
     const double *dt_prev;        // [replicas] adaptive: timestep of the previous step
     const struct PairRow *pair_rows;    // compiled table of the specialised pair program
@@ -472,6 +473,10 @@ __device__ __forceinline__ d3 block_forces(const StepArrays &A, StepShared &sh, 
     if (live) {
         pair_forces<BOX, PROG>(A, sh, sel, s, pos, me, F, interactions);
         bonded_forces(A, P, sel, replica, pos, me, F);
+        if (A.ext && sel.ff_class == BD_FF_ALL) {
+            const double *e = A.ext + 3 * ((size_t) replica * A.n + w_orig(me.w));
+            F.x += e[0]; F.y += e[1]; F.z += e[2];
+        }
     }
     bool any_wall = false;
 #pragma unroll 1

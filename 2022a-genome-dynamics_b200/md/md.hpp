@@ -24,6 +24,10 @@
  *   MD/misc/box.hpp:18-81, misc/math.hpp:18-44, misc/neighbor_searcher.hpp:23-131
  *   MD/simulation/brownian_dynamics.hpp:24-73
  *
+ * Driver-defined md::forcefield subclasses (3-sim-1kb's glue_forcefield / loop_forcefield) keep working:
+ * they are evaluated on the host on positions fetched from the device and enter the engine's force
+ * sum through bd_set_external_forces -- correct, but each step then crosses PCIe twice.
+ *
  * Not offered (no driver uses them): Langevin / Newtonian integrators, Lennard-Jones family,
  * plane surfaces, composite / brute-force force fields, xy_periodic_box as a unit cell.
  *
@@ -872,6 +876,25 @@ namespace md
                     check(MD_B200_CALL(set_positions)(h_, 0, &sys_.b200_host_positions()->x), "set_positions");
                     device_valid_ = true;
                 }
+                host_forces();
+            }
+
+            bool has_host_forcefields() const
+            {
+                for (auto const& a : attached_)
+                    if (!a.dev) return true;
+                return false;
+            }
+
+            // energy of the driver-defined force fields, evaluated on the host
+            md::scalar host_energy()
+            {
+                if (!has_host_forcefields()) return 0;
+                fetch_positions();
+                md::scalar e = 0;
+                for (auto const& a : attached_)
+                    if (!a.dev) e += a.ff->compute_energy(sys_);
+                return e;
             }
 
             void fetch_positions()
@@ -913,6 +936,23 @@ namespace md
             int device_ordinal() const { return device_; }
 
         private:
+            // driver-defined force fields: evaluate them on the current positions and hand the sum to
+            // the engine, which adds it to every whole-system force evaluation
+            void host_forces()
+            {
+                if (!has_host_forcefields()) {
+                    if (external_set_) check(MD_B200_CALL(set_external_forces)(h_, 0, nullptr), "set_external_forces");
+                    external_set_ = false;
+                    return;
+                }
+                fetch_positions();
+                external_.assign(sys_.particle_count(), md::vector{});
+                for (auto const& a : attached_)
+                    if (!a.dev) a.ff->compute_force(sys_, md::array_view<md::vector>(external_.data(), external_.size()));
+                check(MD_B200_CALL(set_external_forces)(h_, 0, &external_.data()->x), "set_external_forces");
+                external_set_ = true;
+            }
+
             struct attachment
             {
                 md::forcefield* ff;
@@ -979,10 +1019,12 @@ namespace md
                 attached_.clear();
                 for (auto const& ff : sys_.b200_forcefields()) {
                     auto* dev = dynamic_cast<device_forcefield*>(ff.get());
-                    if (!dev)
-                        throw std::runtime_error(
-                            "md (B200 engine): a user-defined md::forcefield subclass cannot be evaluated on the device; "
-                            "express it with the make_*_forcefield factories");
+                    if (!dev) {
+                        // a driver-defined md::forcefield subclass: evaluated by the driver on the host,
+                        // its force enters the engine through set_external_forces (host_forces())
+                        attached_.push_back({ff.get(), nullptr, 0});
+                        continue;
+                    }
                     dev->b200_id = -1;
                     dev->b200_attach(*this, sys_);
                     attached_.push_back({ff.get(), dev, dev->b200_structure()});
@@ -997,6 +1039,8 @@ namespace md
             int device_ = 0;
             class_map classes_;
             std::vector<attachment> attached_;
+            std::vector<md::vector> external_;
+            bool external_set_ = false;
             bool host_valid_ = true;
             bool device_valid_ = false;
             bool box_set_ = false;
@@ -1585,7 +1629,7 @@ namespace md
         b.sync(true);
         double e = 0;
         b200::check(MD_B200_CALL(compute_energy)(b.handle(), 0, BD_FF_ALL, 0, &e), "compute_energy");
-        return e;
+        return e + b.host_energy();
     }
 
     inline void system::compute_force(md::array_view<md::vector> forces)
@@ -1657,7 +1701,8 @@ namespace md
     // The callback is invoked after every step with the 1-based step number, exactly as in the
     // reference; between callbacks the potentials are re-evaluated so that whatever the callback
     // changed (scales, walls, cutoffs) acts on the next step.  Without a callback the whole run is
-    // one engine call.  Noise: counter-based Philox keyed by (seed, step, particle) on the device
+    // one engine call -- unless the system holds driver-defined md::forcefield subclasses, whose
+    // forces are evaluated by the driver on the host before every step.  Noise: counter-based Philox keyed by (seed, step, particle) on the device
     // (the reference draws sfc64 + ziggurat normals on the host: same distribution, different stream).
     inline void simulate_brownian_dynamics(md::system& system, md::brownian_dynamics_config config)
     {
@@ -1671,7 +1716,7 @@ namespace md
         cfg.spacestep = config.spacestep;
         cfg.seed = config.seed;
         cfg.replay_normals = nullptr;
-        if (!config.callback) {
+        if (!config.callback && !b.has_host_forcefields()) {
             cfg.steps = config.steps;
             cfg.first_step = 1;
             b200::check(MD_B200_CALL(step)(b.handle(), &cfg), "step");
@@ -1686,7 +1731,7 @@ namespace md
             b200::check(MD_B200_CALL(step)(b.handle(), &cfg), "step");
             b.device_advanced();
             b.collect();
-            config.callback(s);
+            if (config.callback) config.callback(s);
         }
     }
 

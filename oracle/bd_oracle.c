@@ -911,6 +911,7 @@ struct orc_system {
     point_ff point[BD_MAX_POINT_FF];
     /* brownian_simulator state (MD/simulation/detail/brownian_simulator.hpp:79-84) */
     v3 *forces, *weiners;
+    v3 *external; /* host-evaluated user forcefields (set_external_forces), or NULL */
     sfc64 rng;
     double last_dt;
     bd_counters counters;
@@ -968,6 +969,7 @@ int orc_destroy(orc_system *s)
     free(s->pos);
     free(s->forces);
     free(s->weiners);
+    free(s->external);
     free(s);
     return 0;
 }
@@ -1493,6 +1495,27 @@ static int eval_all(orc_system *s, int ff_class, int ff, v3 *forces, double *ene
     if (ff_class != BD_FF_ALL && !hit) {
         return fail("oracle: bad forcefield class / id");
     }
+    /* a user forcefield is one more member of the sum forcefield */
+    if (ff_class == BD_FF_ALL && forces && s->external) {
+        for (size_t i = 0; i < s->n; i++) {
+            forces[i] = v3_add(forces[i], s->external[i]);
+        }
+    }
+    return 0;
+}
+
+int orc_set_external_forces(orc_system *s, int32_t replica, const double *xyz)
+{
+    (void) replica;
+    if (!xyz) {
+        free(s->external);
+        s->external = NULL;
+        return 0;
+    }
+    if (!s->external) {
+        s->external = malloc((s->n ? s->n : 1) * sizeof(v3));
+    }
+    memcpy(s->external, xyz, s->n * sizeof(v3));
     return 0;
 }
 

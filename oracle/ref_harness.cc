@@ -257,9 +257,21 @@ namespace
     };
 }
 
+// a driver-defined forcefield: adds a force array the caller evaluated (set_external_forces)
+struct external_forcefield : md::forcefield
+{
+    std::vector<md::vector> forces;
+    md::scalar compute_energy(md::system const&) override { return 0; }
+    void compute_force(md::system const&, md::array_view<md::vector> out) override
+    {
+        for (std::size_t i = 0; i < forces.size(); i++) out[i] += forces[i];
+    }
+};
+
 struct ref_system
 {
     md::system system;
+    std::shared_ptr<external_forcefield> external;
     std::vector<std::uint8_t> type;
     int ntypes = 1;
     int box_kind = BD_BOX_OPEN;
@@ -298,6 +310,7 @@ struct ref_system
         for (auto& s : bend) add(s.used && s.enabled, s.ff);
         for (auto& s : wall) add(s.used && s.enabled, s.ff);
         for (auto& s : point) add(s.used && s.enabled, s.ff);
+        add(external != nullptr, external);
     }
 };
 
@@ -658,6 +671,22 @@ static md::forcefield* pick(ref_system* s, std::int32_t ff_class, std::int32_t f
     case BD_FF_POINT: return s->point[ff].ff.get();
     default: return nullptr;
     }
+}
+
+int ref_set_external_forces(ref_system* s, std::int32_t, double const* xyz)
+{
+    REF_TRY
+    if (!xyz) {
+        s->external.reset();
+    } else {
+        if (!s->external) s->external = std::make_shared<external_forcefield>();
+        std::size_t const n = s->system.particle_count();
+        s->external->forces.resize(n);
+        for (std::size_t i = 0; i < n; i++) s->external->forces[i] = {xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]};
+    }
+    s->reregister();
+    return 0;
+    REF_CATCH
 }
 
 int ref_compute_forces(ref_system* s, std::int32_t, std::int32_t ff_class, std::int32_t ff,

@@ -13,6 +13,7 @@
 //               simulation_driver_interphase.cc:9-88 (per-step callback moving scales and walls)
 //   blend:      4-sim-ab/box/src/simulation/simulation_driver.cc, 4-sim-ab/sphere/src/simulation_driver.cc:95-233
 //   spindle:    5-sim-genome/src/simulation_spindle/simulation_driver.cc:90-175 (point sources, bending)
+//   chromatin:  3-sim-1kb/src/simulation/simulation.cpp:100-175 + its own glue / loop md::forcefield subclasses
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
@@ -393,6 +394,136 @@ namespace
     }
 }
 
+// ---- 3-sim-1kb in small: driver-defined force fields over dynamic pair lists ------------------------
+// (3-sim-1kb/src/simulation/forces/glue_forcefield.cpp:3-43, loop_forcefield.cpp:8-50,
+//  simulation.cpp:100-175: periodic softcore repulsion + attraction, spring bonds, per-monomer bending)
+namespace
+{
+    struct pair_list
+    {
+        std::vector<std::pair<md::index, md::index>> pairs;
+    };
+
+    class glue_forcefield : public md::forcefield
+    {
+    public:
+        glue_forcefield(std::shared_ptr<pair_list> list, md::periodic_box const& box, md::scalar energy, md::scalar cutoff)
+            : _list{list}, _box{box}, _potential{.energy = -energy, .diameter = cutoff}
+        {
+        }
+
+        md::scalar compute_energy(md::system const& system) override
+        {
+            auto const positions = system.view_positions();
+            md::scalar total = 0;
+            for (auto const& pair : _list->pairs)
+                total += _potential.evaluate_energy(_box.shortest_displacement(positions[pair.first], positions[pair.second]));
+            return total;
+        }
+
+        void compute_force(md::system const& system, md::array_view<md::vector> forces) override
+        {
+            auto const positions = system.view_positions();
+            for (auto const& pair : _list->pairs) {
+                auto const f = _potential.evaluate_force(_box.shortest_displacement(positions[pair.first], positions[pair.second]));
+                forces[pair.first] += f;
+                forces[pair.second] -= f;
+            }
+        }
+
+    private:
+        std::shared_ptr<pair_list> _list;
+        md::periodic_box _box;
+        md::softcore_potential<8, 3> _potential;
+    };
+
+    class loop_forcefield : public md::forcefield
+    {
+    public:
+        loop_forcefield(std::shared_ptr<pair_list> list, md::scalar stiffness, md::scalar length)
+            : _list{list}, _potential{.spring_constant = stiffness, .equilibrium_distance = length}
+        {
+        }
+
+        md::scalar compute_energy(md::system const& system) override
+        {
+            auto const positions = system.view_positions();
+            md::scalar total = 0;
+            for (auto const& pair : _list->pairs) total += _potential.evaluate_energy(positions[pair.first] - positions[pair.second]);
+            return total;
+        }
+
+        void compute_force(md::system const& system, md::array_view<md::vector> forces) override
+        {
+            auto const positions = system.view_positions();
+            for (auto const& pair : _list->pairs) {
+                auto const f = _potential.evaluate_force(positions[pair.first] - positions[pair.second]);
+                forces[pair.first] += f;
+                forces[pair.second] -= f;
+            }
+        }
+
+    private:
+        std::shared_ptr<pair_list> _list;
+        md::spring_potential _potential;
+    };
+
+    void chromatin()
+    {
+        md::system system;
+        system.require(monomer_data_attribute);
+        double const box_size = 2.4;
+        std::vector<std::pair<md::index, md::index>> chains;
+        for (int c = 0; c < 4; c++) {
+            md::index const start = system.particle_count();
+            for (int i = 0; i < 60; i++) {
+                auto part = system.add_particle();
+                part.mobility = 1;
+                part.view(monomer_data_attribute) = {.bending_energy = (i / 20) % 2 ? 2.0 : 1.0};
+            }
+            chains.push_back({start, system.particle_count()});
+        }
+        place_chains(system, chains, 0.28, 1.1, 41);
+
+        md::softcore_potential<2, 3> const repulsive{.energy = 3, .diameter = 0.30};
+        md::softcore_potential<8, 3> const attractive{.energy = 0.3 * -1, .diameter = 0.45};
+        md::periodic_box const box{.x_period = box_size, .y_period = box_size, .z_period = box_size};
+        system.add_forcefield(
+            md::make_neighbor_pairwise_forcefield<md::periodic_box>(repulsive + attractive)
+            .set_unit_cell(box)
+            .set_neighbor_distance(0.45));
+        auto bonds = system.add_forcefield(
+            md::make_bonded_pairwise_forcefield(md::spring_potential{.spring_constant = 100, .equilibrium_distance = 0.3}));
+        auto bends = system.add_forcefield(md::make_bonded_triplewise_forcefield(
+            [](md::system const& sys, md::index, md::index i, md::index) {
+                return md::cosine_bending_potential{sys.view(monomer_data_attribute)[i].bending_energy};
+            }));
+        for (auto const& chain : chains) {
+            bonds->add_bonded_range(chain.first, chain.second);
+            bends->add_bonded_range(chain.first, chain.second);
+        }
+        auto loops = std::make_shared<pair_list>();
+        auto glues = std::make_shared<pair_list>();
+        loops->pairs = {{5, 40}, {70, 110}, {130, 170}};
+        glues->pairs = {{10, 14}, {65, 71}, {200, 204}};
+        system.add_forcefield(loop_forcefield{loops, 50, 0.3});
+        system.add_forcefield(glue_forcefield{glues, box, 2.0, 0.45});
+
+        std::vector<md::vector> forces(system.particle_count());
+        system.compute_force(forces);
+        print_vectors("chromatin.force", forces, 6);
+        std::printf("chromatin.energy %.17g\n", system.compute_potential_energy());
+        // the kinetic part of the driver: the pair lists change while the simulation runs
+        md::simulate_brownian_dynamics(system, {.temperature = 0, .timestep = 1e-5, .steps = 60, .callback = [&](md::step step) {
+            if (step == 20) loops->pairs.push_back({185, 230});
+            if (step == 40) glues->pairs.erase(glues->pairs.begin());
+        }});
+        md::simulate_brownian_dynamics(system, {.temperature = 0, .timestep = 1e-5, .steps = 20});
+        print_points("chromatin.pos", system.view_positions(), 5);
+        std::printf("chromatin.energy_end %.17g\n", system.compute_potential_energy());
+    }
+}
+
 int main()
 {
     {
@@ -411,5 +542,6 @@ int main()
         sim.run("blend_sphere");
     }
     spindle();
+    chromatin();
     return 0;
 }

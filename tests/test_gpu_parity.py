@@ -150,6 +150,25 @@ def test_replayed_trajectory_matches_oracle(engine, oracle, name):
     assert np.abs(se.get_positions() - so.get_positions()).max() <= TRAJ_TOL
 
 
+def test_external_forces_enter_every_whole_system_evaluation(engine, oracle):
+    """bd_set_external_forces: host-evaluated user forcefields (3-sim-1kb glue / loop)."""
+    scen = SMALL["chromatin_1kb"]()
+    se, _ = build(engine, scen)
+    so, _ = build(oracle, scen)
+    ext = np.random.default_rng(2).normal(size=(scen.n, 3)) * 5.0
+    for s in (se, so):
+        s.set_external_forces(ext)
+    assert rel_force_error(se.compute_forces(), so.compute_forces()) <= 1e-12
+    assert rel_force_error(se.compute_forces(ff_class=bd.FF_PAIR, ff=0), so.compute_forces(ff_class=bd.FF_PAIR, ff=0)) <= 1e-12
+    z = oracle.normals(3, 12 * scen.n * 3)
+    for s in (se, so):
+        s.step(12, scen.timestep, scen.temperature, replay_normals=z)
+    assert np.abs(se.get_positions() - so.get_positions()).max() <= TRAJ_TOL
+    for s in (se, so):
+        s.set_external_forces(None)
+    assert rel_force_error(se.compute_forces(), so.compute_forces()) <= 1e-12
+
+
 @pytest.mark.parametrize("name", ["ab_box", "ab_sphere"])
 def test_long_replay_rebuilds_with_the_oracle(engine, oracle, name):
     """200 steps at a large timestep: the Verlet list is rebuilt many times.  In a periodic box the

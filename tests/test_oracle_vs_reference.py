@@ -116,3 +116,26 @@ def test_table_potential_equals_expression_templates(reference):
     fn = reference.lib.ref_selfcheck_expression_templates
     fn.restype = ctypes.c_double
     assert fn() == 0.0
+
+
+def test_external_forces_are_one_more_forcefield(oracle, reference):
+    """set_external_forces: a host-evaluated md::forcefield subclass (3-sim-1kb's glue / loop force
+    fields) as one more member of the reference's sum forcefield."""
+    scen = SMALL["chromatin_1kb"]()
+    so, _ = build(oracle, scen)
+    sr, _ = build(reference, scen)
+    ext = np.random.default_rng(2).normal(size=(scen.n, 3)) * 5.0
+    base = sr.compute_forces()
+    for s in (so, sr):
+        s.set_external_forces(ext)
+    assert np.array_equal(sr.compute_forces(), base + ext)
+    assert np.array_equal(so.compute_forces(), sr.compute_forces())
+    # only the whole-system evaluation carries it
+    assert np.array_equal(so.compute_forces(ff_class=1, ff=0), sr.compute_forces(ff_class=1, ff=0))
+    z = reference.normals(3, 8 * scen.n * 3)
+    so.step(8, scen.timestep, scen.temperature, replay_normals=z)
+    sr.step(8, scen.timestep, scen.temperature, seed=3)
+    assert np.array_equal(so.get_positions(), sr.get_positions())
+    for s in (so, sr):
+        s.set_external_forces(None)
+    assert np.array_equal(so.compute_forces(), sr.compute_forces())
