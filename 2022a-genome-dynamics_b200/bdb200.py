@@ -171,6 +171,9 @@ ENGINE_ONLY = {
     "set_owned_device": [C.c_void_p, C.c_void_p],
     "gather_positions_indexed": [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p],
     "scatter_positions_indexed": [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p],
+    "contact_update": [C.c_void_p, C.c_int32, C.c_double],
+    "contact_accumulate": [C.c_void_p, C.c_int32, C.POINTER(C.c_uint32), C.c_int64, C.POINTER(C.c_int64)],
+    "contact_clear": [C.c_void_p, C.c_int32],
 }
 
 
@@ -494,6 +497,23 @@ class System:
 
     def scatter_positions_indexed(self, d_index: int, count: int, d_xyz: int):
         self.b.call("scatter_positions_indexed", self.h, C.c_void_p(d_index), int(count), C.c_void_p(d_xyz))
+
+    # contact map on the device (contact_map.cc:25-91 of the interphase driver)
+    def contact_update(self, distance: float, replica: int = 0):
+        self.b.call("contact_update", self.h, int(replica), float(distance))
+
+    def contact_accumulate(self, replica: int = 0) -> np.ndarray:
+        """[m, 3] uint32 rows (i, j, count), i < j, sorted by (i, j)."""
+        count = C.c_int64(0)
+        self.b.call("contact_accumulate", self.h, int(replica), None, 0, C.byref(count))
+        out = np.empty((max(count.value, 0), 3), dtype=np.uint32)
+        if count.value:
+            self.b.call("contact_accumulate", self.h, int(replica), out.ctypes.data_as(C.POINTER(C.c_uint32)),
+                        int(count.value), C.byref(count))
+        return out
+
+    def contact_clear(self, replica: int = 0):
+        self.b.call("contact_clear", self.h, int(replica))
 
     def get_launch_count(self) -> int:
         v = C.c_int64(0)

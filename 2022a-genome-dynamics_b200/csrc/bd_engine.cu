@@ -13,6 +13,7 @@
 #include <cstring>
 #include <string>
 #include <vector>
+#include <cub/cub.cuh>
 
 #include "../../include/bd_cuda.h"
 #include "bd_device.cuh"
@@ -103,6 +104,16 @@ struct bd_engine {
     DevBuf<uint8_t> d_type, d_pair_mask, d_point_mask, order, d_owned;
     DevBuf<double> replay, xyz_all, ext;
     bool ext_on = false;
+
+    // contact map accumulated on the device (bd_contact_*)
+    bd_engine *contact_search = nullptr;  // a second engine used as the neighbour searcher at the contact distance
+    double contact_distance = 0;
+    DevBuf<unsigned long long> contact_keys[2], contact_new;  // (i << 32 | j), sorted unique; double-buffered
+    DevBuf<uint32_t> contact_counts[2], contact_ones, contact_pairs;
+    DevBuf<unsigned char> contact_temp;
+    DevBuf<unsigned long long> contact_runs;
+    int contact_cur = 0;
+    size_t contact_size = 0;
 
     // topology (device CSR by original index)
     DevBuf<uint32_t> bond_start, bend_start, bend_adj, triples;
@@ -514,6 +525,16 @@ extern "C" int bd_destroy(bd_engine *h)
     h->nbr4.release();
     h->bondrow.release();
     h->d_bond_rows.release();
+    if (h->contact_search) bd_destroy(h->contact_search);
+    for (int k = 0; k < 2; k++) {
+        h->contact_keys[k].release();
+        h->contact_counts[k].release();
+    }
+    h->contact_new.release();
+    h->contact_ones.release();
+    h->contact_pairs.release();
+    h->contact_temp.release();
+    h->contact_runs.release();
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     delete h;
     return 0;
@@ -1426,4 +1447,160 @@ extern "C" int bd_get_launch_count(bd_engine *h, int64_t *out)
 int bd_internal_fail(const char *msg)
 {
     return fail(msg);
+}
+
+// ---- contact map on the device -------------------------------------------------------------------
+//
+// Replaces contact_map::update / accumulate / clear of the interphase driver
+// (5-sim-genome/src/simulation_interphase/contact_map.cc:25-91), which downloads all positions every
+// contactmap_update_interval steps, runs md::neighbor_searcher<open_box> with the default hash modulus
+// on the host and adds the pairs into an Eigen sparse matrix.  Here the pairs within the contact
+// distance are found by a second engine used as the searcher (list radius = contact distance, fp64
+// test, the reference's pair set), turned into 64-bit keys (i << 32 | j) and merged into a sorted
+// (key, count) table by one radix sort + one reduce-by-key (CUB).  Positions never leave the device;
+// only bd_contact_accumulate copies the (i, j, count) triplets out.
+
+__global__ void k_contact_keys(const uint32_t *pairs, unsigned long long count, unsigned long long *keys, uint32_t *ones)
+{
+    unsigned long long const k = (unsigned long long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= count) return;
+    uint32_t const a = pairs[2 * k], b = pairs[2 * k + 1];
+    uint32_t const i = a < b ? a : b, j = a < b ? b : a;
+    keys[k] = ((unsigned long long) i << 32) | j;
+    ones[k] = 1u;
+}
+
+extern "C" int bd_contact_clear(bd_engine *h, int32_t replica)
+{
+    NEED(h);
+    if (replica != 0 && (uint32_t) replica >= h->replicas) return fail("bd_contact_clear: bad replica");
+    h->contact_size = 0;
+    return 0;
+}
+
+extern "C" int bd_contact_update(bd_engine *h, int32_t replica, double distance)
+{
+    NEED(h);
+    if (replica < 0 || (uint32_t) replica >= h->replicas) return fail("bd_contact_update: bad replica");
+    if (!(distance > 0)) return fail("bd_contact_update: the contact distance must be positive");
+    if (h->n < 2) return 0;
+    cudaStream_t const st = h->stream;
+    bd_engine *q = h->contact_search;
+    if (!q) {
+        if (bd_create(h->n, 1, h->device, &q)) return 1;
+        h->contact_search = q;
+        double const unit[3] = {1, 1, 1};
+        bd_term none;
+        std::memset(&none, 0, sizeof none);
+        int32_t ff = -1;
+        // open box whatever the simulation's unit cell is (contact_map.cc:64); rows hold exactly the contacts
+        if (bd_set_box(q, BD_BOX_OPEN, unit) || bd_set_option(q, "verlet_factor", 1.0)
+            || bd_add_pair_ff(q, 1, &none, distance, nullptr, &ff))
+            return 1;
+        h->contact_distance = distance;
+    } else if (distance != h->contact_distance) {
+        bd_term none;
+        std::memset(&none, 0, sizeof none);
+        if (bd_update_pair_ff(q, 0, &none, distance)) return 1;
+        h->contact_distance = distance;
+    }
+    if (bd_set_stream(q, st)) return 1;
+    // positions of the replica in original order, device to device
+    k_gather_positions<<<blocks_for(h->n, 256), 256, 0, st>>>(h->pos[h->cur].p, h->slot_of.p, h->xyz_stage.p,
+                                                              (uint32_t) replica * h->n, h->n);
+    h->launches++;
+    CK(cudaGetLastError());
+    if (bd_set_positions_device(q, h->xyz_stage.p)) return 1;
+    if (prepare_list(q)) return 1;
+
+    // the contacts of this configuration
+    DControl c;
+    CK(cudaMemcpy(&c, q->ctl.p, sizeof c, cudaMemcpyDeviceToHost));
+    size_t const cap = (size_t) (c.listed_entries / 2) + 1;  // the rows are a superset by the shadow bound
+    if (h->contact_pairs.count < 2 * cap) CK(h->contact_pairs.alloc(2 * cap + cap / 4));
+    CK(cudaMemsetAsync(q->pair_count.p, 0, sizeof(unsigned long long), st));
+    k_export_pairs<<<blocks_for(q->n, NL_BLOCK), NL_BLOCK, 0, st>>>(nlist_arrays(q), 0u, h->contact_pairs.p,
+                                                                     (unsigned long long) cap, q->pair_count.p);
+    h->launches++;
+    CK(cudaGetLastError());
+    unsigned long long found = 0;
+    CK(cudaMemcpyAsync(&found, q->pair_count.p, sizeof found, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (found > cap) return fail("bd_contact_update: pair export overflow");
+    if (found == 0) return 0;
+
+    // merge: [accumulated keys + counts | new keys + ones] -> sort by key -> sum counts of equal keys
+    int const cur = h->contact_cur, nxt = cur ^ 1;
+    size_t const total = h->contact_size + (size_t) found;
+    for (DevBuf<unsigned long long> *b : {&h->contact_keys[cur], &h->contact_keys[nxt], &h->contact_new})
+        if (b->count < total) {
+            DevBuf<unsigned long long> grown;
+            CK(grown.alloc(total + total / 2));
+            if (b == &h->contact_keys[cur] && h->contact_size)
+                CK(cudaMemcpyAsync(grown.p, b->p, h->contact_size * sizeof(unsigned long long), cudaMemcpyDeviceToDevice, st));
+            CK(cudaStreamSynchronize(st));
+            b->release();
+            *b = grown;
+            grown.p = nullptr;
+            grown.count = 0;
+        }
+    for (DevBuf<uint32_t> *b : {&h->contact_counts[cur], &h->contact_counts[nxt], &h->contact_ones})
+        if (b->count < total) {
+            DevBuf<uint32_t> grown;
+            CK(grown.alloc(total + total / 2));
+            if (b == &h->contact_counts[cur] && h->contact_size)
+                CK(cudaMemcpyAsync(grown.p, b->p, h->contact_size * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+            CK(cudaStreamSynchronize(st));
+            b->release();
+            *b = grown;
+            grown.p = nullptr;
+            grown.count = 0;
+        }
+    if (h->contact_runs.count < 1) CK(h->contact_runs.alloc(1));
+    k_contact_keys<<<(unsigned) ((found + 255) / 256), 256, 0, st>>>(h->contact_pairs.p, found,
+                                                                     h->contact_keys[cur].p + h->contact_size,
+                                                                     h->contact_counts[cur].p + h->contact_size);
+    h->launches++;
+    CK(cudaGetLastError());
+    size_t need_sort = 0, need_reduce = 0;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, need_sort, h->contact_keys[cur].p, h->contact_new.p, h->contact_counts[cur].p,
+                                       h->contact_ones.p, (int) total, 0, 64, st));
+    CK(cub::DeviceReduce::ReduceByKey(nullptr, need_reduce, h->contact_new.p, h->contact_keys[nxt].p, h->contact_ones.p,
+                                      h->contact_counts[nxt].p, h->contact_runs.p, cuda::std::plus<>(), (int) total, st));
+    size_t const need = std::max(need_sort, need_reduce);
+    if (h->contact_temp.count < need) CK(h->contact_temp.alloc(need + need / 4));
+    size_t bytes = h->contact_temp.count;
+    CK(cub::DeviceRadixSort::SortPairs(h->contact_temp.p, bytes, h->contact_keys[cur].p, h->contact_new.p,
+                                       h->contact_counts[cur].p, h->contact_ones.p, (int) total, 0, 64, st));
+    bytes = h->contact_temp.count;
+    CK(cub::DeviceReduce::ReduceByKey(h->contact_temp.p, bytes, h->contact_new.p, h->contact_keys[nxt].p, h->contact_ones.p,
+                                      h->contact_counts[nxt].p, h->contact_runs.p, cuda::std::plus<>(), (int) total, st));
+    h->launches += 2;
+    unsigned long long runs = 0;
+    CK(cudaMemcpyAsync(&runs, h->contact_runs.p, sizeof runs, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    h->contact_cur = nxt;
+    h->contact_size = (size_t) runs;
+    return 0;
+}
+
+extern "C" int bd_contact_accumulate(bd_engine *h, int32_t replica, uint32_t *triplets_out, int64_t cap, int64_t *count_out)
+{
+    NEED(h);
+    (void) replica;
+    if (!count_out || cap < 0) return fail("bd_contact_accumulate: bad arguments");
+    *count_out = (int64_t) h->contact_size;
+    size_t const m = std::min<size_t>(h->contact_size, (size_t) cap);
+    if (m == 0) return 0;
+    std::vector<unsigned long long> keys(m);
+    std::vector<uint32_t> counts(m);
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaMemcpy(keys.data(), h->contact_keys[h->contact_cur].p, m * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(counts.data(), h->contact_counts[h->contact_cur].p, m * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    for (size_t k = 0; k < m; k++) {  // row-major (i, j) order: the order of the reference's sparse matrix walk
+        triplets_out[3 * k] = (uint32_t) (keys[k] >> 32);
+        triplets_out[3 * k + 1] = (uint32_t) keys[k];
+        triplets_out[3 * k + 2] = counts[k];
+    }
+    return 0;
 }

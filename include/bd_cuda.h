@@ -59,6 +59,20 @@ int bd_set_owned_device(bd_engine *h, const uint8_t *d_owned);
 int bd_gather_positions_indexed(bd_engine *h, const uint32_t *d_index, int64_t count, double *d_xyz);
 int bd_scatter_positions_indexed(bd_engine *h, const uint32_t *d_index, int64_t count, const double *d_xyz);
 
+/* ---- contact map accumulated on the device -------------------------------------
+ * Replaces contact_map::update / accumulate / clear of the interphase driver
+ * (5-sim-genome/src/simulation_interphase/contact_map.cc:25-37 clear, :40-76 update, :79-91 accumulate),
+ * which copies all positions to the host every contactmap_update_interval steps, searches them with
+ * md::neighbor_searcher<open_box> and adds 1 per unordered pair into a sparse matrix.  The engine keeps
+ * ONE map: bd_contact_update adds every pair (i < j) of `replica`'s current configuration whose OPEN-box
+ * distance is <= `distance` (the reference's fp64 test; the simulation's own unit cell is ignored, as in
+ * contact_map.cc:64); positions stay on the device.  bd_contact_accumulate writes up to `cap`
+ * (i, j, count) triplets in (i, j) order -- the order of the reference's row-major sparse walk -- and
+ * the total number of distinct pairs to *count_out (call with cap = 0 to size the buffer). */
+int bd_contact_update(bd_engine *h, int32_t replica, double distance);
+int bd_contact_accumulate(bd_engine *h, int32_t replica, uint32_t *triplets_out, int64_t cap, int64_t *count_out);
+int bd_contact_clear(bd_engine *h, int32_t replica);
+
 /* All replicas at once through HOST buffers laid out [n_replicas][n_beads][3] (original bead order);
  * with pinned buffers the copies are asynchronous on the engine's stream.  bd_get_all_positions
  * returns after the data has arrived. */

@@ -341,3 +341,82 @@ def test_empty_system(engine):
     s.step(3, 1e-3)
     assert s.get_positions().shape == (0, 3)
     assert s.compute_energy() == 0.0
+
+
+def test_statistical_equivalence_with_reference_noise(engine, oracle):
+    """Long runs cannot be compared bead by bead (device Philox vs the reference's sfc64 + ziggurat), so
+    the ensemble statistics are: radius of gyration per chain and the number of contacts, averaged over
+    replicas that start from the same configuration (10Mb ana/telophase model)."""
+    import ensemble as en
+
+    scen = sc.genome_10mb(total=320, bend_energy=0.7)
+    steps, r_gpu, r_cpu, contact = 1500, 192, 48, 0.25
+
+    def observables(xyz):
+        rg = en.radius_of_gyration(xyz, scen.chains).mean()
+        return rg, len(oracle.nsearch_pairs(bd.BOX_OPEN, None, scen.n, contact, xyz))
+
+    gpu = en.ReplicaEnsemble(engine, scen, r_gpu, seed=21)
+    gpu.step(steps)
+    a = np.array([observables(x) for x in gpu.positions()])
+    cpu = en.ReplicaEnsemble(oracle, scen, r_cpu, seed=5)
+    cpu.step(steps)
+    b = np.array([observables(x) for x in cpu.positions()])
+    start = np.array(observables(scen.positions[0]))
+    for k, name in enumerate(("radius of gyration", "contacts")):
+        err = np.sqrt(a[:, k].var(ddof=1) / r_gpu + b[:, k].var(ddof=1) / r_cpu)
+        assert abs(a[:, k].mean() - b[:, k].mean()) < 4.5 * err, (name, a[:, k].mean(), b[:, k].mean(), err)
+    # the run did move the chains away from their start by far more than the resolution of the test
+    assert abs(b[:, 0].mean() - start[0]) > 20 * np.sqrt(b[:, 0].var(ddof=1) / r_cpu)
+    gpu.close()
+    cpu.close()
+
+
+@pytest.mark.gpu
+def test_contact_map_accumulates_on_the_device(engine, oracle):
+    """bd_contact_* against contact_map.cc:25-91 restated with the oracle's neighbour searcher:
+    one count per unordered pair within the contact distance per update, open box even when the
+    simulation is periodic, triplets in (i, j) order, clear() empties the map."""
+    from collections import Counter
+
+    s = sc.chromatin_1kb(n_chains=6, chain_len=200)   # periodic unit cell: the map must ignore it
+    e, _ = build(engine, s)
+    distance = 0.24
+    want = Counter()
+    assert e.contact_accumulate().shape == (0, 3)
+    for k in range(6):
+        e.step(15, s.timestep, s.temperature, seed=5, first_step=1 + 15 * k)
+        e.contact_update(distance)
+        x = e.get_positions()
+        pairs = oracle.nsearch_pairs(bd.BOX_OPEN, None, s.n, distance, x)
+        assert np.array_equal(sort_pairs(pairs), sort_pairs(brute_pairs(x, distance)))
+        want.update(map(tuple, sort_pairs(pairs).tolist()))
+        if k == 2:                                   # the engine keeps stepping on the same list afterwards
+            got = e.contact_accumulate()
+            assert len(got) == len(want)
+    got = e.contact_accumulate()
+    ref = np.array([(i, j, c) for (i, j), c in sorted(want.items())], dtype=np.uint32)
+    assert got.dtype == np.uint32 and np.array_equal(got, ref)
+    assert (got[:, 0] < got[:, 1]).all() and got[:, 2].max() > 1
+    e.contact_clear()
+    assert e.contact_accumulate().shape == (0, 3)
+    e.contact_update(distance * 1.5)                 # a new distance re-tunes the searcher
+    x = e.get_positions()
+    one = sort_pairs(brute_pairs(x, distance * 1.5))
+    got = e.contact_accumulate()
+    assert np.array_equal(got[:, :2], one.astype(np.uint32)) and (got[:, 2] == 1).all()
+    e.close()
+
+
+@pytest.mark.gpu
+def test_contact_map_of_one_replica_of_an_ensemble(engine):
+    s = sc.genome_10mb(total=320, replicas=3)
+    e = bd.System(engine, s.n, 3)
+    s.apply(e)
+    e.step(20, s.timestep, s.temperature, seed=2)
+    for r in (2, 0):
+        e.contact_clear()
+        e.contact_update(0.3, replica=r)
+        got = e.contact_accumulate()
+        assert np.array_equal(got[:, :2], sort_pairs(brute_pairs(e.get_positions(replica=r), 0.3)).astype(np.uint32))
+    e.close()
