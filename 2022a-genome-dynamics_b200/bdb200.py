@@ -174,6 +174,8 @@ ENGINE_ONLY = {
     "contact_update": [C.c_void_p, C.c_int32, C.c_double],
     "contact_accumulate": [C.c_void_p, C.c_int32, C.POINTER(C.c_uint32), C.c_int64, C.POINTER(C.c_int64)],
     "contact_clear": [C.c_void_p, C.c_int32],
+    "snapshot_begin": [C.c_void_p, C.c_int32, C.c_int32],
+    "snapshot_wait": [C.c_void_p, C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.c_int64)],
 }
 
 
@@ -210,7 +212,10 @@ class Backend:
                 "normals": [C.c_uint64, C.c_int64, _dbl_p],
                 "sfc64": [C.c_uint64, C.c_int64, _P(C.c_uint64)],
                 "eval_potential": [C.c_void_p, C.c_int32, _dbl_p, _dbl_p, _dbl_p],
+                "quantize_positions": [_dbl_p, C.c_int64, C.c_int32, _P(C.c_float)],  # oracle only
             }.items():
+                if name == "quantize_positions" and prefix != "orc_":
+                    continue
                 f = getattr(self.lib, prefix + name)
                 f.restype = C.c_int
                 f.argtypes = argtypes
@@ -244,6 +249,12 @@ class Backend:
             if count.value <= cap:
                 return out[: count.value]
             cap = count.value
+
+    def quantize_positions(self, xyz, fraction_bits: int = 16) -> np.ndarray:
+        xyz = np.ascontiguousarray(xyz, dtype=np.float64).reshape(-1, 3)
+        out = np.empty(xyz.shape, dtype=np.float32)
+        self.call("quantize_positions", _dp(xyz), len(xyz), int(fraction_bits), out.ctypes.data_as(_P(C.c_float)))
+        return out
 
     def normals(self, seed: int, count: int) -> np.ndarray:
         out = np.zeros(count, dtype=np.float64)
@@ -511,6 +522,18 @@ class System:
             self.b.call("contact_accumulate", self.h, int(replica), out.ctypes.data_as(C.POINTER(C.c_uint32)),
                         int(count.value), C.byref(count))
         return out
+
+    # single-precision snapshots (simulation_store.cc:253-276 of 5-sim-genome)
+    def snapshot_begin(self, replica: int = 0, fraction_bits: int = 16):
+        self.b.call("snapshot_begin", self.h, int(replica), int(fraction_bits))
+
+    def snapshot_wait(self) -> np.ndarray:
+        """float32 [beads, 3] (all replicas concatenated when begun with replica=-1); a copy."""
+        ptr, count = C.POINTER(C.c_float)(), C.c_int64(0)
+        self.b.call("snapshot_wait", self.h, C.byref(ptr), C.byref(count))
+        if count.value == 0:
+            return np.empty((0, 3), dtype=np.float32)
+        return np.ctypeslib.as_array(ptr, shape=(count.value, 3)).copy()
 
     def contact_clear(self, replica: int = 0):
         self.b.call("contact_clear", self.h, int(replica))

@@ -114,6 +114,13 @@ struct bd_engine {
     DevBuf<unsigned long long> contact_runs;
     int contact_cur = 0;
     size_t contact_size = 0;
+    // single-precision snapshots (bd_snapshot_begin / bd_snapshot_wait)
+    DevBuf<float> snap_dev;
+    float *snap_host = nullptr;  // pinned
+    size_t snap_host_count = 0, snap_count = 0;
+    cudaStream_t snap_stream = nullptr;
+    cudaEvent_t snap_ready = nullptr, snap_done = nullptr;
+    bool snap_pending = false;
 
     // topology (device CSR by original index)
     DevBuf<uint32_t> bond_start, bend_start, bend_adj, triples;
@@ -535,6 +542,11 @@ extern "C" int bd_destroy(bd_engine *h)
     h->contact_pairs.release();
     h->contact_temp.release();
     h->contact_runs.release();
+    h->snap_dev.release();
+    if (h->snap_host) cudaFreeHost(h->snap_host);
+    if (h->snap_ready) cudaEventDestroy(h->snap_ready);
+    if (h->snap_done) cudaEventDestroy(h->snap_done);
+    if (h->snap_stream) cudaStreamDestroy(h->snap_stream);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     delete h;
     return 0;
@@ -578,18 +590,29 @@ extern "C" int bd_set_types(bd_engine *h, const uint8_t *type, int32_t ntypes, c
     return upload_words(h);
 }
 
+/* Positions replaced from outside: records and shadows are rewritten in place and the displacement
+ * from the last list build is folded into the device-side rebuild criterion -- a caller that uploads
+ * what it just downloaded (a per-step driver callback) does not pay for a list build. */
+static int scatter_tracked(bd_engine *h, const double *d_xyz, uint32_t first, uint32_t count)
+{
+    if (upload_params(h)) return 1;
+    k_scatter_tracked<<<blocks_for(count, 256), 256, 0, h->stream>>>(h->pos[h->cur].p, h->shadow[h->cur].p, h->bpos.p,
+                                                                    h->slot_of.p, d_xyz, first, count, h->d_params.p,
+                                                                    h->ctl.p);
+    h->launches++;
+    CK(cudaGetLastError());
+    return 0;
+}
+
 extern "C" int bd_set_positions(bd_engine *h, int32_t replica, const double *xyz)
 {
     NEED(h);
     if (replica < 0 || (uint32_t) replica >= h->replicas) return fail("bd_set_positions: bad replica");
     if (h->n == 0) return 0;
     CK(cudaMemcpyAsync(h->xyz_stage.p, xyz, 3 * (size_t) h->n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-    k_scatter_positions<<<blocks_for(h->n, 256), 256, 0, h->stream>>>(h->pos[h->cur].p, h->slot_of.p, h->xyz_stage.p,
-                                                                      (uint32_t) replica * h->n, h->n);
-    h->launches++;
-    CK(cudaGetLastError());
+    if (scatter_tracked(h, h->xyz_stage.p, (uint32_t) replica * h->n, h->n)) return 1;
     CK(cudaStreamSynchronize(h->stream));  // xyz may be pageable and is reused by the caller
-    return request_rebuild(h);
+    return 0;
 }
 
 extern "C" int bd_get_positions(bd_engine *h, int32_t replica, double *xyz)
@@ -613,10 +636,7 @@ extern "C" int bd_set_all_positions(bd_engine *h, const double *xyz)
     if (h->ntot == 0) return 0;
     if (h->xyz_all.count < 3 * (size_t) h->ntot) CK(h->xyz_all.alloc(3 * (size_t) h->ntot));
     CK(cudaMemcpyAsync(h->xyz_all.p, xyz, 3 * (size_t) h->ntot * sizeof(double), cudaMemcpyHostToDevice, h->stream));
-    k_scatter_positions<<<blocks_for(h->ntot, 256), 256, 0, h->stream>>>(h->pos[h->cur].p, h->slot_of.p, h->xyz_all.p, 0, h->ntot);
-    h->launches++;
-    CK(cudaGetLastError());
-    return request_rebuild(h);
+    return scatter_tracked(h, h->xyz_all.p, 0, h->ntot);
 }
 
 extern "C" int bd_get_all_positions(bd_engine *h, double *xyz)
@@ -635,10 +655,7 @@ extern "C" int bd_set_positions_device(bd_engine *h, const double *d_xyz)
 {
     NEED(h);
     if (h->ntot == 0) return 0;
-    k_scatter_positions<<<blocks_for(h->ntot, 256), 256, 0, h->stream>>>(h->pos[h->cur].p, h->slot_of.p, d_xyz, 0, h->ntot);
-    h->launches++;
-    CK(cudaGetLastError());
-    return request_rebuild(h);
+    return scatter_tracked(h, d_xyz, 0, h->ntot);
 }
 
 extern "C" int bd_get_positions_device(bd_engine *h, double *d_xyz)
@@ -1602,5 +1619,86 @@ extern "C" int bd_contact_accumulate(bd_engine *h, int32_t replica, uint32_t *tr
         triplets_out[3 * k + 1] = (uint32_t) keys[k];
         triplets_out[3 * k + 2] = counts[k];
     }
+    return 0;
+}
+
+// ---- single-precision snapshots ------------------------------------------------------------------
+//
+// The step either side of the hot path on sampling steps.  The drivers' stores convert the fp64
+// positions to float on the host after a blocking download: 5-sim-genome quantises to 16 fraction bits
+// (simulation_common/simulation_store.cc:253-276 with quantize() at :403-407), 4-sim-ab and 3-sim-1kb
+// hand the doubles to an HDF5 float dataset, i.e. a plain conversion (4-sim-ab/box/src/simulation/
+// simulation_store.cc:57-66, 3-sim-1kb/src/simulation/store.cpp).  Here the conversion runs on the device in
+// original bead order, the float buffer (half the bytes) crosses PCIe on a second stream into pinned
+// memory, and the engine keeps stepping meanwhile.
+
+__global__ void k_snapshot(const bead4 *pos, const uint32_t *slot_of, float *out, uint32_t first, uint32_t count,
+                           int fraction_bits)
+{
+    uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const bead4 *p = pos + slot_of[first + i];
+    float v[3] = {__double2float_rn(p->x), __double2float_rn(p->y), __double2float_rn(p->z)};
+    if (fraction_bits >= 0) {
+        // quantize(): nearbyint(float(val) * scale) / scale, scale = 1 << bits, all in float
+        float const scale = (float) (1u << fraction_bits);
+#pragma unroll
+        for (int d = 0; d < 3; d++) v[d] = __fdiv_rn(rintf(__fmul_rn(v[d], scale)), scale);
+    }
+    out[3 * (size_t) i] = v[0];
+    out[3 * (size_t) i + 1] = v[1];
+    out[3 * (size_t) i + 2] = v[2];
+}
+
+extern "C" int bd_snapshot_begin(bd_engine *h, int32_t replica, int32_t fraction_bits)
+{
+    NEED(h);
+    if (replica >= (int32_t) h->replicas) return fail("bd_snapshot_begin: bad replica");
+    if (fraction_bits > 30) return fail("bd_snapshot_begin: at most 30 fraction bits");
+    if (h->snap_pending) return fail("bd_snapshot_begin: the previous snapshot has not been collected (bd_snapshot_wait)");
+    uint32_t const first = replica < 0 ? 0u : (uint32_t) replica * h->n;
+    uint32_t const count = replica < 0 ? h->ntot : h->n;
+    h->snap_count = count;
+    if (count == 0) {
+        h->snap_pending = true;
+        return 0;
+    }
+    if (!h->snap_stream) {
+        CK(cudaStreamCreateWithFlags(&h->snap_stream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&h->snap_ready, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&h->snap_done, cudaEventDisableTiming));
+    }
+    size_t const floats = 3 * (size_t) count;
+    if (h->snap_dev.count < floats) {
+        CK(cudaStreamSynchronize(h->snap_stream));
+        CK(h->snap_dev.alloc(floats));
+    }
+    if (h->snap_host_count < floats) {
+        if (h->snap_host) CK(cudaFreeHost(h->snap_host));
+        h->snap_host = nullptr;
+        h->snap_host_count = 0;
+        CK(cudaHostAlloc((void **) &h->snap_host, floats * sizeof(float), cudaHostAllocDefault));
+        h->snap_host_count = floats;
+    }
+    k_snapshot<<<blocks_for(count, 256), 256, 0, h->stream>>>(h->pos[h->cur].p, h->slot_of.p, h->snap_dev.p, first, count,
+                                                             fraction_bits);
+    h->launches++;
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(h->snap_ready, h->stream));
+    CK(cudaStreamWaitEvent(h->snap_stream, h->snap_ready, 0));
+    CK(cudaMemcpyAsync(h->snap_host, h->snap_dev.p, floats * sizeof(float), cudaMemcpyDeviceToHost, h->snap_stream));
+    CK(cudaEventRecord(h->snap_done, h->snap_stream));
+    h->snap_pending = true;
+    return 0;
+}
+
+extern "C" int bd_snapshot_wait(bd_engine *h, const float **xyz_out, int64_t *count_out)
+{
+    NEED(h);
+    if (!h->snap_pending) return fail("bd_snapshot_wait: no snapshot in flight (bd_snapshot_begin)");
+    if (h->snap_count) CK(cudaEventSynchronize(h->snap_done));
+    h->snap_pending = false;
+    if (xyz_out) *xyz_out = h->snap_host;
+    if (count_out) *count_out = (int64_t) h->snap_count;
     return 0;
 }

@@ -804,6 +804,39 @@ __global__ void k_scatter_positions(bead4 *pos, const uint32_t *slot_of, const d
     p->z = xyz[3 * (size_t) i + 2];
 }
 
+/* positions replaced by the caller while a list exists: the rows stay valid as long as no bead is
+ * further than the skin allows from where it was at the last build, which is the reference's own
+ * criterion (neighbor_list.hpp:132-158 looks at the positions, not at who wrote them).  Write the
+ * record and its shadow, and fold the displacement into the control block; k_rebuild_begin decides. */
+__global__ void k_scatter_tracked(bead4 *pos, float4 *shadow, const bead4 *bpos, const uint32_t *slot_of,
+                                  const double *xyz, uint32_t first, uint32_t count, const DParams *params,
+                                  DControl *ctl)
+{
+    uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
+    double moved2 = 0.0;
+    if (i < count) {
+        uint32_t const s = slot_of[first + i];
+        double const x = xyz[3 * (size_t) i], y = xyz[3 * (size_t) i + 1], z = xyz[3 * (size_t) i + 2];
+        pos[s].x = x;
+        pos[s].y = y;
+        pos[s].z = z;
+        bead4 const b0 = bpos[s];
+        d3 d;
+        if (params->box_kind == BD_BOX_PERIODIC) {
+            shadow[s] = make_shadow<BD_BOX_PERIODIC>(*params, ctl->grid, x, y, z);
+            d = displacement_t<BD_BOX_PERIODIC>(*params, x, y, z, b0.x, b0.y, b0.z);
+        } else {
+            shadow[s] = make_shadow<BD_BOX_OPEN>(*params, ctl->grid, x, y, z);
+            d = displacement_t<BD_BOX_OPEN>(*params, x, y, z, b0.x, b0.y, b0.z);
+        }
+        moved2 = sqnorm_exact(d.x, d.y, d.z);
+        if (!(moved2 == moved2)) moved2 = __longlong_as_double(0x7ff0000000000000ll);  // NaN: force a rebuild
+    }
+    for (int o = 16; o > 0; o >>= 1) moved2 = fmax(moved2, __shfl_xor_sync(0xffffffffu, moved2, o));
+    if ((threadIdx.x & 31) == 0 && moved2 > 0.0)
+        atomicMax(&ctl->max_disp2_bits, (unsigned long long) __double_as_longlong(moved2));
+}
+
 __global__ void k_gather_positions(const bead4 *pos, const uint32_t *slot_of, double *xyz,
                                    uint32_t first, uint32_t count)
 {

@@ -73,6 +73,19 @@ int bd_contact_update(bd_engine *h, int32_t replica, double distance);
 int bd_contact_accumulate(bd_engine *h, int32_t replica, uint32_t *triplets_out, int64_t cap, int64_t *count_out);
 int bd_contact_clear(bd_engine *h, int32_t replica);
 
+/* ---- single-precision snapshots -------------------------------------------------
+ * The drivers' stores write float positions: 5-sim-genome quantises to 16 fraction bits on the host,
+ * quantize(val, bits) = nearbyint(float(val) * 2^bits) / 2^bits in float arithmetic
+ * (5-sim-genome/src/simulation_common/simulation_store.cc:253-276, :403-407); 4-sim-ab and 3-sim-1kb
+ * convert to float (4-sim-ab/box/src/simulation/simulation_store.cc:57-66).  bd_snapshot_begin converts
+ * replica `replica` (-1 = every replica, [n_replicas][n_beads][3]) on the device in original bead order
+ * -- fraction_bits >= 0: the quantisation above, bit for bit; < 0: round-to-nearest float -- and starts
+ * the copy into pinned host memory on a second stream; the engine can keep stepping.  bd_snapshot_wait
+ * blocks until the floats have arrived and returns the engine-owned buffer (valid until the next
+ * bd_snapshot_begin) and the number of beads in it. */
+int bd_snapshot_begin(bd_engine *h, int32_t replica, int32_t fraction_bits);
+int bd_snapshot_wait(bd_engine *h, const float **xyz_out, int64_t *count_out);
+
 /* All replicas at once through HOST buffers laid out [n_replicas][n_beads][3] (original bead order);
  * with pinned buffers the copies are asynchronous on the engine's stream.  bd_get_all_positions
  * returns after the data has arrived. */

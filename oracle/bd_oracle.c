@@ -1648,3 +1648,18 @@ int orc_get_counters(orc_system *s, bd_counters *out)
     }
     return 0;
 }
+
+/* simulation_store.cc:403-407: float const scale = 1 << bits; nearbyint(float(val) * scale) / scale */
+int orc_quantize_positions(const double *xyz, int64_t count, int32_t fraction_bits, float *out)
+{
+    for (int64_t k = 0; k < 3 * count; k++) {
+        float const v = (float) xyz[k];
+        if (fraction_bits < 0) {
+            out[k] = v;
+        } else {
+            float const scale = (float) (1 << fraction_bits);
+            out[k] = nearbyintf(v * scale) / scale;
+        }
+    }
+    return 0;
+}

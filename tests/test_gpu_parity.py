@@ -420,3 +420,44 @@ def test_contact_map_of_one_replica_of_an_ensemble(engine):
         got = e.contact_accumulate()
         assert np.array_equal(got[:, :2], sort_pairs(brute_pairs(e.get_positions(replica=r), 0.3)).astype(np.uint32))
     e.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("bits", [16, 8, -1])
+def test_snapshot_floats_are_the_stores_bit_for_bit(engine, oracle, bits):
+    """bd_snapshot_* against simulation_store.cc:253-276,403-407 (quantize) restated in the oracle
+    and in numpy; the engine keeps stepping while the copy is in flight."""
+    s = sc.genome_10mb(total=320, replicas=3)
+    e = bd.System(engine, s.n, 3)
+    s.apply(e)
+    x = np.stack([e.get_positions(r) for r in range(3)])
+    # ties of the rounding, negative values, values beyond float's integer range
+    wild = x[0].copy()
+    wild[:6] = [[0.5 / 65536, 1.5 / 65536, 2.5 / 65536], [-0.5 / 65536, -1.5 / 65536, -2.5 / 65536],
+                [1e9 + 0.3, -1e9 - 0.3, 3.0000076], [123.4567891234, -0.0, 0.0],
+                [1 + 2.0 ** -24, 1 + 2.0 ** -23, 1 - 2.0 ** -25], [2.0 ** -30, -2.0 ** -30, 1e-45]]
+
+    def want(a):
+        a = np.asarray(a).reshape(-1, 3)
+        ref = oracle.quantize_positions(a, bits)
+        f = a.astype(np.float32)
+        mine = f if bits < 0 else np.rint(f * np.float32(1 << bits)) / np.float32(1 << bits)
+        assert mine.dtype == np.float32 and np.array_equal(ref.view(np.uint32), mine.view(np.uint32))
+        return ref
+
+    e.set_positions(wild, replica=1)
+    e.snapshot_begin(replica=1, fraction_bits=bits)
+    got = e.snapshot_wait()
+    assert got.dtype == np.float32 and np.array_equal(got.view(np.uint32), want(wild).view(np.uint32))
+    e.set_positions(x[1], replica=1)
+    e.snapshot_begin(replica=-1, fraction_bits=bits)
+    e.step(5, s.timestep, s.temperature, seed=9)     # overlaps the copy; the snapshot is of the state before
+    got = e.snapshot_wait()
+    assert np.array_equal(got.view(np.uint32), want(x).view(np.uint32))
+    after = np.stack([e.get_positions(r) for r in range(3)])
+    assert not np.array_equal(after, x)
+    e.snapshot_begin(replica=-1, fraction_bits=bits)
+    assert np.array_equal(e.snapshot_wait().view(np.uint32), want(after).view(np.uint32))
+    with pytest.raises(bd.BackendError):
+        e.snapshot_wait()
+    e.close()
