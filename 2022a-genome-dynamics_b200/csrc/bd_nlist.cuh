@@ -329,6 +329,7 @@ __global__ void __launch_bounds__(NL_BLOCK) k_place(NlistArrays A)
 }
 
 constexpr int ROWS_BLOCK = 128;
+constexpr uint32_t ROWS_QUEUE = 16;  // queued hits per thread between write-outs
 
 /* ELL rows: every bead lists the beads of its replica within the list radius at build time.
  *
@@ -344,8 +345,8 @@ __global__ void __launch_bounds__(ROWS_BLOCK) k_rows(NlistArrays A)
     if (!A.ctl->doing_rebuild) return;
     __shared__ DParams P;
     __shared__ DGrid G;
-    __shared__ uint2 runs[27][ROWS_BLOCK];      // [cell][thread] {first slot, end slot}, empty cells dropped
-    __shared__ uint32_t stage[ROW_PAD][ROWS_BLOCK];  // the group of the row being filled
+    __shared__ uint32_t runs[27][ROWS_BLOCK];   // [cell][thread] keys of the non-empty surrounding cells
+    __shared__ uint32_t hits[ROWS_QUEUE][ROWS_BLOCK];  // [entry][thread] listed slots not yet written out
     __shared__ uint8_t bitpos[3][32];            // position of bit i of axis d inside morton_key()
     for (uint32_t i = threadIdx.x; i < sizeof(DParams) / 4; i += blockDim.x)
         ((uint32_t *) &P)[i] = ((const uint32_t *) A.params)[i];
@@ -424,7 +425,7 @@ __global__ void __launch_bounds__(ROWS_BLOCK) k_rows(NlistArrays A)
                     if (ix < cnt[0] && iy < cnt[1] && iz < cnt[2]) {
                         uint32_t const key = (replica << G.totalbits) | dil[0][ix] | dil[1][iy] | dil[2][iz];
                         uint32_t const b = A.cell_start[key], e = A.cell_start[key + 1];
-                        if (b < e) runs[nruns++][tid] = make_uint2(b, e);
+                        if (b < e) runs[nruns++][tid] = key;
                     }
                 }
 
@@ -433,30 +434,66 @@ __global__ void __launch_bounds__(ROWS_BLOCK) k_rows(NlistArrays A)
         uint32_t count = 0, run = 0, j = 0, e = 0;
         bool over = false;
         if (w_ghost(me.w)) nruns = 0;  // no force is evaluated for a ghost: it needs no row
-        // four candidates of a run are requested together: the walk is bound by the latency of these loads
-        auto consider = [&](uint32_t jj, const float4 &q) {
-            float const d2 = periodic ? shadow_dist2<BD_BOX_PERIODIC>(ms, q, scale)
-                                      : shadow_dist2<BD_BOX_OPEN>(ms, q, scale);
-            if (d2 <= filter2 && jj != s) {
+        // A hit is one predicated store into the thread's queue column; whole groups of ROW_PAD leave the
+        // queue together when it fills up.  (Writing each group as it completes costs a divergent branch
+        // per candidate -- some lane of the warp nearly always has a hit -- and was 40 % of this kernel.)
+        uint32_t qn = 0;
+        uint32_t *const queue = &hits[0][tid];
+        auto flush = [&](bool last) {
+            uint32_t const groups = qn / ROW_PAD;
+            for (uint32_t g = 0; g < groups; g++) {
+                const uint32_t *q4 = queue + g * ROW_PAD * ROWS_BLOCK;
                 if (count < A.cap) {
-                    stage[count % ROW_PAD][tid] = jj;
-                    count++;
-                    if (count % ROW_PAD == 0) {
-                        *dst = make_uint4(stage[0][tid], stage[1][tid], stage[2][tid], stage[3][tid]);
-                        dst += A.pstride;
-                    }
+                    *dst = make_uint4(q4[0], q4[ROWS_BLOCK], q4[2 * ROWS_BLOCK], q4[3 * ROWS_BLOCK]);
+                    dst += A.pstride;
+                    count += ROW_PAD;
                 } else {
                     over = true;
                 }
             }
+            uint32_t const rem = qn - groups * ROW_PAD;
+            if (!last) {
+                for (uint32_t k = 0; k < rem; k++) queue[k * ROWS_BLOCK] = queue[(groups * ROW_PAD + k) * ROWS_BLOCK];
+            } else if (rem) {
+                // the last group is padded with the sentinel slot: the step kernel reads whole groups
+                const uint32_t *q4 = queue + groups * ROW_PAD * ROWS_BLOCK;
+                if (count < A.cap) {
+                    *dst = make_uint4(q4[0], rem > 1 ? q4[ROWS_BLOCK] : A.ntot, rem > 2 ? q4[2 * ROWS_BLOCK] : A.ntot, A.ntot);
+                    count += rem;
+                } else {
+                    over = true;
+                }
+            }
+            qn = rem;
         };
+        auto consider = [&](uint32_t jj, const float4 &q) {
+            float const d2 = periodic ? shadow_dist2<BD_BOX_PERIODIC>(ms, q, scale)
+                                      : shadow_dist2<BD_BOX_OPEN>(ms, q, scale);
+            if (d2 <= filter2 && jj != s) {
+                queue[qn * ROWS_BLOCK] = jj;
+                qn++;
+            }
+        };
+        // the bounds of the next run are requested one run ahead (they were just read: cache hits)
+        uint32_t nb = 0, ne = 0;
+        if (nruns) {
+            uint32_t const key = runs[0][tid];
+            nb = A.cell_start[key];
+            ne = A.cell_start[key + 1];
+        }
         while (true) {
             if (j >= e) {
                 if (run == nruns) break;
-                uint2 const r = runs[run++][tid];
-                j = r.x;
-                e = r.y;
+                j = nb;
+                e = ne;
+                run++;
+                if (run < nruns) {
+                    uint32_t const key = runs[run][tid];
+                    nb = A.cell_start[key];
+                    ne = A.cell_start[key + 1];
+                }
             }
+            // four candidates of a run are requested together: the walk is bound by the latency of these loads
             if (e - j >= 4) {
                 float4 const q0 = A.shadow[j], q1 = A.shadow[j + 1], q2 = A.shadow[j + 2], q3 = A.shadow[j + 3];
                 consider(j, q0);
@@ -469,13 +506,10 @@ __global__ void __launch_bounds__(ROWS_BLOCK) k_rows(NlistArrays A)
                 consider(j, q);
                 j++;
             }
+            if (qn > ROWS_QUEUE - 4) flush(false);
         }
+        flush(true);
         A.nnbr[s] = count;
-        // the last group is padded with the sentinel slot: the step kernel reads whole groups
-        if (count % ROW_PAD) {
-            for (uint32_t k = count % ROW_PAD; k < ROW_PAD; k++) stage[k][tid] = A.ntot;
-            *dst = make_uint4(stage[0][tid], stage[1][tid], stage[2][tid], stage[3][tid]);
-        }
         overflowed += over;
         tot += count;
         longest = max(longest, count);
