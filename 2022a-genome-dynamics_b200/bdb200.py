@@ -139,6 +139,8 @@ def _api(prefix: str):
         "update_pair_ff": [vp, i32, vp, dbl],
         "add_bond_ff": [vp, i32, vp, _u32_p, i64, _P(i32)],
         "update_bond_ff": [vp, i32, vp],
+        "set_bond_pairs": [vp, i32, _u32_p, i64],
+        "set_bond_min_image": [vp, i32, i32],
         "add_bend_ff": [vp, _u32_p, _dbl_p, i64, _P(i32)],
         "add_wall_ff": [vp, i32, i32, i32, vp, _dbl_p, _dbl_p, _P(i32)],
         "update_wall_ff": [vp, i32, vp, _dbl_p, _dbl_p],
@@ -356,6 +358,14 @@ class System:
         self.b.call("add_bond_ff", self.h, tab.shape[1], tab.ctypes.data,
                     p.ctypes.data_as(_u32_p), len(p), C.byref(ff))
         return ff.value
+
+    def set_bond_pairs(self, ff, pairs):
+        """Replace the pair list of a bond forcefield (a dynamic glue / loop list; may be empty)."""
+        p = np.ascontiguousarray(pairs, dtype=np.uint32).reshape(-1, 2)
+        self.b.call("set_bond_pairs", self.h, ff, p.ctypes.data_as(_u32_p), len(p))
+
+    def set_bond_min_image(self, ff, on=True):
+        self.b.call("set_bond_min_image", self.h, ff, int(bool(on)))
 
     def update_bond_ff(self, ff, tab):
         tab = self._table(tab, self.ntypes**2)

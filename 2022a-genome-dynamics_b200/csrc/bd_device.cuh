@@ -63,7 +63,7 @@ struct __align__(16) DTerm {
 static_assert(sizeof(DTerm) == 64, "DTerm is one 64-byte record");
 
 struct DPair { int32_t enabled, nterms, term_off, has_targets; double dcut, dcut2; };
-struct DBond { int32_t enabled, nterms, term_off, pad; };
+struct DBond { int32_t enabled, nterms, term_off, min_image; };
 struct DBend { int32_t enabled, pad[3]; };
 struct DWall {
     int32_t enabled, nterms, term_off, shape, direction, pad[3];

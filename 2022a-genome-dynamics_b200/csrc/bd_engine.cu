@@ -802,6 +802,28 @@ extern "C" int bd_add_bond_ff(bd_engine *h, int32_t nterms, const bd_term *table
     return fail("bd_add_bond_ff: too many bond forcefields");
 }
 
+/* dynamic pair lists (glue / loop force fields of 3-sim-1kb): only the list crosses to the device; the
+ * slot-space bond rows are refilled by the next list build */
+extern "C" int bd_set_bond_pairs(bd_engine *h, int32_t ff, const uint32_t *pairs, int64_t m)
+{
+    NEED(h);
+    if (ff < 0 || ff >= BD_MAX_BOND_FF || !h->bond[ff].used) return fail("bd_set_bond_pairs: bad forcefield id");
+    if (m < 0 || (m > 0 && !pairs)) return fail("bd_set_bond_pairs: bad pair list");
+    for (int64_t b = 0; b < 2 * m; b++)
+        if (pairs[b] >= h->n) return fail("bd_set_bond_pairs: bond index out of range");
+    h->bond_pairs[ff].assign(pairs, pairs + 2 * m);
+    return upload_topology(h);
+}
+
+extern "C" int bd_set_bond_min_image(bd_engine *h, int32_t ff, int32_t on)
+{
+    NEED(h);
+    if (ff < 0 || ff >= BD_MAX_BOND_FF || !h->bond[ff].used) return fail("bd_set_bond_min_image: bad forcefield id");
+    h->hp.bond[ff].min_image = on != 0;
+    h->params_dirty = true;
+    return 0;
+}
+
 extern "C" int bd_update_bond_ff(bd_engine *h, int32_t ff, const bd_term *table)
 {
     NEED(h);

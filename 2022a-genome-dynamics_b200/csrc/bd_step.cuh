@@ -303,7 +303,11 @@ __device__ __forceinline__ void bonded_forces(const StepArrays &A, const DParams
             bool const second = (adj.y >> 8) & 1u;
             // the force on this bead is scalar * (x_me - x_partner) whichever end it is; only the
             // table row depends on the order (type_first, type_second)
-            double const rx = me.x - o.x, ry = me.y - o.y, rz = me.z - o.z;
+            double rx = me.x - o.x, ry = me.y - o.y, rz = me.z - o.z;
+            if (bf.min_image) {  // a dynamic pair list of glue_forcefield's kind (glue_forcefield.cpp:40)
+                d3 const r = displacement(P, me.x, me.y, me.z, o.x, o.y, o.z);
+                rx = r.x; ry = r.y; rz = r.z;
+            }
             double const r2 = rx * rx + ry * ry + rz * rz;
             int const cell = second ? (int) (tj * T + ti) : (int) (ti * T + tj);
             double sc;
@@ -714,7 +718,11 @@ __global__ void __launch_bounds__(STEP_BLOCK) k_energy(StepArrays A, Select sel,
             const DBond &bf = P.bond[f];
             if (!ff_on(sel, BD_FF_BOND, f, bf.enabled)) continue;
             bead4 const o = load_bead(A.pos + A.slot_of[base + adj.x]);
-            double const rx = me.x - o.x, ry = me.y - o.y, rz = me.z - o.z;
+            double rx = me.x - o.x, ry = me.y - o.y, rz = me.z - o.z;
+            if (bf.min_image) {
+                d3 const r = displacement(P, me.x, me.y, me.z, o.x, o.y, o.z);
+                rx = r.x; ry = r.y; rz = r.z;
+            }
             E += pot_energy(A.terms + bf.term_off + (ti * T + w_type(o.w)) * bf.nterms, bf.nterms,
                             rx * rx + ry * ry + rz * rz);
         }

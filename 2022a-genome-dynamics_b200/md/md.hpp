@@ -1280,6 +1280,30 @@ namespace md
             return *this;
         }
 
+        // ---- extension over micromd: pair lists that change while the simulation runs --------------
+        // 3-sim-1kb's loop_forcefield / glue_forcefield (src/simulation/forces/*.cpp) walk pair sets that
+        // a kinetic model edits between steps.  Replacing the list does not re-create the engine: only
+        // the list is uploaded (bd_set_bond_pairs).  b200_use_shortest_displacement(true) takes the pair
+        // displacement through the system's periodic box, as glue_forcefield does (bd_set_bond_min_image).
+        template<typename PairRange>
+        self& b200_set_bonded_pairs(PairRange const& pairs)
+        {
+            pairs_.clear();
+            for (auto const& p : pairs) {
+                pairs_.push_back(std::uint32_t(std::get<0>(p)));
+                pairs_.push_back(std::uint32_t(std::get<1>(p)));
+            }
+            pairs_dirty_ = true;
+            return *this;
+        }
+
+        self& b200_use_shortest_displacement(bool on)
+        {
+            min_image_ = on;
+            image_dirty_ = true;
+            return *this;
+        }
+
         auto bonded_pairwise_potential(md::system const& system, md::index i, md::index j) const
         {
             if constexpr (std::is_invocable<PotFun const&, md::system const&, md::index, md::index>::value) return potfun_(system, i, j);
@@ -1303,6 +1327,8 @@ namespace md
             }
             b200::check(MD_B200_CALL(add_bond_ff)(b.handle(), nterms_, table_.data(), pairs_.data(),
                                                   std::int64_t(pairs_.size() / 2), &b200_id), "add_bond_ff");
+            if (min_image_) b200::check(MD_B200_CALL(set_bond_min_image)(b.handle(), b200_id, 1), "set_bond_min_image");
+            pairs_dirty_ = image_dirty_ = false;
         }
 
         bool b200_refresh(b200::binding& b, md::system const& sys) override
@@ -1314,11 +1340,24 @@ namespace md
                 b200::check(MD_B200_CALL(update_bond_ff)(b.handle(), b200_id, table.data()), "update_bond_ff");
                 table_ = std::move(table);
             }
+            if (pairs_dirty_) {
+                md::index const n = sys.particle_count();
+                for (std::uint32_t v : pairs_)
+                    if (v >= n) throw std::out_of_range("md (B200 engine): bonded pair index out of range");
+                b200::check(MD_B200_CALL(set_bond_pairs)(b.handle(), b200_id, pairs_.data(),
+                                                         std::int64_t(pairs_.size() / 2)), "set_bond_pairs");
+                pairs_dirty_ = false;
+            }
+            if (image_dirty_) {
+                b200::check(MD_B200_CALL(set_bond_min_image)(b.handle(), b200_id, min_image_ ? 1 : 0), "set_bond_min_image");
+                image_dirty_ = false;
+            }
             return true;
         }
 
     private:
         PotFun potfun_;
+        bool pairs_dirty_ = false, image_dirty_ = false, min_image_ = false;
         std::vector<std::uint32_t> pairs_;
         b200::term_list table_;
         int nterms_ = 0;

@@ -869,6 +869,7 @@ typedef struct {
 
 typedef struct {
     int used, enabled, nterms;
+    int min_image; /* glue_forcefield.cpp:24,40: displacement through the periodic box */
     bd_term *table; /* [T*T*nterms] */
     uint32_t *pairs;
     size_t m;
@@ -1107,6 +1108,32 @@ int orc_add_bond_ff(orc_system *s, int32_t nterms, const bd_term *table, const u
     return fail("oracle: too many bond forcefields");
 }
 
+int orc_set_bond_pairs(orc_system *s, int32_t ff, const uint32_t *pairs, int64_t m)
+{
+    if (ff < 0 || ff >= BD_MAX_BOND_FF || !s->bond[ff].used || m < 0) {
+        return fail("oracle: bad bond forcefield id or pair count");
+    }
+    for (int64_t b = 0; b < 2 * m; b++) {
+        if (pairs[b] >= s->n) {
+            return fail("oracle: bond index out of range");
+        }
+    }
+    free(s->bond[ff].pairs);
+    s->bond[ff].m = (size_t) m;
+    s->bond[ff].pairs = malloc((m ? m : 1) * 2 * sizeof *s->bond[ff].pairs);
+    memcpy(s->bond[ff].pairs, pairs, (size_t) m * 2 * sizeof *s->bond[ff].pairs);
+    return 0;
+}
+
+int orc_set_bond_min_image(orc_system *s, int32_t ff, int32_t on)
+{
+    if (ff < 0 || ff >= BD_MAX_BOND_FF || !s->bond[ff].used) {
+        return fail("oracle: bad bond forcefield id");
+    }
+    s->bond[ff].min_image = on != 0;
+    return 0;
+}
+
 int orc_update_bond_ff(orc_system *s, int32_t ff, const bd_term *table)
 {
     if (ff < 0 || ff >= BD_MAX_BOND_FF || !s->bond[ff].used) {
@@ -1277,13 +1304,15 @@ static void pair_ff_eval(orc_system *s, pair_ff *ff, v3 *forces, double *energy)
     }
 }
 
-/* MD/forcefield/bonded_pairwise_forcefield.hpp:56-93 -- no minimum image */
+/* MD/forcefield/bonded_pairwise_forcefield.hpp:56-93 -- no minimum image -- or, with min_image,
+ * 3-sim-1kb/src/simulation/forces/glue_forcefield.cpp:17-45 */
 static void bond_ff_eval(orc_system *s, bond_ff *ff, v3 *forces, double *energy)
 {
     for (size_t k = 0; k < ff->m; k++) {
         size_t const i = ff->pairs[2 * k], j = ff->pairs[2 * k + 1];
         const bd_term *row = pair_row(s, ff->table, ff->nterms, i, j);
-        v3 const r = v3_sub(s->pos[i], s->pos[j]);
+        v3 const r = ff->min_image ? shortest_displacement(&s->box, s->pos[i], s->pos[j])
+                                   : v3_sub(s->pos[i], s->pos[j]);
         if (forces) {
             v3 const f = pot_force(row, ff->nterms, r);
             forces[i] = v3_add(forces[i], f);

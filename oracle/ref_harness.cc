@@ -222,8 +222,10 @@ namespace
     {
         bool used = false;
         bool enabled = false;
+        bool min_image = false;
         int nterms = 0;
         std::vector<bd_term> table;
+        std::vector<std::uint32_t> pairs;
         std::shared_ptr<md::forcefield> ff;
     };
 
@@ -313,6 +315,74 @@ struct ref_system
         add(external != nullptr, external);
     }
 };
+
+// A pair-list force field with the displacement taken through the periodic box: the shape of
+// 3-sim-1kb's glue_forcefield (src/simulation/forces/glue_forcefield.cpp:17-45), on micromd's
+// md::periodic_box::shortest_displacement and the same potential evaluation as the bonded force field.
+template<typename PotFun>
+struct boxed_pair_forcefield : md::forcefield
+{
+    ref_system* owner;
+    int slot;
+    PotFun potfun;
+
+    boxed_pair_forcefield(ref_system* s, int k, PotFun f) : owner{s}, slot{k}, potfun{f} {}
+
+    md::vector displacement(md::point a, md::point b) const
+    {
+        if (owner->box_kind == BD_BOX_PERIODIC) {
+            return owner->pbox.shortest_displacement(a, b);
+        }
+        return md::open_box{}.shortest_displacement(a, b);
+    }
+
+    md::scalar compute_energy(md::system const& system) override
+    {
+        auto const positions = system.view_positions();
+        auto const& pairs = owner->bond[slot].pairs;
+        md::scalar total = 0;
+        for (std::size_t b = 0; b + 1 < pairs.size(); b += 2) {
+            md::index const i = pairs[b], j = pairs[b + 1];
+            total += potfun(i, j).evaluate_energy(displacement(positions[i], positions[j]));
+        }
+        return total;
+    }
+
+    void compute_force(md::system const& system, md::array_view<md::vector> forces) override
+    {
+        auto const positions = system.view_positions();
+        auto const& pairs = owner->bond[slot].pairs;
+        for (std::size_t b = 0; b + 1 < pairs.size(); b += 2) {
+            md::index const i = pairs[b], j = pairs[b + 1];
+            auto const f = potfun(i, j).evaluate_force(displacement(positions[i], positions[j]));
+            forces[i] += f;
+            forces[j] -= f;
+        }
+    }
+};
+
+// (re)build the micromd force field object of bond slot k from its stored pairs
+static void build_bond_ff(ref_system* s, int k)
+{
+    bond_slot& slot = s->bond[k];
+    auto potfun = [s, k](md::index i, md::index j) {
+        bond_slot const& sl = s->bond[k];
+        return table_potential{
+            sl.table.data() + (std::size_t(s->type[i]) * s->ntypes + s->type[j]) * sl.nterms,
+            sl.nterms
+        };
+    };
+    if (slot.min_image) {
+        slot.ff = std::make_shared<boxed_pair_forcefield<decltype(potfun)>>(s, k, potfun);
+    } else {
+        auto ff = md::make_bonded_pairwise_forcefield(potfun);
+        for (std::size_t b = 0; b + 1 < slot.pairs.size(); b += 2) {
+            ff.add_bonded_pair(slot.pairs[b], slot.pairs[b + 1]);
+        }
+        slot.ff = std::make_shared<decltype(ff)>(ff);
+    }
+    s->reregister();
+}
 
 #define REF_TRY try {
 #define REF_CATCH                                                                                  \
@@ -464,22 +534,36 @@ int ref_add_bond_ff(ref_system* s, std::int32_t nterms, const bd_term* table,
         slot.used = slot.enabled = true;
         slot.nterms = nterms;
         slot.table.assign(table, table + std::size_t(s->ntypes) * s->ntypes * nterms);
-        auto ff = md::make_bonded_pairwise_forcefield([s, k](md::index i, md::index j) {
-            bond_slot const& sl = s->bond[k];
-            return table_potential{
-                sl.table.data() + (std::size_t(s->type[i]) * s->ntypes + s->type[j]) * sl.nterms,
-                sl.nterms
-            };
-        });
-        for (std::int64_t b = 0; b < m; b++) {
-            ff.add_bonded_pair(pairs[2 * b], pairs[2 * b + 1]);
-        }
-        slot.ff = std::make_shared<decltype(ff)>(ff);
-        s->reregister();
+        slot.pairs.assign(pairs, pairs + 2 * m);
+        build_bond_ff(s, k);
         *ff_out = k;
         return 0;
     }
     return fail("ref: too many bond forcefields");
+    REF_CATCH
+}
+
+int ref_set_bond_pairs(ref_system* s, std::int32_t ff, const std::uint32_t* pairs, std::int64_t m)
+{
+    REF_TRY
+    if (ff < 0 || ff >= BD_MAX_BOND_FF || !s->bond[ff].used || m < 0) {
+        return fail("ref: bad bond forcefield id or pair count");
+    }
+    s->bond[ff].pairs.assign(pairs, pairs + 2 * m);
+    build_bond_ff(s, ff);
+    return 0;
+    REF_CATCH
+}
+
+int ref_set_bond_min_image(ref_system* s, std::int32_t ff, std::int32_t on)
+{
+    REF_TRY
+    if (ff < 0 || ff >= BD_MAX_BOND_FF || !s->bond[ff].used) {
+        return fail("ref: bad bond forcefield id");
+    }
+    s->bond[ff].min_image = on != 0;
+    build_bond_ff(s, ff);
+    return 0;
     REF_CATCH
 }
 

@@ -20,6 +20,7 @@
 #include <functional>
 #include <memory>
 #include <random>
+#include <string>
 #include <utility>
 #include <vector>
 
@@ -468,8 +469,13 @@ namespace
         md::spring_potential _potential;
     };
 
-    void chromatin()
+    // device_lists (B200 header only): the same model with the two pair-list force fields evaluated by
+    // the engine -- a bonded force field whose list is replaced while the simulation runs
+    // (b200_set_bonded_pairs), the glue one through the periodic box (b200_use_shortest_displacement)
+    void chromatin(bool device_lists = false)
     {
+        char const* const tag = device_lists ? "chromatin_dev" : "chromatin";
+        auto const name = [&](char const* what) { return std::string(tag) + what; };
         md::system system;
         system.require(monomer_data_attribute);
         double const box_size = 2.4;
@@ -506,21 +512,39 @@ namespace
         auto glues = std::make_shared<pair_list>();
         loops->pairs = {{5, 40}, {70, 110}, {130, 170}};
         glues->pairs = {{10, 14}, {65, 71}, {200, 204}};
-        system.add_forcefield(loop_forcefield{loops, 50, 0.3});
-        system.add_forcefield(glue_forcefield{glues, box, 2.0, 0.45});
+        std::function<void()> lists_changed = [] {};
+#ifdef MD_B200_MD_HPP
+        if (device_lists) {
+            auto loop_ff = system.add_forcefield(
+                md::make_bonded_pairwise_forcefield(md::spring_potential{.spring_constant = 50, .equilibrium_distance = 0.3}));
+            auto glue_ff = system.add_forcefield(
+                md::make_bonded_pairwise_forcefield(md::softcore_potential<8, 3>{.energy = -2.0, .diameter = 0.45}));
+            glue_ff->b200_use_shortest_displacement(true);
+            lists_changed = [=] {
+                loop_ff->b200_set_bonded_pairs(loops->pairs);
+                glue_ff->b200_set_bonded_pairs(glues->pairs);
+            };
+            lists_changed();
+        }
+#endif
+        if (!device_lists) {
+            system.add_forcefield(loop_forcefield{loops, 50, 0.3});
+            system.add_forcefield(glue_forcefield{glues, box, 2.0, 0.45});
+        }
 
         std::vector<md::vector> forces(system.particle_count());
         system.compute_force(forces);
-        print_vectors("chromatin.force", forces, 6);
-        std::printf("chromatin.energy %.17g\n", system.compute_potential_energy());
+        print_vectors(name(".force").c_str(), forces, 6);
+        std::printf("%s.energy %.17g\n", tag, system.compute_potential_energy());
         // the kinetic part of the driver: the pair lists change while the simulation runs
         md::simulate_brownian_dynamics(system, {.temperature = 0, .timestep = 1e-5, .steps = 60, .callback = [&](md::step step) {
             if (step == 20) loops->pairs.push_back({185, 230});
             if (step == 40) glues->pairs.erase(glues->pairs.begin());
+            if (step == 20 || step == 40) lists_changed();
         }});
         md::simulate_brownian_dynamics(system, {.temperature = 0, .timestep = 1e-5, .steps = 20});
-        print_points("chromatin.pos", system.view_positions(), 5);
-        std::printf("chromatin.energy_end %.17g\n", system.compute_potential_energy());
+        print_points(name(".pos").c_str(), system.view_positions(), 5);
+        std::printf("%s.energy_end %.17g\n", tag, system.compute_potential_energy());
     }
 }
 
@@ -543,5 +567,8 @@ int main()
     }
     spindle();
     chromatin();
+#ifdef MD_B200_MD_HPP
+    chromatin(true);
+#endif
     return 0;
 }

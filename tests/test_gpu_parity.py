@@ -461,3 +461,55 @@ def test_snapshot_floats_are_the_stores_bit_for_bit(engine, oracle, bits):
     with pytest.raises(bd.BackendError):
         e.snapshot_wait()
     e.close()
+
+
+@pytest.mark.gpu
+def test_dynamic_pair_lists_on_the_device(engine, oracle):
+    """glue- and loop-shaped pair lists edited between steps (set_bond_pairs), the glue
+    list through the periodic box (set_bond_min_image); engine against the oracle, which
+    tests/test_oracle_vs_reference.py pins to micromd for the same calls."""
+    rng = np.random.default_rng(17)
+    s = sc.chromatin_1kb(n_chains=3, chain_len=120)
+    L, n = np.asarray(s.period), s.n
+    well = bd.pair_table(s.ntypes, lambda ti, tj: [bd.softwell(6, -1.5, 0.4)])
+    spring = bd.pair_table(s.ntypes, lambda ti, tj: [bd.spring(40.0, 0.3)])
+
+    def random_pairs(m):
+        i = rng.integers(0, n, size=m)
+        j = (i + rng.integers(1, n - 1, size=m)) % n
+        return np.stack([i, j], axis=1).astype(np.uint32)
+
+    x = s.positions[0] + np.random.default_rng(5).integers(-2, 3, size=(n, 3)) * L   # periodic images
+    systems, ids = [], []
+    for backend in (engine, oracle):
+        e, _ = build(backend, s)
+        e.set_positions(x)
+        glue = e.add_bond_ff(well, np.zeros((0, 2), np.uint32))
+        loop = e.add_bond_ff(spring, np.zeros((0, 2), np.uint32))
+        e.set_bond_min_image(glue, True)
+        systems.append(e)
+        ids.append((glue, loop))
+    z = oracle.normals(3, 6 * 4 * n * 3).reshape(6, 4, n, 3)
+    for round_ in range(6):
+        gp, lp = random_pairs(40 + 5 * round_), random_pairs(12)
+        if round_ == 4:
+            gp = gp[:0]
+        out = []
+        for e, (glue, loop) in zip(systems, ids):
+            e.set_bond_pairs(glue, gp)
+            e.set_bond_pairs(loop, lp)
+            out.append((e.compute_forces(ff_class=bd.FF_BOND, ff=glue), e.compute_forces(ff_class=bd.FF_BOND, ff=loop),
+                        e.compute_energy(ff_class=bd.FF_BOND, ff=glue), e.compute_forces(), e.compute_energy()))
+            e.step(4, s.timestep, s.temperature, replay_normals=z[round_])
+        (fg, fl, eg, fa, ea), (og, ol, oeg, oa, oea) = out
+        assert rel_force_error(fl, ol) <= FORCE_TOL and rel_force_error(fa, oa) <= FORCE_TOL
+        if len(gp):
+            assert np.abs(og).max() > 0 and rel_force_error(fg, og) <= FORCE_TOL
+        else:
+            assert not fg.any()
+        assert eg == pytest.approx(oeg, rel=1e-9, abs=1e-12) and ea == pytest.approx(oea, rel=1e-9)
+        assert np.abs(systems[0].get_positions() - systems[1].get_positions()).max() <= TRAJ_TOL
+    with pytest.raises(bd.BackendError):
+        systems[0].set_bond_pairs(ids[0][0], np.array([[0, n]], np.uint32))
+    for e in systems:
+        e.close()

@@ -38,6 +38,13 @@ def parse(text):
 
 
 def compare(got, want):
+    # the B200 header runs the 3-sim-1kb case a second time with its pair-list force fields on the device
+    # (chromatin_dev.*): same model, so the same numbers as the reference's chromatin.* lines
+    dev = [(t.replace("chromatin_dev", "chromatin"), a) for t, a in got if t.startswith("chromatin_dev")]
+    got = [(t, a) for t, a in got if not t.startswith("chromatin_dev")]
+    ref_chromatin = [(t, a) for t, a in want if t.startswith("chromatin.")]
+    assert dev and [t for t, _ in dev] == [t for t, _ in ref_chromatin]
+    got, want = got + dev, want + ref_chromatin
     assert [t for t, _ in got] == [t for t, _ in want]
     for (tag, a), (_, b) in zip(got, want):
         err = np.abs(a - b).max() / max(1.0, np.abs(b).max())

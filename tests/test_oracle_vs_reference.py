@@ -139,3 +139,57 @@ def test_external_forces_are_one_more_forcefield(oracle, reference):
     for s in (so, sr):
         s.set_external_forces(None)
     assert np.array_equal(so.compute_forces(), sr.compute_forces())
+
+
+def test_dynamic_pair_lists_with_and_without_minimum_image(oracle, reference):
+    """set_bond_pairs / set_bond_min_image: the oracle against micromd's bonded force field (plain
+    displacement, the loop_forcefield case) and against a glue_forcefield-shaped class on
+    md::periodic_box::shortest_displacement, with the list edited between steps."""
+    import scenarios as sc
+    from cases import rel_force_error
+
+    rng = np.random.default_rng(17)
+    s = sc.chromatin_1kb(n_chains=3, chain_len=120)
+    L = np.asarray(s.period)
+    n = s.n
+    well = bd.pair_table(s.ntypes, lambda ti, tj: [bd.softwell(6, -1.5, 0.4)])
+    spring = bd.pair_table(s.ntypes, lambda ti, tj: [bd.spring(40.0, 0.3)])
+
+    def random_pairs(m):
+        i = rng.integers(0, n, size=m)
+        j = (i + rng.integers(1, n - 1, size=m)) % n
+        return np.stack([i, j], axis=1).astype(np.uint32)
+
+    systems = []
+    for backend in (oracle, reference):
+        e, _ = build(backend, s)
+        systems.append(e)
+    x = s.positions[0] + np.random.default_rng(5).integers(-2, 3, size=(n, 3)) * L   # images: min-image matters
+    ids = []
+    for e in systems:
+        e.set_positions(x)
+        glue = e.add_bond_ff(well, np.zeros((0, 2), np.uint32))
+        loop = e.add_bond_ff(spring, np.zeros((0, 2), np.uint32))
+        e.set_bond_min_image(glue, True)
+        ids.append((glue, loop))
+    for round_ in range(6):
+        gp, lp = random_pairs(40 + 5 * round_), random_pairs(12)
+        if round_ == 4:
+            gp = gp[:0]                                   # an empty list is a valid list
+        out = []
+        for e, (glue, loop) in zip(systems, ids):
+            e.set_bond_pairs(glue, gp)
+            e.set_bond_pairs(loop, lp)
+            fg = e.compute_forces(ff_class=bd.FF_BOND, ff=glue)
+            fl = e.compute_forces(ff_class=bd.FF_BOND, ff=loop)
+            eg = e.compute_energy(ff_class=bd.FF_BOND, ff=glue)
+            e.step(4, s.timestep, s.temperature, seed=3, first_step=1 + 4 * round_)
+            out.append((fg, fl, eg, e.get_positions()))
+        (fg, fl, eg, xo), (rg, rl, reg, xr) = out
+        assert rel_force_error(fl, rl) <= 1e-12
+        if len(gp):
+            assert np.abs(rg).max() > 0 and rel_force_error(fg, rg) <= 1e-12
+        assert eg == pytest.approx(reg, rel=1e-12, abs=1e-12)
+        assert np.abs(xo - xr).max() <= 1e-11
+    for e in systems:
+        e.close()
