@@ -566,11 +566,14 @@ __global__ void __launch_bounds__(BAL_TILE) k_balance(NlistArrays A)
         // thread t now owns the bead at offset src[t]: move that bead's row to column pbase + t
         uint32_t const from = src[threadIdx.x];
         bool const owner = chunk * BAL_TILE + from < A.n;  // dead offsets were ranked last
+        // (only the groups the row has: what lies beyond a row's padded length is never read)
         uint32_t const groups = (longest + ROW_PAD - 1) / ROW_PAD;
+        uint32_t const mine_groups = owner ? (len[from] + ROW_PAD - 1) / ROW_PAD : 0u;
         for (uint32_t g = 0; g < groups; g++) {
-            uint4 const v = A.nbr4[(size_t) g * A.pstride + pbase + from];
+            uint4 v = make_uint4(0u, 0u, 0u, 0u);
+            if (g < mine_groups) v = A.nbr4[(size_t) g * A.pstride + pbase + from];
             __syncthreads();
-            A.nbr4[(size_t) g * A.pstride + pbase + threadIdx.x] = v;
+            if (g < mine_groups) A.nbr4[(size_t) g * A.pstride + pbase + threadIdx.x] = v;
         }
         A.plen[pbase + threadIdx.x] = owner ? len[from] : 0u;
         if (A.bond_deg) {
