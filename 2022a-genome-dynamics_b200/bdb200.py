@@ -176,6 +176,8 @@ ENGINE_ONLY = {
     "contact_update": [C.c_void_p, C.c_int32, C.c_double],
     "contact_accumulate": [C.c_void_p, C.c_int32, C.POINTER(C.c_uint32), C.c_int64, C.POINTER(C.c_int64)],
     "contact_clear": [C.c_void_p, C.c_int32],
+    "refine_spline": [_dbl_p, _P(C.c_int64), C.c_int64, C.c_int32, _P(C.c_int64), _P(C.c_int64), C.c_int64, C.c_int64,
+                      C.c_int64, _dbl_p, C.c_int32],
     "snapshot_begin": [C.c_void_p, C.c_int32, C.c_int32],
     "snapshot_wait": [C.c_void_p, C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.c_int64)],
 }
@@ -215,8 +217,10 @@ class Backend:
                 "sfc64": [C.c_uint64, C.c_int64, _P(C.c_uint64)],
                 "eval_potential": [C.c_void_p, C.c_int32, _dbl_p, _dbl_p, _dbl_p],
                 "quantize_positions": [_dbl_p, C.c_int64, C.c_int32, _P(C.c_float)],  # oracle only
+                "refine_spline": [_dbl_p, _P(C.c_int64), C.c_int64, C.c_int32, _P(C.c_int64), _P(C.c_int64), C.c_int64,
+                                  C.c_int64, C.c_int64, _dbl_p],  # oracle only
             }.items():
-                if name == "quantize_positions" and prefix != "orc_":
+                if name in ("quantize_positions", "refine_spline") and prefix != "orc_":
                     continue
                 f = getattr(self.lib, prefix + name)
                 f.restype = C.c_int
@@ -256,6 +260,22 @@ class Backend:
         xyz = np.ascontiguousarray(xyz, dtype=np.float64).reshape(-1, 3)
         out = np.empty(xyz.shape, dtype=np.float32)
         self.call("quantize_positions", _dp(xyz), len(xyz), int(fraction_bits), out.ctypes.data_as(_P(C.c_float)))
+        return out
+
+    def refine_spline(self, coarse_xyz, coarse_ranges, factor, fine_ranges, n_fine, attach=None, fine_init=None,
+                      device=0) -> np.ndarray:
+        """5-sim-genome/src/refine (spline refinement of every chain + nucleolar attachment); [n_fine, 3]."""
+        coarse = np.ascontiguousarray(coarse_xyz, dtype=np.float64).reshape(-1, 3)
+        cr = np.ascontiguousarray(coarse_ranges, dtype=np.int64).reshape(-1, 2)
+        fr = np.ascontiguousarray(fine_ranges, dtype=np.int64).reshape(-1, 2)
+        at = np.ascontiguousarray(attach if attach is not None else np.zeros((0, 2)), dtype=np.int64).reshape(-1, 2)
+        out = np.zeros((int(n_fine), 3)) if fine_init is None else np.array(fine_init, dtype=np.float64).reshape(int(n_fine), 3)
+        i64p = _P(C.c_int64)
+        args = [_dp(coarse), cr.ctypes.data_as(i64p), len(cr), int(factor), fr.ctypes.data_as(i64p),
+                at.ctypes.data_as(i64p), len(at), len(coarse), int(n_fine), _dp(out)]
+        if self.prefix == "bd_":
+            args.append(int(device))
+        self.call("refine_spline", *args)
         return out
 
     def normals(self, seed: int, count: int) -> np.ndarray:

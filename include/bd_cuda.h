@@ -86,6 +86,21 @@ int bd_contact_clear(bd_engine *h, int32_t replica);
 int bd_snapshot_begin(bd_engine *h, int32_t replica, int32_t fraction_bits);
 int bd_snapshot_wait(bd_engine *h, const float **xyz_out, int64_t *count_out);
 
+/* ---- spline refinement between phases ------------------------------------------
+ * Replaces 5-sim-genome/src/refine (refinement.py:11-21, run.py:27-40), a Python/scipy step between the
+ * packing and the relaxation binaries: coarse chain c = rows [coarse_ranges[c][0], coarse_ranges[c][1]) of
+ * coarse_xyz (m >= 4 points) is interpolated by the cubic spline of scipy.interpolate.splprep(k=3, s=0) on
+ * u_i = (i + 1/2)/m, evaluated at (f + 1/2)/(m * factor), and its first fine_ranges[c][1] - fine_ranges[c][0]
+ * points become rows fine_ranges[c][0].. of the output; then every attach[a] = {nor, nuc} copies bead nor to
+ * bead nuc.  Rows of the output no chain covers are left as the caller passed them.  The _device variant
+ * takes DEVICE position arrays (ranges stay on the host) and runs on `cuda_stream` (NULL = default). */
+int bd_refine_spline(const double *coarse_xyz, const int64_t *coarse_ranges, int64_t n_chains, int32_t factor,
+                     const int64_t *fine_ranges, const int64_t *attach, int64_t n_attach, int64_t n_coarse,
+                     int64_t n_fine, double *fine_xyz_out, int32_t device);
+int bd_refine_spline_device(const double *d_coarse, const int64_t *coarse_ranges, int64_t n_chains, int32_t factor,
+                            const int64_t *fine_ranges, const int64_t *attach, int64_t n_attach, int64_t n_coarse,
+                            int64_t n_fine, double *d_fine, void *cuda_stream);
+
 /* All replicas at once through HOST buffers laid out [n_replicas][n_beads][3] (original bead order);
  * with pinned buffers the copies are asynchronous on the engine's stream.  bd_get_all_positions
  * returns after the data has arrived. */

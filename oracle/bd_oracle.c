@@ -1692,3 +1692,78 @@ int orc_quantize_positions(const double *xyz, int64_t count, int32_t fraction_bi
     }
     return 0;
 }
+
+/* refinement.py:11-21 + run.py:27-40.  The not-a-knot cubic spline from its B-spline-free definition:
+ * a dense solve of the (m x m) system in the second derivatives by Gaussian elimination with partial
+ * pivoting -- deliberately a different algorithm from the engine's closed-form elimination. */
+int orc_refine_spline(const double *coarse_xyz, const int64_t *coarse_ranges, int64_t n_chains, int32_t factor,
+                      const int64_t *fine_ranges, const int64_t *attach, int64_t n_attach, int64_t n_coarse,
+                      int64_t n_fine, double *fine_xyz_out)
+{
+    (void) n_coarse;
+    (void) n_fine;
+    for (int64_t c = 0; c < n_chains; c++) {
+        int64_t const beg = coarse_ranges[2 * c], m = coarse_ranges[2 * c + 1] - beg;
+        int64_t const fbeg = fine_ranges[2 * c], fcount = fine_ranges[2 * c + 1] - fbeg;
+        if (m < 4) {
+            return fail("oracle: a coarse chain needs at least 4 points");
+        }
+        double const h = 1.0 / (double) m;
+        double *A = malloc((size_t) m * m * sizeof *A);
+        double *M = malloc((size_t) m * 3 * sizeof *M);
+        for (int d = 0; d < 3; d++) {
+            memset(A, 0, (size_t) m * m * sizeof *A);
+            double *rhs = M + (size_t) d * m;
+            /* row 0 and row m-1: continuity of the third derivative at u_1 and u_{m-2} */
+            A[0] = 1; A[1] = -2; A[2] = 1; rhs[0] = 0;
+            A[(m - 1) * m + m - 3] = 1; A[(m - 1) * m + m - 2] = -2; A[(m - 1) * m + m - 1] = 1; rhs[m - 1] = 0;
+            for (int64_t i = 1; i < m - 1; i++) {
+                A[i * m + i - 1] = 1; A[i * m + i] = 4; A[i * m + i + 1] = 1;
+                const double *y = coarse_xyz + 3 * (beg + i) + d;
+                rhs[i] = 6.0 * (y[-3] - 2.0 * y[0] + y[3]) / (h * h);
+            }
+            for (int64_t col = 0; col < m; col++) {
+                int64_t piv = col;
+                for (int64_t r = col + 1; r < m; r++) {
+                    if (fabs(A[r * m + col]) > fabs(A[piv * m + col])) piv = r;
+                }
+                if (piv != col) {
+                    for (int64_t k = 0; k < m; k++) { double t = A[col * m + k]; A[col * m + k] = A[piv * m + k]; A[piv * m + k] = t; }
+                    double t = rhs[col]; rhs[col] = rhs[piv]; rhs[piv] = t;
+                }
+                for (int64_t r = col + 1; r < m; r++) {
+                    double const f = A[r * m + col] / A[col * m + col];
+                    if (f == 0.0) continue;
+                    for (int64_t k = col; k < m; k++) A[r * m + k] -= f * A[col * m + k];
+                    rhs[r] -= f * rhs[col];
+                }
+            }
+            for (int64_t r = m - 1; r >= 0; r--) {
+                double acc = rhs[r];
+                for (int64_t k = r + 1; k < m; k++) acc -= A[r * m + k] * rhs[k];
+                rhs[r] = acc / A[r * m + r];
+            }
+        }
+        int64_t const n = m * factor;
+        for (int64_t f = 0; f < fcount && f < n; f++) {
+            double const u = ((double) f + 0.5) / (double) n;
+            int64_t i = (int64_t) floor((u - 0.5 * h) / h);
+            i = i < 0 ? 0 : (i > m - 2 ? m - 2 : i);
+            double const t = u - ((double) i + 0.5) * h;
+            for (int d = 0; d < 3; d++) {
+                double const y0 = coarse_xyz[3 * (beg + i) + d], y1 = coarse_xyz[3 * (beg + i + 1) + d];
+                double const m0 = M[(size_t) d * m + i], m1 = M[(size_t) d * m + i + 1];
+                double const b = (y1 - y0) / h - h * (2.0 * m0 + m1) / 6.0;
+                fine_xyz_out[3 * (fbeg + f) + d] = y0 + b * t + 0.5 * m0 * t * t + (m1 - m0) / (6.0 * h) * t * t * t;
+            }
+        }
+        free(A);
+        free(M);
+    }
+    for (int64_t a = 0; a < n_attach; a++) {
+        for (int d = 0; d < 3; d++) {
+            fine_xyz_out[3 * attach[2 * a + 1] + d] = fine_xyz_out[3 * attach[2 * a] + d];
+        }
+    }
+    return 0;
+}
