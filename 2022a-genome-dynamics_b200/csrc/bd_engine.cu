@@ -59,6 +59,12 @@ struct DevBuf {
         count = n;
         return cudaMalloc((void **) &p, std::max<size_t>(n, 1) * sizeof(T));
     }
+    /* keep the allocation when it is already large enough (arrays that are re-uploaded often) */
+    cudaError_t ensure(size_t n)
+    {
+        if (p && count >= n) return cudaSuccess;
+        return alloc(n + n / 4);
+    }
     void release()
     {
         if (p) cudaFree(p);
@@ -88,6 +94,7 @@ struct bd_engine {
     DevBuf<uint2> bondrow;    // bonded partners by thread position, resolved to slots at every rebuild
     DevBuf<BondRow> d_bond_rows;
     uint32_t npad = 0, pstride = 0, bond_deg = 0;
+    bool bond_rows_stale = false;  // bonded pair lists changed since the bond rows were written
     bool bonds_compiled = false;
     int nbond_rows = 0;
     uint8_t bond_slot[BD_MAX_BOND_FF] = {};
@@ -370,10 +377,10 @@ static int upload_topology(bd_engine *h)
     for (uint32_t i = 0; i < n; i++) deg = std::max(deg, start[i + 1] - start[i]);
     CK(cudaStreamSynchronize(h->stream));
     h->bond_deg = deg;
-    CK(h->bondrow.alloc((size_t) deg * h->pstride));
+    CK(h->bondrow.ensure((size_t) deg * h->pstride));
     h->list_verified = false;
-    CK(h->bond_start.alloc(n + 1));
-    CK(h->bond_adj.alloc(adj.size()));
+    CK(h->bond_start.ensure(n + 1));
+    CK(h->bond_adj.ensure(adj.size()));
     CK(cudaMemcpy(h->bond_start.p, start.data(), (n + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice));
     if (!adj.empty()) CK(cudaMemcpy(h->bond_adj.p, adj.data(), adj.size() * sizeof(uint2), cudaMemcpyHostToDevice));
 
@@ -404,7 +411,10 @@ static int upload_topology(bd_engine *h)
         CK(cudaMemcpy(h->bend_energy.p, ten.data(), ten.size() * sizeof(double), cudaMemcpyHostToDevice));
         CK(cudaMemcpy(h->bend_ff.p, tff.data(), tff.size(), cudaMemcpyHostToDevice));
     }
-    return request_rebuild(h);  // the slot-space bond rows are refilled by the rebuild chain
+    // the slot-space bond rows are rewritten behind the next rebuild chain (k_bond_rows); the Verlet rows
+    // do not depend on the bonded lists, so no list build is asked for
+    h->bond_rows_stale = true;
+    return 0;
 }
 
 // ---- lifetime ------------------------------------------------------------------------------------
@@ -1107,6 +1117,13 @@ static int enqueue_rebuild_chain(bd_engine *h)
     k_rows<<<row_blocks, ROWS_BLOCK, 0, st>>>(A);
     k_balance<<<std::min(h->chunks * h->replicas, 148u * 16u), BAL_TILE, 0, st>>>(A);
     h->launches += 11;
+    if (h->bond_rows_stale) {
+        if (h->bond_deg) {
+            k_bond_rows<<<std::min(h->chunks * h->replicas, 148u * 16u), BAL_TILE, 0, st>>>(A);
+            h->launches += 1;
+        }
+        h->bond_rows_stale = false;
+    }
     CK(cudaGetLastError());
     return 0;
 }

@@ -592,6 +592,30 @@ __global__ void __launch_bounds__(BAL_TILE) k_balance(NlistArrays A)
     }
 }
 
+/* The slot-space bond rows alone, for the current assignment of beads to thread positions: what k_balance
+ * writes at a list build, redone when only the bonded pair lists changed (bd_set_bond_pairs: the glue /
+ * loop lists of 3-sim-1kb are edited every few steps, the Verlet rows are not affected). */
+__global__ void __launch_bounds__(BAL_TILE) k_bond_rows(NlistArrays A)
+{
+    uint32_t const chunks = A.npad / BAL_TILE;
+    for (uint32_t tile = blockIdx.x; tile < chunks * A.replicas; tile += gridDim.x) {
+        uint32_t const chunk = tile % chunks, replica = tile / chunks;
+        uint32_t const base = replica * A.n + chunk * BAL_TILE;
+        uint32_t const pbase = replica * A.npad + chunk * BAL_TILE;
+        bool const live = chunk * BAL_TILE + threadIdx.x < A.n;
+        uint32_t k = 0;
+        if (live) {
+            uint32_t const from = A.order[base + threadIdx.x];
+            uint32_t const oi = w_orig(A.bpos[base + from].w);
+            for (uint32_t c = A.bond_start[oi]; c < A.bond_start[oi + 1] && k < A.bond_deg; c++, k++) {
+                uint2 const adj = A.bond_adj[c];
+                A.bondrow[(size_t) k * A.pstride + pbase + threadIdx.x] = make_uint2(A.slot_of[replica * A.n + adj.x], adj.y);
+            }
+        }
+        for (; k < A.bond_deg; k++) A.bondrow[(size_t) k * A.pstride + pbase + threadIdx.x] = make_uint2(0xffffffffu, 0u);
+    }
+}
+
 /* Verlet list as unordered pairs of original indices (validation, get_neighbor_list) */
 __global__ void __launch_bounds__(NL_BLOCK) k_export_pairs(NlistArrays A, uint32_t replica,
                                                            uint32_t *pairs_out,

@@ -513,3 +513,30 @@ def test_dynamic_pair_lists_on_the_device(engine, oracle):
         systems[0].set_bond_pairs(ids[0][0], np.array([[0, n]], np.uint32))
     for e in systems:
         e.close()
+
+
+@pytest.mark.gpu
+def test_replacing_a_pair_list_does_not_rebuild_the_verlet_list(engine):
+    """bd_set_bond_pairs refreshes the slot-space bond rows only (k_bond_rows): the number of list builds
+    stays what the displacement criterion asks for, and the forces are those of a fresh engine."""
+    s = sc.chromatin_1kb(n_chains=4, chain_len=150)
+    n = s.n
+    spring = bd.pair_table(s.ntypes, lambda ti, tj: [bd.spring(40.0, 0.3)])
+    rng = np.random.default_rng(2)
+    e, _ = build(engine, s)
+    ff = e.add_bond_ff(spring, np.zeros((0, 2), np.uint32))
+    e.step(3, s.timestep, s.temperature, seed=1)
+    before = e.get_counters().list_rebuilds
+    for k in range(10):
+        i = rng.integers(0, n - 40, size=20)
+        pairs = np.stack([i, i + rng.integers(2, 40, size=20)], axis=1).astype(np.uint32)
+        e.set_bond_pairs(ff, pairs)
+        f = e.compute_forces()
+    assert e.get_counters().list_rebuilds == before
+    fresh, _ = build(engine, s)
+    ff2 = fresh.add_bond_ff(spring, pairs)
+    fresh.set_positions(e.get_positions())
+    assert rel_force_error(f, fresh.compute_forces()) <= FORCE_TOL
+    assert ff2 == ff
+    e.close()
+    fresh.close()
