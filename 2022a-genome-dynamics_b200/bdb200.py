@@ -178,6 +178,8 @@ ENGINE_ONLY = {
     "contact_clear": [C.c_void_p, C.c_int32],
     "refine_spline": [_dbl_p, _P(C.c_int64), C.c_int64, C.c_int32, _P(C.c_int64), _P(C.c_int64), C.c_int64, C.c_int64,
                       C.c_int64, _dbl_p, C.c_int32],
+    "search_pairs": [C.c_void_p, C.c_int32, C.c_double, C.c_int32, _u32_p, C.c_int64, C.POINTER(C.c_int64)],
+    "pair_distances": [C.c_void_p, C.c_int32, _u32_p, C.c_int64, C.c_int32, _dbl_p],
     "snapshot_begin": [C.c_void_p, C.c_int32, C.c_int32],
     "snapshot_wait": [C.c_void_p, C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.c_int64)],
 }
@@ -551,6 +553,25 @@ class System:
         if count.value:
             self.b.call("contact_accumulate", self.h, int(replica), out.ctypes.data_as(C.POINTER(C.c_uint32)),
                         int(count.value), C.byref(count))
+        return out
+
+    # pair search / pair distances on the resident positions (glue_simulator.cpp:35-80 of 3-sim-1kb)
+    def search_pairs(self, distance: float, use_box: bool = True, replica: int = 0) -> np.ndarray:
+        """[m, 2] uint32 pairs (i < j) within `distance`, sorted by (i, j)."""
+        count = C.c_int64(0)
+        cap = max(1024, 8 * self.n)
+        while True:
+            out = np.empty((cap, 2), dtype=np.uint32)
+            self.b.call("search_pairs", self.h, int(replica), float(distance), int(bool(use_box)),
+                        out.ctypes.data_as(_u32_p), cap, C.byref(count))
+            if count.value <= cap:
+                return out[: count.value]
+            cap = count.value
+
+    def pair_distances(self, pairs, min_image: bool = False, replica: int = 0) -> np.ndarray:
+        p = np.ascontiguousarray(pairs, dtype=np.uint32).reshape(-1, 2)
+        out = np.empty(len(p))
+        self.b.call("pair_distances", self.h, int(replica), p.ctypes.data_as(_u32_p), len(p), int(bool(min_image)), _dp(out))
         return out
 
     # single-precision snapshots (simulation_store.cc:253-276 of 5-sim-genome)

@@ -1534,31 +1534,39 @@ extern "C" int bd_contact_clear(bd_engine *h, int32_t replica)
     return 0;
 }
 
-extern "C" int bd_contact_update(bd_engine *h, int32_t replica, double distance)
+/* Pairs of `replica`'s CURRENT configuration within `distance`, left in h->contact_pairs on the device
+ * (unordered, i < j).  A second engine acts as the searcher: list radius = distance, the reference's fp64
+ * test.  use_box = 0 searches in an open box whatever the simulation's unit cell is (contact_map.cc:64),
+ * 1 in the simulation's own box (the searcher glue_simulator.cpp:42 keeps). */
+static int search_current(bd_engine *h, int32_t replica, double distance, int use_box, unsigned long long *found_out)
 {
-    NEED(h);
-    if (replica < 0 || (uint32_t) replica >= h->replicas) return fail("bd_contact_update: bad replica");
-    if (!(distance > 0)) return fail("bd_contact_update: the contact distance must be positive");
+    *found_out = 0;
     if (h->n < 2) return 0;
     cudaStream_t const st = h->stream;
     bd_engine *q = h->contact_search;
+    int const kind = use_box ? h->hp.box_kind : BD_BOX_OPEN;
+    double const unit[3] = {1, 1, 1};
+    const double *period = kind == BD_BOX_PERIODIC ? h->hp.period : unit;
+    bd_term none;
+    std::memset(&none, 0, sizeof none);
     if (!q) {
         if (bd_create(h->n, 1, h->device, &q)) return 1;
         h->contact_search = q;
-        double const unit[3] = {1, 1, 1};
-        bd_term none;
-        std::memset(&none, 0, sizeof none);
         int32_t ff = -1;
-        // open box whatever the simulation's unit cell is (contact_map.cc:64); rows hold exactly the contacts
-        if (bd_set_box(q, BD_BOX_OPEN, unit) || bd_set_option(q, "verlet_factor", 1.0)
+        // a list radius of exactly the distance: the rows hold precisely the wanted pairs
+        if (bd_set_box(q, kind, period) || bd_set_option(q, "verlet_factor", 1.0)
             || bd_add_pair_ff(q, 1, &none, distance, nullptr, &ff))
             return 1;
         h->contact_distance = distance;
-    } else if (distance != h->contact_distance) {
-        bd_term none;
-        std::memset(&none, 0, sizeof none);
-        if (bd_update_pair_ff(q, 0, &none, distance)) return 1;
-        h->contact_distance = distance;
+    } else {
+        if (q->hp.box_kind != kind || (kind == BD_BOX_PERIODIC && std::memcmp(q->hp.period, period, 3 * sizeof(double)) != 0))
+            if (bd_set_box(q, kind, period)) return 1;
+        if (distance != h->contact_distance) {
+            // the engine keeps a list whose radius still covers the new cutoff; the searcher wants rows at
+            // exactly the new distance
+            if (bd_update_pair_ff(q, 0, &none, distance) || request_rebuild(q)) return 1;
+            h->contact_distance = distance;
+        }
     }
     if (bd_set_stream(q, st)) return 1;
     // positions of the replica in original order, device to device
@@ -1569,7 +1577,6 @@ extern "C" int bd_contact_update(bd_engine *h, int32_t replica, double distance)
     if (bd_set_positions_device(q, h->xyz_stage.p)) return 1;
     if (prepare_list(q)) return 1;
 
-    // the contacts of this configuration
     DControl c;
     CK(cudaMemcpy(&c, q->ctl.p, sizeof c, cudaMemcpyDeviceToHost));
     size_t const cap = (size_t) (c.listed_entries / 2) + 1;  // the rows are a superset by the shadow bound
@@ -1582,7 +1589,19 @@ extern "C" int bd_contact_update(bd_engine *h, int32_t replica, double distance)
     unsigned long long found = 0;
     CK(cudaMemcpyAsync(&found, q->pair_count.p, sizeof found, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
-    if (found > cap) return fail("bd_contact_update: pair export overflow");
+    if (found > cap) return fail("bd: pair export overflow in the searcher");
+    *found_out = found;
+    return 0;
+}
+
+extern "C" int bd_contact_update(bd_engine *h, int32_t replica, double distance)
+{
+    NEED(h);
+    if (replica < 0 || (uint32_t) replica >= h->replicas) return fail("bd_contact_update: bad replica");
+    if (!(distance > 0)) return fail("bd_contact_update: the contact distance must be positive");
+    cudaStream_t const st = h->stream;
+    unsigned long long found = 0;
+    if (search_current(h, replica, distance, 0, &found)) return 1;
     if (found == 0) return 0;
 
     // merge: [accumulated keys + counts | new keys + ones] -> sort by key -> sum counts of equal keys
@@ -1739,5 +1758,100 @@ extern "C" int bd_snapshot_wait(bd_engine *h, const float **xyz_out, int64_t *co
     h->snap_pending = false;
     if (xyz_out) *xyz_out = h->snap_host;
     if (count_out) *count_out = (int64_t) h->snap_count;
+    return 0;
+}
+
+// ---- pair search and pair distances on the resident positions -----------------------------------
+//
+// What 3-sim-1kb's kinetic models ask of the positions every update (glues/glue_simulator.cpp:35-80): the
+// pairs within the binding distance (search) and the current distance of every glued pair (unbond).  Both
+// are answered from the device-resident positions; only pairs and distances cross PCIe.
+
+__global__ void k_unpack_keys(const unsigned long long *keys, unsigned long long count, uint32_t *pairs)
+{
+    unsigned long long const k = (unsigned long long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= count) return;
+    pairs[2 * k] = (uint32_t) (keys[k] >> 32);
+    pairs[2 * k + 1] = (uint32_t) keys[k];
+}
+
+__global__ void k_pair_distances(const bead4 *pos, const uint32_t *slot_of, uint32_t base, const uint32_t *pairs, uint32_t m,
+                                 const DParams *params, int min_image, double *out)
+{
+    uint32_t const k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= m) return;
+    bead4 const a = pos[slot_of[base + pairs[2 * k]]], b = pos[slot_of[base + pairs[2 * k + 1]]];
+    d3 r;
+    if (min_image) {
+        r = displacement(*params, a.x, a.y, a.z, b.x, b.y, b.z);
+    } else {
+        r.x = __dsub_rn(a.x, b.x);
+        r.y = __dsub_rn(a.y, b.y);
+        r.z = __dsub_rn(a.z, b.z);
+    }
+    out[k] = sqrt(sqnorm_exact(r.x, r.y, r.z));  // md::vector::norm (MD/basic_types/point.hpp:120-134)
+}
+
+extern "C" int bd_search_pairs(bd_engine *h, int32_t replica, double distance, int32_t use_box, uint32_t *pairs_out,
+                               int64_t cap, int64_t *count_out)
+{
+    NEED(h);
+    if (replica < 0 || (uint32_t) replica >= h->replicas) return fail("bd_search_pairs: bad replica");
+    if (!(distance > 0) || cap < 0 || !count_out) return fail("bd_search_pairs: bad arguments");
+    cudaStream_t const st = h->stream;
+    unsigned long long found = 0;
+    if (search_current(h, replica, distance, use_box != 0, &found)) return 1;
+    *count_out = (int64_t) found;
+    size_t const m = std::min<size_t>((size_t) found, (size_t) cap);
+    if (found == 0 || m == 0) return 0;
+    // sorted by (i, j): the device emits the pairs in no particular order
+    DevBuf<unsigned long long> keys, sorted;
+    DevBuf<uint32_t> ones;  // k_contact_keys also writes a count column
+    CK(keys.alloc(found));
+    CK(sorted.alloc(found));
+    CK(ones.alloc(found));
+    k_contact_keys<<<(unsigned) ((found + 255) / 256), 256, 0, st>>>(h->contact_pairs.p, found, keys.p, ones.p);
+    size_t need = 0;
+    CK(cub::DeviceRadixSort::SortKeys(nullptr, need, keys.p, sorted.p, (int) found, 0, 64, st));
+    if (h->contact_temp.count < need) CK(h->contact_temp.alloc(need + need / 4));
+    size_t bytes = h->contact_temp.count;
+    CK(cub::DeviceRadixSort::SortKeys(h->contact_temp.p, bytes, keys.p, sorted.p, (int) found, 0, 64, st));
+    k_unpack_keys<<<(unsigned) ((found + 255) / 256), 256, 0, st>>>(sorted.p, found, h->contact_pairs.p);
+    h->launches += 3;
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(pairs_out, h->contact_pairs.p, 2 * m * sizeof(uint32_t), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    keys.release();
+    sorted.release();
+    ones.release();
+    if (e != cudaSuccess) return fail(std::string("bd_search_pairs: ") + cudaGetErrorString(e));
+    return 0;
+}
+
+extern "C" int bd_pair_distances(bd_engine *h, int32_t replica, const uint32_t *pairs, int64_t m, int32_t min_image,
+                                 double *out)
+{
+    NEED(h);
+    if (replica < 0 || (uint32_t) replica >= h->replicas) return fail("bd_pair_distances: bad replica");
+    if (m < 0 || (m > 0 && (!pairs || !out))) return fail("bd_pair_distances: bad arguments");
+    for (int64_t k = 0; k < 2 * m; k++)
+        if (pairs[k] >= h->n) return fail("bd_pair_distances: bead index out of range");
+    if (m == 0) return 0;
+    if (upload_params(h)) return 1;
+    DevBuf<uint32_t> d_pairs;
+    DevBuf<double> d_out;
+    CK(d_pairs.alloc(2 * (size_t) m));
+    CK(d_out.alloc((size_t) m));
+    cudaError_t e = cudaMemcpyAsync(d_pairs.p, pairs, 2 * (size_t) m * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream);
+    k_pair_distances<<<blocks_for((size_t) m, 256), 256, 0, h->stream>>>(h->pos[h->cur].p, h->slot_of.p, (uint32_t) replica * h->n,
+                                                                         d_pairs.p, (uint32_t) m, h->d_params.p, min_image != 0,
+                                                                         d_out.p);
+    h->launches++;
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_out.p, (size_t) m * sizeof(double), cudaMemcpyDeviceToHost, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    d_pairs.release();
+    d_out.release();
+    if (e != cudaSuccess) return fail(std::string("bd_pair_distances: ") + cudaGetErrorString(e));
     return 0;
 }

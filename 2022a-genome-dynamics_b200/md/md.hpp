@@ -64,6 +64,7 @@
 #ifndef MD_B200_PREFIX
 #define MD_B200_PREFIX bd_
 #define MD_B200_HANDLE_NAME bd_engine
+#define MD_B200_ENGINE 1  // bound to libbd_b200.so: the engine-only entry points of bd_cuda.h exist
 #else
 #define MD_B200_HANDLE_NAME md_b200_backend_handle
 #endif
@@ -1816,6 +1817,61 @@ namespace md
         md::scalar dcut_;
         std::vector<md::point> points_;
     };
+
+#ifdef MD_B200_ENGINE
+    // ---- extension over micromd: questions about the device-resident positions ----------------------
+    // 3-sim-1kb's kinetic glue model (src/simulation/glues/glue_simulator.cpp:35-80) asks two things of the
+    // positions at every update: the pairs within the binding distance and the current length of every
+    // glued pair.  Answered here without bringing the positions to the host.
+    namespace b200
+    {
+        extern "C" {
+        int bd_search_pairs(bd_engine* h, std::int32_t replica, double distance, std::int32_t use_box, std::uint32_t* pairs_out,
+                            std::int64_t cap, std::int64_t* count_out);
+        int bd_pair_distances(bd_engine* h, std::int32_t replica, const std::uint32_t* pairs, std::int64_t m,
+                              std::int32_t min_image, double* out);
+        }
+
+        // pairs (i < j) within `distance`, sorted; use_box: the system's unit cell (md::neighbor_searcher<periodic_box>)
+        // or an open box (md::neighbor_searcher<open_box>)
+        inline std::vector<std::pair<md::index, md::index>> search_pairs(md::system& system, md::scalar distance, bool use_box = true)
+        {
+            std::vector<std::pair<md::index, md::index>> out;
+            if (system.particle_count() < 2) return out;
+            auto& b = system.b200_binding();
+            b.sync(true);
+            std::int64_t cap = std::int64_t(system.particle_count()) * 16, count = 0;
+            std::vector<std::uint32_t> pairs;
+            for (;;) {
+                pairs.resize(std::size_t(cap) * 2);
+                check(bd_search_pairs(b.handle(), 0, distance, use_box ? 1 : 0, pairs.data(), cap, &count), "search_pairs");
+                if (count <= cap) break;
+                cap = count;
+            }
+            out.reserve(std::size_t(count));
+            for (std::int64_t k = 0; k < count; k++) out.emplace_back(pairs[2 * k], pairs[2 * k + 1]);
+            return out;
+        }
+
+        // |x_i - x_j| of every pair, through the box's shortest displacement when min_image is set
+        template<typename PairRange>
+        std::vector<md::scalar> pair_distances(md::system& system, PairRange const& pair_range, bool min_image = false)
+        {
+            std::vector<std::uint32_t> pairs;
+            for (auto const& p : pair_range) {
+                pairs.push_back(std::uint32_t(std::get<0>(p)));
+                pairs.push_back(std::uint32_t(std::get<1>(p)));
+            }
+            std::vector<md::scalar> out(pairs.size() / 2);
+            if (out.empty()) return out;
+            auto& b = system.b200_binding();
+            b.sync(true);
+            check(bd_pair_distances(b.handle(), 0, pairs.data(), std::int64_t(out.size()), min_image ? 1 : 0, out.data()),
+                  "pair_distances");
+            return out;
+        }
+    }
+#endif
 }
 
 #endif  // MD_B200_MD_HPP

@@ -73,6 +73,19 @@ int bd_contact_update(bd_engine *h, int32_t replica, double distance);
 int bd_contact_accumulate(bd_engine *h, int32_t replica, uint32_t *triplets_out, int64_t cap, int64_t *count_out);
 int bd_contact_clear(bd_engine *h, int32_t replica);
 
+/* ---- pair search and pair distances on the resident positions -------------------
+ * What 3-sim-1kb's kinetic glue model asks of the positions at every update
+ * (src/simulation/glues/glue_simulator.cpp:35-80): `_searcher.search` -- all pairs within the binding
+ * distance -- and the current distance of every glued pair (unbond: r_ij.norm() > max_distance).  Both are
+ * answered from the device-resident positions, so an update moves pairs and distances over PCIe, not all
+ * positions.  bd_search_pairs writes up to `cap` pairs (i < j) SORTED by (i, j) and the total to *count_out;
+ * use_box = 1 searches in the simulation's box (md::neighbor_searcher<periodic_box>), 0 in an open box.
+ * The pair set is the reference's (fp64 test r^2 <= distance^2).  bd_pair_distances writes |x_i - x_j|,
+ * through the box's shortest displacement when min_image is set. */
+int bd_search_pairs(bd_engine *h, int32_t replica, double distance, int32_t use_box, uint32_t *pairs_out, int64_t cap,
+                    int64_t *count_out);
+int bd_pair_distances(bd_engine *h, int32_t replica, const uint32_t *pairs, int64_t m, int32_t min_image, double *out);
+
 /* ---- single-precision snapshots -------------------------------------------------
  * The drivers' stores write float positions: 5-sim-genome quantises to 16 fraction bits on the host,
  * quantize(val, bits) = nearbyint(float(val) * 2^bits) / 2^bits in float arithmetic

@@ -17,7 +17,9 @@
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
+#include <algorithm>
 #include <functional>
+#include <iterator>
 #include <memory>
 #include <random>
 #include <string>
@@ -545,6 +547,34 @@ namespace
         md::simulate_brownian_dynamics(system, {.temperature = 0, .timestep = 1e-5, .steps = 20});
         print_points(name(".pos").c_str(), system.view_positions(), 5);
         std::printf("%s.energy_end %.17g\n", tag, system.compute_potential_energy());
+
+        // what the kinetic glue model asks of the positions at every update (glues/glue_simulator.cpp:35-80):
+        // the pairs within the binding distance and the current length of every glued pair
+        std::vector<std::pair<md::index, md::index>> near;
+        std::vector<md::scalar> lengths;
+        bool asked_device = false;
+#ifdef MD_B200_ENGINE
+        if (device_lists) {
+            near = md::b200::search_pairs(system, 0.4);
+            lengths = md::b200::pair_distances(system, glues->pairs, true);
+            asked_device = true;
+        }
+#endif
+        if (!asked_device) {
+            md::neighbor_searcher<md::periodic_box> searcher{box, 0.4};
+            searcher.set_points(system.view_positions());
+            searcher.search(std::back_inserter(near));
+            std::sort(near.begin(), near.end());
+            auto const positions = system.view_positions();
+            for (auto const& pair : glues->pairs)
+                lengths.push_back(box.shortest_displacement(positions[pair.first], positions[pair.second]).norm());
+        }
+        double checksum = 0;
+        for (auto const& pair : near) checksum += double(pair.first) * 1009 + double(pair.second);
+        std::printf("%s.near %zu %.17g\n", tag, near.size(), checksum);
+        std::printf("%s.gluelen", tag);
+        for (md::scalar l : lengths) std::printf(" %.17g", l);
+        std::printf("\n");
     }
 }
 

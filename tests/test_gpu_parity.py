@@ -540,3 +540,35 @@ def test_replacing_a_pair_list_does_not_rebuild_the_verlet_list(engine):
     assert ff2 == ff
     e.close()
     fresh.close()
+
+
+@pytest.mark.gpu
+def test_pair_search_and_distances_on_resident_positions(engine, oracle):
+    """bd_search_pairs / bd_pair_distances: what glue_simulator.cpp:35-80 asks of the positions, answered
+    on the device -- pair sets equal to the reference searcher's on the same coordinates, in sorted order."""
+    s = sc.chromatin_1kb(n_chains=5, chain_len=160)
+    L = np.asarray(s.period)
+    e, _ = build(engine, s)
+    for k in range(3):
+        e.step(12, s.timestep, s.temperature, seed=4, first_step=1 + 12 * k)
+        x = e.get_positions()
+        for dist in (0.33, 0.5):
+            boxed = e.search_pairs(dist, use_box=True)
+            want = sort_pairs(oracle.nsearch_pairs(bd.BOX_PERIODIC, L, s.n, dist, x))
+            assert np.array_equal(boxed, want) and np.array_equal(want, sort_pairs(brute_pairs(x, dist, L)))
+            opened = e.search_pairs(dist, use_box=False)
+            assert np.array_equal(opened, sort_pairs(brute_pairs(x, dist)))
+            assert len(boxed) >= len(opened) > 0
+        pairs = boxed[:: max(1, len(boxed) // 50)]
+        d = x[pairs[:, 0]] - x[pairs[:, 1]]
+        assert np.array_equal(e.pair_distances(pairs), np.sqrt(d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1] + d[:, 2] * d[:, 2]))
+        dm = d - np.rint(d * (1 / L)) * L
+        got = e.pair_distances(pairs, min_image=True)
+        assert np.abs(got - np.sqrt((dm * dm).sum(axis=1))).max() <= 1e-15 and (got <= 0.5 * (1 + 1e-12)).all()
+    # the contact map shares the searcher: switching between the two uses keeps both right
+    e.contact_update(0.33)
+    assert np.array_equal(e.contact_accumulate()[:, :2], sort_pairs(brute_pairs(e.get_positions(), 0.33)))
+    assert e.pair_distances(np.zeros((0, 2), np.uint32)).shape == (0,)
+    with pytest.raises(bd.BackendError):
+        e.pair_distances(np.array([[0, s.n]], np.uint32))
+    e.close()
