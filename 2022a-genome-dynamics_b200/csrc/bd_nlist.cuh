@@ -453,7 +453,8 @@ __global__ void __launch_bounds__(ROWS_BLOCK) k_rows(NlistArrays A)
             }
             uint32_t const rem = qn - groups * ROW_PAD;
             if (!last) {
-                for (uint32_t k = 0; k < rem; k++) queue[k * ROWS_BLOCK] = queue[(groups * ROW_PAD + k) * ROWS_BLOCK];
+                if (groups)
+                    for (uint32_t k = 0; k < rem; k++) queue[k * ROWS_BLOCK] = queue[(groups * ROW_PAD + k) * ROWS_BLOCK];
             } else if (rem) {
                 // the last group is padded with the sentinel slot: the step kernel reads whole groups
                 const uint32_t *q4 = queue + groups * ROW_PAD * ROWS_BLOCK;
@@ -466,10 +467,10 @@ __global__ void __launch_bounds__(ROWS_BLOCK) k_rows(NlistArrays A)
             }
             qn = rem;
         };
-        auto consider = [&](uint32_t jj, const float4 &q) {
+        auto consider = [&](uint32_t jj, const float4 &q, bool on) {
             float const d2 = periodic ? shadow_dist2<BD_BOX_PERIODIC>(ms, q, scale)
                                       : shadow_dist2<BD_BOX_OPEN>(ms, q, scale);
-            if (d2 <= filter2 && jj != s) {
+            if (on && d2 <= filter2 && jj != s) {
                 queue[qn * ROWS_BLOCK] = jj;
                 qn++;
             }
@@ -493,20 +494,21 @@ __global__ void __launch_bounds__(ROWS_BLOCK) k_rows(NlistArrays A)
                     ne = A.cell_start[key + 1];
                 }
             }
-            // four candidates of a run are requested together: the walk is bound by the latency of these loads
-            if (e - j >= 4) {
-                float4 const q0 = A.shadow[j], q1 = A.shadow[j + 1], q2 = A.shadow[j + 2], q3 = A.shadow[j + 3];
-                consider(j, q0);
-                consider(j + 1, q1);
-                consider(j + 2, q2);
-                consider(j + 3, q3);
-                j += 4;
-            } else {
-                float4 const q = A.shadow[j];
-                consider(j, q);
-                j++;
-            }
-            if (qn > ROWS_QUEUE - 4) flush(false);
+            // Up to four candidates of the run per iteration, requested together (the walk is bound by
+            // the latency of these loads).  One path for every lane: a run with fewer than four beads left
+            // repeats its first candidate with the test switched off -- two code paths here had the lanes
+            // of a warp take turns (15 of 32 active).
+            uint32_t const left = e - j;
+            uint32_t const j1 = left > 1u ? j + 1 : j, j2 = left > 2u ? j + 2 : j, j3 = left > 3u ? j + 3 : j;
+            float4 const q0 = A.shadow[j], q1 = A.shadow[j1], q2 = A.shadow[j2], q3 = A.shadow[j3];
+            consider(j, q0, true);
+            consider(j1, q1, left > 1u);
+            consider(j2, q2, left > 2u);
+            consider(j3, q3, left > 3u);
+            j += left < 4u ? left : 4u;
+            // write-outs are taken together by the lanes that are here: whoever has whole groups queued
+            // writes them when any lane must (early write-outs are always safe)
+            if (__any_sync(__activemask(), qn > ROWS_QUEUE - 4)) flush(false);
         }
         flush(true);
         A.nnbr[s] = count;
