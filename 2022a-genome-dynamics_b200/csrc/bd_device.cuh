@@ -115,7 +115,7 @@ struct DControl {
     unsigned long long max_disp2_bits;  // bits of max_i |x_i - x_i(build)|^2, kept by the step kernel
     unsigned long long listed_entries;  // sum of row lengths at the last build (2 x listed pairs)
     unsigned long long bbox_lo[3], bbox_hi[3];  // order-preserving encodings of the bounding box
-    DGrid grid;
+    alignas(16) DGrid grid;                     // copied to shared memory in 16-byte pieces
 };
 
 /* forcefield selection for compute_forces / compute_energy of a single forcefield */

@@ -159,8 +159,8 @@ __device__ __forceinline__ double compiled_pair_scalar(const PairRow &row, doubl
 constexpr int HIT_CAP = 16;  // near-hits buffered per bead between the two phases of the pair walk
 
 struct StepShared {
-    DParams P;
-    DGrid G;
+    alignas(16) DParams P;
+    alignas(16) DGrid G;
     float filter2;  // widened cutoff^2 of the shadow pre-filter
     uint32_t hits[HIT_CAP][STEP_BLOCK];
     double wall_red[STEP_BLOCK / 32][BD_MAX_WALL_FF][WALL_STATS];
@@ -434,23 +434,21 @@ __device__ __forceinline__ void wall_force(const StepArrays &A, const DWall &wf,
     }
 }
 
+/* block-wide copy in 16-byte pieces (both sides 16-byte aligned, size a multiple of 16) */
+__device__ __forceinline__ void copy16(void *dst, const void *src, uint32_t bytes)
+{
+    for (uint32_t i = threadIdx.x; i < bytes / 16u; i += blockDim.x) ((uint4 *) dst)[i] = ((const uint4 *) src)[i];
+}
+
 template <int PROG>
 __device__ __forceinline__ void load_shared(StepShared &sh, const StepArrays &A, Select sel)
 {
-    for (uint32_t i = threadIdx.x; i < sizeof(DParams) / 4; i += blockDim.x)
-        ((uint32_t *) &sh.P)[i] = ((const uint32_t *) A.params)[i];
-    for (uint32_t i = threadIdx.x; i < sizeof(DGrid) / 4; i += blockDim.x)
-        ((uint32_t *) &sh.G)[i] = ((const uint32_t *) &A.ctl->grid)[i];
-    if (PROG != PROG_GENERIC) {
-        uint32_t const words = A.ntypes2 * (sizeof(PairRow) / 4);
-        for (uint32_t i = threadIdx.x; i < words; i += blockDim.x)
-            ((uint32_t *) dyn_smem)[i] = ((const uint32_t *) A.pair_rows)[i];
-    }
-    if (A.bonds_compiled) {
-        uint32_t *dst = (uint32_t *) (dyn_smem + A.ntypes2 * sizeof(PairRow));
-        uint32_t const words = (uint32_t) A.nbond_rows * (sizeof(BondRow) / 4);
-        for (uint32_t i = threadIdx.x; i < words; i += blockDim.x) dst[i] = ((const uint32_t *) A.bond_rows)[i];
-    }
+    static_assert(sizeof(DParams) % 16 == 0 && sizeof(DGrid) % 16 == 0, "copied in 16-byte pieces");
+    copy16(&sh.P, A.params, sizeof(DParams));
+    copy16(&sh.G, &A.ctl->grid, sizeof(DGrid));
+    if (PROG != PROG_GENERIC) copy16(dyn_smem, A.pair_rows, A.ntypes2 * (uint32_t) sizeof(PairRow));
+    if (A.bonds_compiled)
+        copy16(dyn_smem + A.ntypes2 * sizeof(PairRow), A.bond_rows, (uint32_t) A.nbond_rows * (uint32_t) sizeof(BondRow));
     __syncthreads();
     if (threadIdx.x == 0) {
         // widened cutoff of the pre-filter: r <= dcut implies r_shadow <= dcut + shadow_eps / 4, and the
