@@ -104,6 +104,8 @@ struct bd_engine {
     DevBuf<DTerm> d_terms;
     DevBuf<PairRow> d_pair_rows;
     int prog = PROG_GENERIC;   // specialised pair program of the current tables (upload_params)
+    bool k2_uniform = false;   // ... whose rows all share k2a / k2b
+    double k2a = 0, k2b = 0;
     int fast_ff = 0;
     bool specialize = true;
     DevBuf<double> force, wprev, xyz_stage, wall_partial, wall_out, energy_partial, energy_out, dt_prev, dt_last;
@@ -244,7 +246,7 @@ static int compile_pair_program(bd_engine *h, std::vector<PairRow> &rows)
     if (nterms > 2) return 0;
     const DTerm *tab = h->hterms.data() + h->pair[ff].term_off;
     bool second = false;
-    rows.assign((size_t) T * T, PairRow{0, 0, 0, 0});
+    rows.assign((size_t) T * T, PairRow{0, 0, 0, 0});  // {ca, cb, k2a, k2b}
     for (int c = 0; c < T * T; c++) {
         for (int k = 0; k < nterms; k++) {
             const DTerm &t = tab[c * nterms + k];
@@ -267,6 +269,22 @@ static int compile_pair_program(bd_engine *h, std::vector<PairRow> &rows)
             if (std::memcmp(&rows[a * T + b], &rows[b * T + a], sizeof(PairRow)) != 0) return 0;
     h->prog = second ? PROG_SC23_SC83 : PROG_SC23;
     h->fast_ff = ff;
+    // rows with a zero coefficient do not care about their k2 (0 * g^2 is +0 for any finite g)
+    h->k2_uniform = true;
+    h->k2a = h->k2b = 0.0;
+    bool seen_a = false, seen_b = false;
+    for (const PairRow &r : rows) {
+        if (r.ca != 0.0) {
+            if (seen_a && r.k2a != h->k2a) h->k2_uniform = false;
+            h->k2a = r.k2a;
+            seen_a = true;
+        }
+        if (r.cb != 0.0) {
+            if (seen_b && r.k2b != h->k2b) h->k2_uniform = false;
+            h->k2b = r.k2b;
+            seen_b = true;
+        }
+    }
     return 0;
 }
 
@@ -1038,6 +1056,9 @@ static StepArrays step_arrays(bd_engine *h)
     A.pair_rows = h->d_pair_rows.p;
     A.ntypes2 = (uint32_t) (h->hp.ntypes * h->hp.ntypes);
     A.fast_ff = h->fast_ff;
+    A.k2_uniform = h->prog != PROG_GENERIC && h->k2_uniform;
+    A.k2a = h->k2a;
+    A.k2b = h->k2b;
     A.n = h->n;
     A.replicas = h->replicas;
     A.ntot = h->ntot;

@@ -64,6 +64,8 @@ struct StepArrays {
     int32_t any_bend;                   // some bending forcefield exists
     uint32_t ntypes2;             // rows in pair_rows
     int32_t fast_ff;              // the pair forcefield the specialised program evaluates
+    int32_t k2_uniform;           // every row of pair_rows has the same k2a and k2b: taken from here
+    double k2a, k2b;
     uint32_t n, replicas, ntot, chunks;
 };
 
@@ -113,9 +115,12 @@ enum PairProgram {
     PROG_COUNT = 3
 };
 
-/* one row of a compiled pair table: c = factor * P * Q * energy * k2, k2 = 1 / diameter^2 */
+/* one row of a compiled pair table: c = factor * P * Q * energy * k2, k2 = 1 / diameter^2.  In every
+ * reference driver the diameters are global (only the factors depend on the bead classes), so the k2 of
+ * all rows are equal: the kernel then takes them from the launch parameters and reads 16 bytes per
+ * evaluated pair from shared memory instead of 32 (StepArrays::k2_uniform). */
 struct __align__(16) PairRow {
-    double k2a, ca, k2b, cb;
+    double ca, cb, k2a, k2b;
 };
 
 /* one row of a compiled bond table: a single harmonic / spring / semispring term (or none) */
@@ -142,16 +147,16 @@ __device__ __forceinline__ d3 displacement_t(const DParams &P, double ax, double
 
 /* softcore<P,3> force scalar without the factor: c * g^2 * (u2)^((P-2)/2), g = 1 - (u2)^(P/2) */
 template <int PROG>
-__device__ __forceinline__ double compiled_pair_scalar(const PairRow &row, double r2)
+__device__ __forceinline__ double compiled_pair_scalar(double ca, double cb, double k2a, double k2b, double r2)
 {
-    double const ua = row.k2a * r2;
+    double const ua = k2a * r2;
     double const ga = 1.0 - ua;
-    double s = ga >= 0.0 ? row.ca * ga * ga : 0.0;
+    double s = ga >= 0.0 ? ca * ga * ga : 0.0;
     if (PROG == PROG_SC23_SC83) {
-        double const ub = row.k2b * r2;
+        double const ub = k2b * r2;
         double const vb = ub * ub * ub;
         double const gb = 1.0 - vb * ub;
-        s += gb >= 0.0 ? row.cb * gb * gb * vb : 0.0;
+        s += gb >= 0.0 ? cb * gb * gb * vb : 0.0;
     }
     return s;
 }
@@ -247,7 +252,14 @@ __device__ __forceinline__ void pair_forces(const StepArrays &A, StepShared &sh,
                 double const r2 = sqnorm_exact(r.x, r.y, r.z);  // NaN for the sentinel: every test fails
                 if (PROG != PROG_GENERIC) {
                     if (r2 <= dcut2) {
-                        double const sc = compiled_pair_scalar<PROG>(mine[w_type(o.w)], r2);
+                        const PairRow &row = mine[w_type(o.w)];
+                        double sc;
+                        if (A.k2_uniform) {
+                            double2 const c = *reinterpret_cast<const double2 *>(&row.ca);
+                            sc = compiled_pair_scalar<PROG>(c.x, c.y, A.k2a, A.k2b, r2);
+                        } else {
+                            sc = compiled_pair_scalar<PROG>(row.ca, row.cb, row.k2a, row.k2b, r2);
+                        }
                         F.x += sc * r.x; F.y += sc * r.y; F.z += sc * r.z;
                         interactions += 1u;  // every pair is seen from both ends: halved when read out
                     }
