@@ -336,6 +336,16 @@ static int upload_params(bd_engine *h)
                            h->stream));
     std::vector<PairRow> rows;
     compile_pair_program(h, rows);
+    if (h->prog != PROG_GENERIC && h->k2_uniform) {
+        // the kernel reads uniform tables as ca[T*T] followed by cb[T*T] (bd_step.cuh: pair_forces)
+        std::vector<PairRow> packed(rows.size(), PairRow{0, 0, 0, 0});
+        double *flat = reinterpret_cast<double *>(packed.data());
+        for (size_t c = 0; c < rows.size(); c++) {
+            flat[c] = rows[c].ca;
+            flat[rows.size() + c] = rows[c].cb;
+        }
+        rows.swap(packed);
+    }
     if (h->prog != PROG_GENERIC)
         CK(cudaMemcpyAsync(h->d_pair_rows.p, rows.data(), rows.size() * sizeof(PairRow), cudaMemcpyHostToDevice,
                            h->stream));

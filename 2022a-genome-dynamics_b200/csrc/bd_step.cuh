@@ -255,8 +255,12 @@ __device__ __forceinline__ void pair_forces(const StepArrays &A, StepShared &sh,
                         const PairRow &row = mine[w_type(o.w)];
                         double sc;
                         if (A.k2_uniform) {
-                            double2 const c = *reinterpret_cast<const double2 *>(&row.ca);
-                            sc = compiled_pair_scalar<PROG>(c.x, c.y, A.k2a, A.k2b, r2);
+                            // uniform tables are stored as two arrays of doubles, ca[T*T] then cb[T*T]: 8-byte
+                            // reads of 16 or fewer distinct rows never collide on a shared-memory bank
+                            uint32_t const cell = ti * (uint32_t) T + w_type(o.w);
+                            const double *cav = reinterpret_cast<const double *>(dyn_smem);
+                            sc = compiled_pair_scalar<PROG>(cav[cell], PROG == PROG_SC23_SC83 ? cav[A.ntypes2 + cell] : 0.0,
+                                                            A.k2a, A.k2b, r2);
                         } else {
                             sc = compiled_pair_scalar<PROG>(row.ca, row.cb, row.k2a, row.k2b, r2);
                         }
