@@ -161,7 +161,7 @@ __device__ __forceinline__ double compiled_pair_scalar(double ca, double cb, dou
     return s;
 }
 
-constexpr int HIT_CAP = 16;  // near-hits buffered per bead between the two phases of the pair walk
+constexpr int HIT_CAP = 24;  // near-hits buffered per bead between the two phases of the pair walk
 
 struct StepShared {
     alignas(16) DParams P;
