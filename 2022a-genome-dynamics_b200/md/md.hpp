@@ -362,30 +362,35 @@ namespace md
             return t.factor * s;
         }
 
-        // CRTP base: every potential of this header is described by its flattened terms
-        template<typename Derived>
-        struct potential_base
+        // Every potential of this header is described by its flattened terms.  The potentials stay plain
+        // aggregates with the reference's member order (drivers initialise them positionally,
+        // 3-sim-1kb/src/simulation/forces/loop_forcefield.cpp:13), so the host evaluation is injected as two
+        // member functions that forward to these helpers instead of coming from a base class.
+        template<typename Pot>
+        md::scalar flat_energy(Pot const& pot, md::vector r)
         {
-            md::scalar evaluate_energy(md::vector r) const
-            {
-                term_list terms;
-                static_cast<Derived const&>(*this).b200_flatten(terms, 1.0, 0.0);
-                double const r2 = r.squared_norm();
-                double e = 0;
-                for (auto const& t : terms) e += term_energy(t, r2);
-                return e;
-            }
+            term_list terms;
+            pot.b200_flatten(terms, 1.0, 0.0);
+            double const r2 = r.squared_norm();
+            double e = 0;
+            for (auto const& t : terms) e += term_energy(t, r2);
+            return e;
+        }
 
-            md::vector evaluate_force(md::vector r) const
-            {
-                term_list terms;
-                static_cast<Derived const&>(*this).b200_flatten(terms, 1.0, 0.0);
-                double const r2 = r.squared_norm();
-                double s = 0;
-                for (auto const& t : terms) s += term_force_scalar(t, r2);
-                return s * r;
-            }
-        };
+        template<typename Pot>
+        md::vector flat_force(Pot const& pot, md::vector r)
+        {
+            term_list terms;
+            pot.b200_flatten(terms, 1.0, 0.0);
+            double const r2 = r.squared_norm();
+            double s = 0;
+            for (auto const& t : terms) s += term_force_scalar(t, r2);
+            return s * r;
+        }
+
+#define MD_B200_POTENTIAL_MEMBERS                                                                      \
+        md::scalar evaluate_energy(md::vector r) const { return b200::flat_energy(*this, r); }         \
+        md::vector evaluate_force(md::vector r) const { return b200::flat_force(*this, r); }
 
         template<typename P, typename = void>
         struct is_potential : std::false_type {};
@@ -396,8 +401,9 @@ namespace md
 
     // ---- potentials (MD/potential/*.hpp) ----------------------------------------------------------
 
-    struct constant_potential : b200::potential_base<constant_potential>
+    struct constant_potential
     {
+        MD_B200_POTENTIAL_MEMBERS
         md::scalar energy = 0;
         constant_potential() = default;
         explicit constant_potential(md::scalar e) : energy{e} {}
@@ -409,8 +415,9 @@ namespace md
 
     // u(r) = energy (1 - (r/diameter)^P)^Q inside the diameter (MD/potential/softcore_potential.hpp:23-62)
     template<int P, int Q = 3>
-    struct softcore_potential : b200::potential_base<softcore_potential<P, Q>>
+    struct softcore_potential
     {
+        MD_B200_POTENTIAL_MEMBERS
         md::scalar energy = 1;
         md::scalar diameter = 1;
         void b200_flatten(b200::term_list& out, double factor, double cutoff) const
@@ -421,8 +428,9 @@ namespace md
 
     // u(r) = -energy / (1 + (r/decay_distance)^P) (MD/potential/softwell_potential.hpp:26-50)
     template<int P>
-    struct softwell_potential : b200::potential_base<softwell_potential<P>>
+    struct softwell_potential
     {
+        MD_B200_POTENTIAL_MEMBERS
         md::scalar energy = 1;
         md::scalar decay_distance = 1;
         void b200_flatten(b200::term_list& out, double factor, double cutoff) const
@@ -432,8 +440,9 @@ namespace md
     };
 
     // u(r) = spring_constant r^2 / 2 (MD/potential/harmonic_potential.hpp:20-35)
-    struct harmonic_potential : b200::potential_base<harmonic_potential>
+    struct harmonic_potential
     {
+        MD_B200_POTENTIAL_MEMBERS
         md::scalar spring_constant = 1;
         void b200_flatten(b200::term_list& out, double factor, double cutoff) const
         {
@@ -442,8 +451,9 @@ namespace md
     };
 
     // u(r) = spring_constant (r - equilibrium_distance)^2 / 2 (MD/potential/spring_potential.hpp:21-41)
-    struct spring_potential : b200::potential_base<spring_potential>
+    struct spring_potential
     {
+        MD_B200_POTENTIAL_MEMBERS
         md::scalar spring_constant = 1;
         md::scalar equilibrium_distance = 0;
         void b200_flatten(b200::term_list& out, double factor, double cutoff) const
@@ -453,8 +463,9 @@ namespace md
     };
 
     // spring that only pulls (MD/potential/semispring_potential.hpp:23-46)
-    struct semispring_potential : b200::potential_base<semispring_potential>
+    struct semispring_potential
     {
+        MD_B200_POTENTIAL_MEMBERS
         md::scalar spring_constant = 1;
         md::scalar equilibrium_distance = 0;
         void b200_flatten(b200::term_list& out, double factor, double cutoff) const
@@ -476,8 +487,9 @@ namespace md
     };
 
     template<typename Pot>
-    struct scaled_potential : b200::potential_base<scaled_potential<Pot>>
+    struct scaled_potential
     {
+        MD_B200_POTENTIAL_MEMBERS
         Pot potential;
         md::scalar factor;
         scaled_potential(Pot const& p, md::scalar f) : potential{p}, factor{f} {}
@@ -488,8 +500,9 @@ namespace md
     };
 
     template<typename P1, typename P2>
-    struct sum_potential : b200::potential_base<sum_potential<P1, P2>>
+    struct sum_potential
     {
+        MD_B200_POTENTIAL_MEMBERS
         P1 first;
         P2 second;
         sum_potential(P1 const& a, P2 const& b) : first{a}, second{b} {}
@@ -501,8 +514,9 @@ namespace md
     };
 
     template<typename Pot>
-    struct cutoff_potential : b200::potential_base<cutoff_potential<Pot>>
+    struct cutoff_potential
     {
+        MD_B200_POTENTIAL_MEMBERS
         Pot potential;
         md::scalar cutoff_distance;
         cutoff_potential(Pot const& p, md::scalar c) : potential{p}, cutoff_distance{c} {}
@@ -1810,6 +1824,19 @@ namespace md
             }
             std::sort(sorted.begin(), sorted.end());
             for (auto const& p : sorted) *out++ = p;
+        }
+
+        // Indices of the points closer than dcut to `point` (strict, as MD/misc/neighbor_searcher.hpp:104-131).
+        // No simulation driver calls this -- only the hetero-RDF analysis tool does
+        // (4-sim-ab/box/src/rdf_analysis_hetero/distance_histogram.cc:52), one point at a time, which is
+        // host work by nature: a scan of the stored points in ascending index order (the reference emits
+        // the same set in bucket order).
+        template<typename OutputIterator>
+        void query(md::point point, OutputIterator out) const
+        {
+            double const dcut2 = dcut_ * dcut_;
+            for (md::index i = 0; i < points_.size(); i++)
+                if (box_.shortest_displacement(points_[i], point).squared_norm() < dcut2) *out++ = i;
         }
 
     private:

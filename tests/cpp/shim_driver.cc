@@ -444,7 +444,7 @@ namespace
     {
     public:
         loop_forcefield(std::shared_ptr<pair_list> list, md::scalar stiffness, md::scalar length)
-            : _list{list}, _potential{.spring_constant = stiffness, .equilibrium_distance = length}
+            : _list{list}, _potential{stiffness, length}  // positional, as 3-sim-1kb/src/simulation/forces/loop_forcefield.cpp:13
         {
         }
 
@@ -501,7 +501,7 @@ namespace
             .set_unit_cell(box)
             .set_neighbor_distance(0.45));
         auto bonds = system.add_forcefield(
-            md::make_bonded_pairwise_forcefield(md::spring_potential{.spring_constant = 100, .equilibrium_distance = 0.3}));
+            md::make_bonded_pairwise_forcefield(md::spring_potential{100, 0.3}));  // positional aggregate initialisation
         auto bends = system.add_forcefield(md::make_bonded_triplewise_forcefield(
             [](md::system const& sys, md::index, md::index i, md::index) {
                 return md::cosine_bending_potential{sys.view(monomer_data_attribute)[i].bending_energy};
@@ -575,6 +575,17 @@ namespace
         std::printf("%s.gluelen", tag);
         for (md::scalar l : lengths) std::printf(" %.17g", l);
         std::printf("\n");
+        // neighbor_searcher::query as the hetero-RDF tool uses it (4-sim-ab/box/src/rdf_analysis_hetero/distance_histogram.cc:52)
+        {
+            md::neighbor_searcher<md::periodic_box> searcher{box, 0.4};
+            searcher.set_points(system.view_positions());
+            std::vector<md::index> around;
+            searcher.query(system.view_positions()[7], std::back_inserter(around));
+            std::sort(around.begin(), around.end());
+            double sum = 0;
+            for (md::index i : around) sum += double(i) * 31 + 1;
+            std::printf("%s.query %zu %.17g\n", tag, around.size(), sum);
+        }
     }
 }
 
