@@ -6,10 +6,9 @@ The same entry points exist with three prefixes:
 * ``orc_`` -- the CPU restatement, ``oracle/liboracle.so`` (test infrastructure only);
 * ``ref_`` -- the unmodified reference micromd, ``oracle/_ref/libmicromd_ref.so`` (test only).
 
-``load_engine()`` is what tests, ``bench.py`` and ``__graft_entry__.py`` use for the product path.
-It raises if the CUDA library is missing: there is no CPU fallback.  ``load_oracle()`` and
-``load_reference()`` exist only so that tests and the bench's cpu_baseline leg can drive the
-checker through the same calls.
+``load_engine()`` is the product path.  It raises if the CUDA library is missing: there is no CPU
+fallback, and this module does not know where the checkers live -- their loaders are test
+infrastructure in ``oracle/checkers.py`` and construct ``Backend(path, prefix)`` themselves.
 """
 from __future__ import annotations
 
@@ -167,6 +166,11 @@ ENGINE_ONLY = {
     "set_positions_device": [C.c_void_p, C.c_void_p],
     "get_positions_device": [C.c_void_p, C.c_void_p],
     "get_launch_count": [C.c_void_p, _P(C.c_int64)],
+    "update_wall_ff_replica": [C.c_void_p, C.c_int32, C.c_int32, _dbl_p, _dbl_p],
+    "get_wall_geometry": [C.c_void_p, C.c_int32, C.c_int32, _dbl_p, _dbl_p],
+    "get_wall_stats_all": [C.c_void_p, C.c_int32, _dbl_p],
+    "set_wall_relaxation": [C.c_void_p, _P(C.c_int32), C.c_int32, _dbl_p, C.c_double],
+    "noise_statistics": [C.c_uint64, C.c_int64, C.c_int64, C.c_int64, C.c_int32, C.c_int32, _dbl_p, C.c_int32],
     "set_all_positions": [C.c_void_p, C.c_void_p],
     "get_all_positions": [C.c_void_p, C.c_void_p],
     "set_owned": [C.c_void_p, _u8_p],
@@ -263,6 +267,14 @@ class Backend:
         out = np.empty(xyz.shape, dtype=np.float32)
         self.call("quantize_positions", _dp(xyz), len(xyz), int(fraction_bits), out.ctypes.data_as(_P(C.c_float)))
         return out
+
+    def noise_statistics(self, seed, first_step, steps, beads, replica=0, device=0) -> dict:
+        """moments, tail counts and correlations of the step kernel's production noise (bd_cuda.h)"""
+        out = np.zeros(20)
+        self.call("noise_statistics", int(seed), int(first_step), int(steps), int(beads), int(replica), int(device),
+                  _dp(out), 20)
+        return {"count": out[0], "sum": out[1:6], "max_abs": out[6], "tail": out[7:14], "lag1": out[14],
+                "cross": out[15:18], "sq_cross": out[18], "triples": out[19]}
 
     def refine_spline(self, coarse_xyz, coarse_ranges, factor, fine_ranges, n_fine, attach=None, fine_init=None,
                       device=0) -> np.ndarray:
@@ -410,13 +422,38 @@ class System:
                     _dp(c), _dp(s), C.byref(ff))
         return ff.value
 
-    def update_wall_ff(self, ff, center, semiaxes, tab=None):
-        c = np.ascontiguousarray(center, dtype=np.float64)
-        s = np.ascontiguousarray(semiaxes, dtype=np.float64)
+    def update_wall_ff(self, ff, center, semiaxes, tab=None, replica=None):
+        """geometry (and optionally the table) of a wall: of every replica, or of one (engine only).
+        center = semiaxes = None changes the table only (engine only)."""
         if tab is not None:
             tab = self._table(tab, self.ntypes)
+        if center is None and semiaxes is None:
+            self.b.call("update_wall_ff", self.h, ff, tab.ctypes.data, None, None)
+            return
+        c = np.ascontiguousarray(center, dtype=np.float64)
+        s = np.ascontiguousarray(semiaxes, dtype=np.float64)
+        if replica is not None:
+            assert tab is None
+            self.b.call("update_wall_ff_replica", self.h, ff, replica, _dp(c), _dp(s))
+            return
         self.b.call("update_wall_ff", self.h, ff, tab.ctypes.data if tab is not None else None,
                     _dp(c), _dp(s))
+
+    def get_wall_geometry(self, ff, replica=0):
+        c, s = np.zeros(3), np.zeros(3)
+        self.b.call("get_wall_geometry", self.h, ff, replica, _dp(c), _dp(s))
+        return c, s
+
+    def get_wall_stats_all(self, ff):
+        out = np.zeros((self.replicas, 4))
+        self.b.call("get_wall_stats_all", self.h, ff, _dp(out))
+        return out
+
+    def set_wall_relaxation(self, ffs, spring, mobility):
+        """device-resident semiaxis feedback of the walls `ffs` (empty = off), bd_cuda.h"""
+        f = (C.c_int32 * max(len(ffs), 1))(*ffs)
+        sp = np.ascontiguousarray(spring, dtype=np.float64)
+        self.b.call("set_wall_relaxation", self.h, f, len(ffs), _dp(sp), float(mobility))
 
     def get_wall_stats(self, ff, replica=0):
         out = np.zeros(4)
@@ -596,9 +633,6 @@ class System:
 
 
 ENGINE_LIB = os.path.join(HERE, "libbd_b200.so")
-ORACLE_LIB = os.path.join(ROOT, "oracle", "liboracle.so")
-REFERENCE_LIB = os.path.join(ROOT, "oracle", "_ref", "libmicromd_ref.so")
-
 _cache = {}
 
 
@@ -616,21 +650,3 @@ def load_engine() -> Backend:
             )
         _cache["bd_"] = Backend(ENGINE_LIB, "bd_")
     return _cache["bd_"]
-
-
-def load_oracle() -> Backend:
-    """TEST INFRASTRUCTURE: the CPU restatement (oracle/bd_oracle.c)."""
-    if "orc_" not in _cache:
-        _cache["orc_"] = Backend(ORACLE_LIB, "orc_")
-    return _cache["orc_"]
-
-
-def load_reference() -> Backend:
-    """TEST INFRASTRUCTURE: the unmodified reference micromd (oracle/_ref)."""
-    if "ref_" not in _cache:
-        _cache["ref_"] = Backend(REFERENCE_LIB, "ref_")
-    return _cache["ref_"]
-
-
-def have_reference() -> bool:
-    return os.path.exists(REFERENCE_LIB)

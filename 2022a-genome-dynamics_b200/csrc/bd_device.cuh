@@ -75,6 +75,21 @@ struct DWall {
 };
 struct DPoint { int32_t enabled, nterms, term_off, has_targets; double source[3]; double pad; };
 
+/* Geometry of one wall forcefield of ONE replica.  The interphase driver moves the wall semiaxes of every
+ * system from that system's own wall reaction after each step
+ * (5-sim-genome/src/simulation_interphase/simulation_driver_interphase.cc:70-80), so in an ensemble the
+ * geometry is per replica: wall_geom[replica][BD_MAX_WALL_FF], device-resident and the master copy
+ * (bd_update_wall_ff[_replica] writes it, k_wall_relax advances it).  The first nine doubles have the
+ * layout of DWall::center/semi/quad, which the kernels overwrite in their shared copy of DParams. */
+struct __align__(16) DWallGeom {
+    double center[3];
+    double semi[3];
+    double quad[3];
+    double pad[3];
+};
+static_assert(sizeof(DWallGeom) == 96, "DWallGeom is 96 bytes");
+constexpr int WALL_GEOM_DOUBLES = 9;
+
 /* everything the host may change between steps; uploaded as one block when dirty */
 struct DParams {
     int32_t ntypes, box_kind;
@@ -386,14 +401,27 @@ __device__ inline void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1)
 }
 
 /* three standard normals for (seed, step, replica, original bead index): the stream does not
- * depend on the sort order, the launch shape or the number of GPUs */
+ * depend on the sort order, the launch shape or the number of GPUs.
+ *
+ * Box-Muller in single precision on the four 32-bit outputs of one Philox call: radii from c0, c1, angles
+ * from c2, c3.  What that means against the reference's double ziggurat (MD/basic_types/ziggurat.hpp:262-322),
+ * stated here and measured by tests/test_gpu_noise.py (bd_noise_statistics, 3e8 draws):
+ *   - values carry a relative rounding of ~1e-7 (a displacement sigma*z of 1e-3 is resolved to 1e-10; the
+ *     fp64 positions to 1e-16): invisible to any moment or histogram at any sample size a run can reach;
+ *   - the radius uniform has 40 bits (the low byte of the angle words, which the float angle cannot see,
+ *     refines c0 / c1), so |z| reaches sqrt(2 ln 2^41) = 7.54; the mass beyond is 5e-14 per draw, less than
+ *     one draw in the 1.2e13 of a 10^6-step run of the 64-replica ensemble. */
 __device__ inline void philox_normals(uint64_t seed, uint64_t step, uint32_t replica, uint32_t orig,
                                       double z[3])
 {
     uint32_t c[4] = {orig, replica, (uint32_t) step, (uint32_t) (step >> 32)};
     philox4x32_10(c, (uint32_t) seed, (uint32_t) (seed >> 32));
-    float const u1 = __uint2float_rn(c[0]) * 2.3283064365386963e-10f + 1.1641532182693481e-10f;
-    float const u2 = __uint2float_rn(c[1]) * 2.3283064365386963e-10f + 1.1641532182693481e-10f;
+    // u = (c + (low byte of the angle word + 1/2) / 256) * 2^-32 in (0, 1): exact in float for small c,
+    // which is where the tail lives
+    float const f1 = __uint2float_rn(c[2] & 0xffu) * 3.90625e-3f + 1.953125e-3f;
+    float const f2 = __uint2float_rn(c[3] & 0xffu) * 3.90625e-3f + 1.953125e-3f;
+    float const u1 = (__uint2float_rn(c[0]) + f1) * 2.3283064365386963e-10f;
+    float const u2 = (__uint2float_rn(c[1]) + f2) * 2.3283064365386963e-10f;
     float const r1 = sqrtf(-2.0f * logf(fminf(u1, 1.0f)));
     float const r2 = sqrtf(-2.0f * logf(fminf(u2, 1.0f)));
     float s1, c1, s2, c2;

@@ -101,6 +101,9 @@ struct bd_engine {
     uint32_t cell_cap = 0, max_bits = 0, cap = 32;
     DevBuf<DControl> ctl;
     DevBuf<DParams> d_params;
+    DevBuf<DWallGeom> wall_geom;  // [replicas][BD_MAX_WALL_FF], the master copy of every wall's geometry
+    WallRelax relax = {};         // device-resident semiaxis relaxation (bd_set_wall_relaxation)
+    bool wall_stats_fresh = false;  // wall_out holds the reduction of the latest force evaluation
     DevBuf<DTerm> d_terms;
     DevBuf<PairRow> d_pair_rows;
     int prog = PROG_GENERIC;   // specialised pair program of the current tables (upload_params)
@@ -509,6 +512,7 @@ extern "C" int bd_create(int64_t n_beads, int32_t n_replicas, int32_t device, bd
         && h->cell_start.alloc((size_t) h->cell_cap + 1) == cudaSuccess
         && h->block_sum.alloc(h->cell_cap / SCAN_TILE + 2) == cudaSuccess
         && h->ctl.alloc(1) == cudaSuccess && h->d_params.alloc(1) == cudaSuccess
+        && h->wall_geom.alloc((size_t) h->replicas * BD_MAX_WALL_FF) == cudaSuccess
         && h->d_terms.alloc(64) == cudaSuccess && h->d_pair_rows.alloc(BD_MAX_TYPES * BD_MAX_TYPES) == cudaSuccess && h->force.alloc(3 * nt) == cudaSuccess
         && h->xyz_stage.alloc(3 * (size_t) h->n) == cudaSuccess
         && h->wall_partial.alloc((size_t) h->replicas * h->chunks * BD_MAX_WALL_FF * WALL_STATS) == cudaSuccess
@@ -527,6 +531,7 @@ extern "C" int bd_create(int64_t n_beads, int32_t n_replicas, int32_t device, bd
         return fail(std::string("bd_create: device allocation failed: ") + cudaGetErrorString(cudaGetLastError()));
     }
     cudaMemsetAsync(h->ctl.p, 0, sizeof(DControl), h->stream);
+    cudaMemsetAsync(h->wall_geom.p, 0, h->wall_geom.count * sizeof(DWallGeom), h->stream);
     cudaMemsetAsync(h->plen.p, 0, std::max<size_t>(h->pstride, 1) * sizeof(uint32_t), h->stream);
     cudaMemsetAsync(h->wall_partial.p, 0, h->wall_partial.count * sizeof(double), h->stream);
     cudaMemsetAsync(h->inter_partial.p, 0, h->inter_partial.count * sizeof(unsigned long long), h->stream);
@@ -564,6 +569,7 @@ extern "C" int bd_destroy(bd_engine *h)
     for (auto *b : {&h->d_type, &h->d_pair_mask, &h->d_point_mask, &h->bend_ff, &h->order, &h->d_owned}) b->release();
     h->ctl.release();
     h->d_params.release();
+    h->wall_geom.release();
     h->d_terms.release();
     h->d_pair_rows.release();
     h->bond_adj.release();
@@ -905,6 +911,34 @@ static double table_range(const bd_term *table, int cells, int nterms)
     return range;
 }
 
+/* Write one wall's geometry for `replica` (or for every replica when replica < 0).  The device table is the
+ * master copy: with the relaxation law active it moves on its own, so single entries are written, never the
+ * whole table. */
+static int write_wall_geometry(bd_engine *h, int ff, int replica, const double center[3], const double semiaxes[3])
+{
+    for (int d = 0; d < 3; d++)
+        if (!(semiaxes[d] > 0)) return fail("bd: wall semiaxes must be positive");
+    DWallGeom g;
+    std::memset(&g, 0, sizeof g);
+    for (int d = 0; d < 3; d++) {
+        g.center[d] = center[d];
+        g.semi[d] = semiaxes[d];
+        g.quad[d] = 1.0 / (semiaxes[d] * semiaxes[d]);  // MD/forcefield/ellipsoid_surface_forcefield.hpp:72-76
+    }
+    if (replica < 0 && h->replicas == 1) replica = 0;
+    if (replica >= 0) {
+        // pageable source: the call returns once the 96 bytes are staged, the local may go away
+        CK(cudaMemcpyAsync(h->wall_geom.p + (size_t) replica * BD_MAX_WALL_FF + ff, &g, sizeof g, cudaMemcpyHostToDevice,
+                           h->stream));
+    } else {
+        std::vector<DWallGeom> all(h->replicas, g);
+        CK(cudaMemcpy2DAsync(h->wall_geom.p + ff, BD_MAX_WALL_FF * sizeof(DWallGeom), all.data(), sizeof(DWallGeom),
+                             sizeof(DWallGeom), h->replicas, cudaMemcpyHostToDevice, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    return 0;
+}
+
 extern "C" int bd_add_wall_ff(bd_engine *h, int32_t shape, int32_t direction, int32_t nterms,
                               const bd_term *table, const double center[3], const double semiaxes[3],
                               int32_t *ff_out)
@@ -914,6 +948,7 @@ extern "C" int bd_add_wall_ff(bd_engine *h, int32_t shape, int32_t direction, in
     if (direction != BD_WALL_INWARD && direction != BD_WALL_OUTWARD) return fail("bd_add_wall_ff: unknown direction");
     for (int k = 0; k < BD_MAX_WALL_FF; k++) {
         if (h->wall[k].used) continue;
+        if (write_wall_geometry(h, k, -1, center, semiaxes)) return 1;
         if (store_table(h, h->wall[k], nterms, table, h->hp.ntypes)) return 1;
         DWall &w = h->hp.wall[k];
         w.enabled = 1;
@@ -922,30 +957,73 @@ extern "C" int bd_add_wall_ff(bd_engine *h, int32_t shape, int32_t direction, in
         w.shape = shape;
         w.direction = direction;
         w.range = table_range(table, h->hp.ntypes, nterms);
-        for (int d = 0; d < 3; d++) {
-            w.center[d] = center[d];
-            w.semi[d] = semiaxes[d];
-            w.quad[d] = 1.0 / (semiaxes[d] * semiaxes[d]);
-        }
         *ff_out = k;
         return 0;
     }
     return fail("bd_add_wall_ff: too many wall forcefields");
 }
 
+/* center / semiaxes may be NULL together: only the table changes (the geometry may be moving on the
+ * device: bd_set_wall_relaxation) */
 extern "C" int bd_update_wall_ff(bd_engine *h, int32_t ff, const bd_term *table, const double center[3],
                                  const double semiaxes[3])
 {
     NEED(h);
     if (ff < 0 || ff >= BD_MAX_WALL_FF || !h->wall[ff].used) return fail("bd_update_wall_ff: bad forcefield id");
+    if ((center == nullptr) != (semiaxes == nullptr)) return fail("bd_update_wall_ff: center and semiaxes go together");
     if (table && store_table(h, h->wall[ff], h->wall[ff].nterms, table, h->wall[ff].cells)) return 1;
-    if (table) h->hp.wall[ff].range = table_range(table, h->wall[ff].cells, h->wall[ff].nterms);
-    for (int d = 0; d < 3; d++) {
-        h->hp.wall[ff].center[d] = center[d];
-        h->hp.wall[ff].semi[d] = semiaxes[d];
-        h->hp.wall[ff].quad[d] = 1.0 / (semiaxes[d] * semiaxes[d]);
+    if (table) {
+        h->hp.wall[ff].range = table_range(table, h->wall[ff].cells, h->wall[ff].nterms);
+        h->params_dirty = true;
     }
-    h->params_dirty = true;
+    if (center) return write_wall_geometry(h, ff, -1, center, semiaxes);
+    return 0;
+}
+
+extern "C" int bd_update_wall_ff_replica(bd_engine *h, int32_t ff, int32_t replica, const double center[3],
+                                         const double semiaxes[3])
+{
+    NEED(h);
+    if (ff < 0 || ff >= BD_MAX_WALL_FF || !h->wall[ff].used) return fail("bd_update_wall_ff_replica: bad forcefield id");
+    if (replica < 0 || (uint32_t) replica >= h->replicas) return fail("bd_update_wall_ff_replica: bad replica");
+    if (!center || !semiaxes) return fail("bd_update_wall_ff_replica: null geometry");
+    return write_wall_geometry(h, ff, replica, center, semiaxes);
+}
+
+extern "C" int bd_get_wall_geometry(bd_engine *h, int32_t ff, int32_t replica, double center[3], double semiaxes[3])
+{
+    NEED(h);
+    if (ff < 0 || ff >= BD_MAX_WALL_FF || !h->wall[ff].used) return fail("bd_get_wall_geometry: bad forcefield id");
+    if (replica < 0 || (uint32_t) replica >= h->replicas) return fail("bd_get_wall_geometry: bad replica");
+    DWallGeom g;
+    CK(cudaMemcpyAsync(&g, h->wall_geom.p + (size_t) replica * BD_MAX_WALL_FF + ff, sizeof g, cudaMemcpyDeviceToHost,
+                       h->stream));
+    if (sync_and_check(h)) return 1;
+    for (int d = 0; d < 3; d++) {
+        if (center) center[d] = g.center[d];
+        if (semiaxes) semiaxes[d] = g.semi[d];
+    }
+    return 0;
+}
+
+extern "C" int bd_set_wall_relaxation(bd_engine *h, const int32_t *ffs, int32_t count, const double spring[3],
+                                      double mobility)
+{
+    NEED(h);
+    if (count < 0 || count > BD_MAX_WALL_FF || (count > 0 && (!ffs || !spring)))
+        return fail("bd_set_wall_relaxation: bad arguments");
+    WallRelax law = {};
+    for (int k = 0; k < count; k++) {
+        if (ffs[k] < 0 || ffs[k] >= BD_MAX_WALL_FF || !h->wall[ffs[k]].used)
+            return fail("bd_set_wall_relaxation: bad forcefield id");
+        if (h->hp.wall[ffs[k]].shape != BD_WALL_ELLIPSOID) return fail("bd_set_wall_relaxation: ellipsoid walls only");
+        law.mask |= 1u << ffs[k];
+    }
+    if (count > 0) {
+        for (int d = 0; d < 3; d++) law.spring[d] = spring[d];
+        law.mobility = mobility;
+    }
+    h->relax = law;
     return 0;
 }
 
@@ -1055,6 +1133,7 @@ static StepArrays step_arrays(bd_engine *h)
     A.bend_ff = h->bend_ff.p;
     A.terms = h->d_terms.p;
     A.params = h->d_params.p;
+    A.wall_geom = h->wall_geom.p;
     A.ctl = h->ctl.p;
     A.wall_partial = h->wall_partial.p;
     A.inter_partial = h->inter_partial.p;
@@ -1280,7 +1359,7 @@ extern "C" int bd_step(bd_engine *h, const bd_step_config *cfg)
         S.dt = cfg->timestep;
         S.dt_prev = h->last_dt;
         S.kT_prev = h->last_kT;
-        S.want_stats = k == cfg->steps - 1;
+        S.want_stats = k == cfg->steps - 1 || h->relax.mask != 0;
         if (replay) S.replay = h->replay.p + ((size_t) k - staged_from) * per_step;
         if (!adaptive) {
             cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -1301,6 +1380,14 @@ extern "C" int bd_step(bd_engine *h, const bd_step_config *cfg)
             k_dt_rotate<<<blocks_for(h->replicas, 128), 128, 0, st>>>(h->dt_bits.p, h->dt_prev.p, h->dt_last.p,
                                                                       cfg->timestep, h->replicas);
             h->launches += 3;
+        }
+        h->wall_stats_fresh = false;
+        if (h->relax.mask) {
+            // the callback's wall update of every replica, on the device (bd_set_wall_relaxation)
+            k_wall_relax<<<h->replicas, RELAX_WIDTH * RELAX_LANES, 0, st>>>(h->wall_partial.p, h->wall_out.p, h->wall_geom.p,
+                                                                           h->relax, h->chunks, cfg->timestep);
+            h->launches += 1;
+            h->wall_stats_fresh = true;
         }
         CK(cudaGetLastError());
         h->cur ^= 1;
@@ -1352,6 +1439,7 @@ extern "C" int bd_compute_forces(bd_engine *h, int32_t replica, int32_t ff_class
     std::memset(&S, 0, sizeof S);
     Select const sel = {ff_class, ff};
     launch_force(h, A, S, sel);
+    h->wall_stats_fresh = false;
     k_gather_forces<<<blocks_for(h->n, 256), 256, 0, h->stream>>>(h->force.p, h->slot_of.p, h->xyz_stage.p,
                                                                   (uint32_t) replica * h->n, h->n);
     h->launches += 2;
@@ -1378,6 +1466,19 @@ extern "C" int bd_compute_energy(bd_engine *h, int32_t replica, int32_t ff_class
     return sync_and_check(h);
 }
 
+/* wall_out <- per-replica sums of the per-chunk statistics of the latest force evaluation */
+static int reduce_wall_stats(bd_engine *h)
+{
+    if (h->wall_stats_fresh) return 0;
+    WallRelax none = {};
+    k_wall_relax<<<h->replicas, RELAX_WIDTH * RELAX_LANES, 0, h->stream>>>(h->wall_partial.p, h->wall_out.p, h->wall_geom.p,
+                                                                          none, h->chunks, 0.0);
+    h->launches += 1;
+    CK(cudaGetLastError());
+    h->wall_stats_fresh = true;
+    return 0;
+}
+
 extern "C" int bd_get_wall_stats(bd_engine *h, int32_t ff, int32_t replica, double out[4])
 {
     NEED(h);
@@ -1385,12 +1486,24 @@ extern "C" int bd_get_wall_stats(bd_engine *h, int32_t ff, int32_t replica, doub
     if (replica < 0 || (uint32_t) replica >= h->replicas) return fail("bd_get_wall_stats: bad replica");
     for (int c = 0; c < 4; c++) out[c] = 0;
     if (h->ntot == 0) return 0;
-    unsigned const width = BD_MAX_WALL_FF * WALL_STATS;
-    k_reduce_partials<<<h->replicas, 32, 0, h->stream>>>(h->wall_partial.p, h->wall_out.p, h->chunks, width);
-    h->launches += 1;
-    CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(out, h->wall_out.p + (size_t) replica * width + (size_t) ff * WALL_STATS,
+    if (reduce_wall_stats(h)) return 1;
+    CK(cudaMemcpyAsync(out, h->wall_out.p + (size_t) replica * RELAX_WIDTH + (size_t) ff * WALL_STATS,
                        WALL_STATS * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    return sync_and_check(h);
+}
+
+/* the same for every replica at once: out[n_replicas][4] */
+extern "C" int bd_get_wall_stats_all(bd_engine *h, int32_t ff, double *out)
+{
+    NEED(h);
+    if (ff < 0 || ff >= BD_MAX_WALL_FF || !h->wall[ff].used) return fail("bd_get_wall_stats_all: bad forcefield id");
+    if (!out) return fail("bd_get_wall_stats_all: null output");
+    for (size_t c = 0; c < 4 * (size_t) h->replicas; c++) out[c] = 0;
+    if (h->ntot == 0) return 0;
+    if (reduce_wall_stats(h)) return 1;
+    CK(cudaMemcpy2DAsync(out, WALL_STATS * sizeof(double), h->wall_out.p + (size_t) ff * WALL_STATS,
+                         RELAX_WIDTH * sizeof(double), WALL_STATS * sizeof(double), h->replicas, cudaMemcpyDeviceToHost,
+                         h->stream));
     return sync_and_check(h);
 }
 
@@ -1528,6 +1641,82 @@ extern "C" int bd_get_launch_count(bd_engine *h, int64_t *out)
 {
     NEED(h);
     *out = h->launches;
+    return 0;
+}
+
+// ---- statistics of the production noise -------------------------------------------------------------
+//
+// The reference draws double-precision ziggurat normals from one sequential sfc64 stream
+// (MD/simulation/detail/brownian_simulator.hpp:61-70); the engine draws philox_normals (bd_device.cuh)
+// keyed by (seed, step, replica, bead).  The streams cannot be compared value by value, so the generator is
+// pinned by its statistics: this entry point draws the normals of `beads` beads for `steps` steps exactly as
+// the step kernel does and returns their moments, tail counts and correlations.
+
+constexpr int NOISE_STATS = 20;
+
+__global__ void __launch_bounds__(256) k_noise_stats(unsigned long long seed, long long first_step, uint32_t steps,
+                                                     uint32_t beads, uint32_t replica, double *out)
+{
+    double acc[NOISE_STATS];
+    for (int c = 0; c < NOISE_STATS; c++) acc[c] = 0.0;
+    unsigned long long const total = (unsigned long long) beads * steps;
+    for (unsigned long long t = (unsigned long long) blockIdx.x * blockDim.x + threadIdx.x; t < total;
+         t += (unsigned long long) gridDim.x * blockDim.x) {
+        uint32_t const bead = (uint32_t) (t % beads);
+        unsigned long long const step = (unsigned long long) first_step + t / beads;
+        double z[3], zn[3];
+        philox_normals(seed, step, replica, bead, z);
+        philox_normals(seed, step + 1, replica, bead, zn);
+        for (int d = 0; d < 3; d++) {
+            double const v = z[d], v2 = v * v, a = fabs(v);
+            acc[0] += 1.0;
+            acc[1] += v;
+            acc[2] += v2;
+            acc[3] += v2 * v;
+            acc[4] += v2 * v2;
+            acc[5] += v2 * v2 * v2;
+            acc[6] = fmax(acc[6], a);
+            for (int k = 1; k <= 7; k++) acc[6 + k] += a > (double) k ? 1.0 : 0.0;  // acc[7..13]: |z| > 1..7
+            acc[14] += v * zn[d];                                                   // lag-1 in time, same bead
+        }
+        acc[15] += z[0] * z[1];  // within one Box-Muller pair
+        acc[16] += z[0] * z[2];  // across the two pairs of one Philox call
+        acc[17] += z[1] * z[2];
+        acc[18] += z[0] * z[0] * z[1] * z[1];  // radius coupling inside a pair: E = 1 for independent normals
+        acc[19] += 1.0;
+    }
+    for (int c = 0; c < NOISE_STATS; c++) {
+        double v = acc[c];
+        for (int o = 16; o > 0; o >>= 1) {
+            double const w = __shfl_xor_sync(0xffffffffu, v, o);
+            v = c == 6 ? fmax(v, w) : v + w;
+        }
+        if ((threadIdx.x & 31) == 0) {
+            if (c == 6) atomicMax((unsigned long long *) &out[c], (unsigned long long) __double_as_longlong(v));
+            else atomicAdd(&out[c], v);
+        }
+    }
+}
+
+extern "C" int bd_noise_statistics(uint64_t seed, int64_t first_step, int64_t steps, int64_t beads, int32_t replica,
+                                   int32_t device, double *out, int32_t out_len)
+{
+    if (!out || out_len < NOISE_STATS) return fail("bd_noise_statistics: out must hold 20 doubles");
+    if (steps < 1 || beads < 1 || first_step < 1 || beads >= (1ll << 32) || steps >= (1ll << 32))
+        return fail("bd_noise_statistics: bad range");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail("bd_noise_statistics: no CUDA device");
+    CK(cudaSetDevice(device));
+    double *d = nullptr;
+    CK(cudaMalloc((void **) &d, NOISE_STATS * sizeof(double)));
+    cudaError_t e = cudaMemset(d, 0, NOISE_STATS * sizeof(double));
+    if (e == cudaSuccess) {
+        k_noise_stats<<<148 * 8, 256>>>(seed, first_step, (uint32_t) steps, (uint32_t) beads, (uint32_t) replica, d);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(out, d, NOISE_STATS * sizeof(double), cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    if (e != cudaSuccess) return fail(std::string("bd_noise_statistics: ") + cudaGetErrorString(e));
     return 0;
 }
 

@@ -49,6 +49,7 @@ struct StepArrays {
     const uint8_t *bend_ff;       // [m]
     const DTerm *terms;
     const DParams *params;
+    const DWallGeom *wall_geom;   // [replicas][BD_MAX_WALL_FF] per-replica wall geometry (bd_device.cuh)
     DControl *ctl;
     double *wall_partial;         // [replicas][chunks][BD_MAX_WALL_FF][4]
     unsigned long long *inter_partial;  // [replicas*chunks*warps] interacting (bead, neighbour) entries so far
@@ -456,6 +457,16 @@ __device__ __forceinline__ void copy16(void *dst, const void *src, uint32_t byte
     for (uint32_t i = threadIdx.x; i < bytes / 16u; i += blockDim.x) ((uint4 *) dst)[i] = ((const uint4 *) src)[i];
 }
 
+/* this replica's wall geometry over the shared copy of the parameters (call between two barriers) */
+__device__ __forceinline__ void load_replica_walls(DParams &P, const DWallGeom *geom, uint32_t replica)
+{
+    for (uint32_t i = threadIdx.x; i < BD_MAX_WALL_FF * WALL_GEOM_DOUBLES; i += blockDim.x) {
+        uint32_t const f = i / WALL_GEOM_DOUBLES, c = i % WALL_GEOM_DOUBLES;
+        if (!P.wall[f].enabled) continue;
+        (&P.wall[f].center[0])[c] = reinterpret_cast<const double *>(geom + (size_t) replica * BD_MAX_WALL_FF + f)[c];
+    }
+}
+
 template <int PROG>
 __device__ __forceinline__ void load_shared(StepShared &sh, const StepArrays &A, Select sel)
 {
@@ -466,6 +477,7 @@ __device__ __forceinline__ void load_shared(StepShared &sh, const StepArrays &A,
     if (A.bonds_compiled)
         copy16(dyn_smem + A.ntypes2 * sizeof(PairRow), A.bond_rows, (uint32_t) A.nbond_rows * (uint32_t) sizeof(BondRow));
     __syncthreads();
+    load_replica_walls(sh.P, A.wall_geom, blockIdx.y);
     if (threadIdx.x == 0) {
         // widened cutoff of the pre-filter: r <= dcut implies r_shadow <= dcut + shadow_eps / 4, and the
         // factor covers the single-precision rounding of the squared distance itself
@@ -699,6 +711,8 @@ __global__ void __launch_bounds__(STEP_BLOCK) k_energy(StepArrays A, Select sel,
 {
     __shared__ DParams P;
     load_params(P, A.params);
+    load_replica_walls(P, A.wall_geom, blockIdx.y);
+    __syncthreads();
     uint32_t const replica = blockIdx.y, chunk = blockIdx.x;
     uint32_t const local = chunk * STEP_BLOCK + threadIdx.x;
     uint32_t const pos = replica * A.npad + local;
@@ -808,6 +822,62 @@ __global__ void k_reduce_partials(const double *partial, double *out, uint32_t c
         double t = 0.0;
         for (uint32_t k = 0; k < chunks; k++) t += partial[((size_t) replica * chunks + k) * width + c];
         out[(size_t) replica * width + c] = t;
+    }
+}
+
+/* Device-resident wall relaxation: what the interphase driver's per-step callback does on the host for
+ * its one system (5-sim-genome/src/simulation_interphase/simulation_driver_interphase.cc:70-80,
+ * simulation_driver_forcefield.cc:230-234), done here for every replica of an ensemble without leaving
+ * the GPU.  After a step, per replica:
+ *     net   = sum over the walls of the group of stats.axial_reaction  -  spring o semiaxes
+ *     semiaxes += dt * mobility * net            (all walls of the group share the semiaxes)
+ * One block per replica: reduces the per-chunk statistics in a fixed order (also the answer of
+ * bd_get_wall_stats[_all]) and rewrites the replica's geometry for the next step. */
+struct WallRelax {
+    uint32_t mask;       // walls of the group (bit f), 0 = no relaxation: the kernel only reduces
+    uint32_t pad;
+    double spring[3];
+    double mobility;
+};
+
+constexpr int RELAX_LANES = 8;
+constexpr int RELAX_WIDTH = BD_MAX_WALL_FF * WALL_STATS;
+
+__global__ void __launch_bounds__(RELAX_WIDTH * RELAX_LANES)
+k_wall_relax(const double *partial, double *out, DWallGeom *geom, WallRelax law, uint32_t chunks, double dt)
+{
+    __shared__ double part[RELAX_WIDTH][RELAX_LANES];
+    __shared__ double total[RELAX_WIDTH];
+    uint32_t const replica = blockIdx.x;
+    uint32_t const c = threadIdx.x / RELAX_LANES, lane = threadIdx.x % RELAX_LANES;
+    double t = 0.0;
+    for (uint32_t k = lane; k < chunks; k += RELAX_LANES) t += partial[((size_t) replica * chunks + k) * RELAX_WIDTH + c];
+    part[c][lane] = t;
+    __syncthreads();
+    if (lane == 0) {
+        double sum = 0.0;
+        for (int l = 0; l < RELAX_LANES; l++) sum += part[c][l];
+        total[c] = sum;
+        out[(size_t) replica * RELAX_WIDTH + c] = sum;
+    }
+    __syncthreads();
+    if (law.mask == 0 || threadIdx.x >= 3) return;
+    int const d = threadIdx.x;
+    DWallGeom *g = geom + (size_t) replica * BD_MAX_WALL_FF;
+    double semi = 0.0, net = 0.0;
+    bool first = true;
+    for (int f = 0; f < BD_MAX_WALL_FF; f++) {
+        if (!((law.mask >> f) & 1u)) continue;
+        if (first) semi = g[f].semi[d];
+        first = false;
+        net += total[f * WALL_STATS + 1 + d];
+    }
+    net = __dsub_rn(net, __dmul_rn(law.spring[d], semi));
+    semi = __dadd_rn(semi, __dmul_rn(__dmul_rn(dt, law.mobility), net));
+    for (int f = 0; f < BD_MAX_WALL_FF; f++) {
+        if (!((law.mask >> f) & 1u)) continue;
+        g[f].semi[d] = semi;
+        g[f].quad[d] = 1.0 / __dmul_rn(semi, semi);
     }
 }
 

@@ -31,8 +31,8 @@
  * Not offered (no driver uses them): Langevin / Newtonian integrators, Lennard-Jones family,
  * plane surfaces, composite / brute-force force fields, xy_periodic_box as a unit cell.
  *
- * Backend selection (tests only): -DMD_B200_PREFIX=orc_ binds the same calls to the CPU oracle so
- * that the host logic of this header can be tested without a GPU.  The product binds bd_.
+ * The header binds the bd_ entry points of libbd_b200.so and nothing else.  (The GPU-less test of its host
+ * logic links generated bd_ -> orc_ forwarders instead of the engine: tests/test_md_shim.py.)
  */
 #ifndef MD_B200_MD_HPP
 #define MD_B200_MD_HPP
@@ -61,20 +61,13 @@
 
 // ---- the C ABI this header binds ------------------------------------------------------------------
 
-#ifndef MD_B200_PREFIX
-#define MD_B200_PREFIX bd_
 #define MD_B200_HANDLE_NAME bd_engine
-#define MD_B200_ENGINE 1  // bound to libbd_b200.so: the engine-only entry points of bd_cuda.h exist
-#else
-#define MD_B200_HANDLE_NAME md_b200_backend_handle
-#endif
-#define MD_B200_CAT2(a, b) a##b
-#define MD_B200_CAT(a, b) MD_B200_CAT2(a, b)
+#define MD_B200_ENGINE 1  // the engine-only entry points of bd_cuda.h exist (extensions below)
 
 extern "C" {
-typedef struct MD_B200_HANDLE_NAME MD_B200_HANDLE_NAME;
-#define BD_FN(name) MD_B200_CAT(MD_B200_PREFIX, name)
-#define BD_HANDLE MD_B200_HANDLE_NAME
+typedef struct bd_engine bd_engine;
+#define BD_FN(name) bd_##name
+#define BD_HANDLE bd_engine
 #include "bd_api_decl.inc"
 #undef BD_HANDLE
 }

@@ -111,12 +111,13 @@ class ClockSampler:
 # ---- reference arm -------------------------------------------------------------------------------
 
 def cpu_backend():
-    import bdb200 as bd
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import checkers  # test infrastructure: only this CPU leg of the bench executes anything under oracle/
 
-    if bd.have_reference():
-        return bd.load_reference(), "reference"
+    if checkers.have_reference():
+        return checkers.load_reference(), "reference"
     subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "liboracle.so"], check=True)
-    return bd.load_oracle(), "port"
+    return checkers.load_oracle(), "port"
 
 
 def cpu_time_steps(backend, scen, start_positions, steps, threads, warm):

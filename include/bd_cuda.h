@@ -42,6 +42,22 @@ int bd_sync(bd_engine *h);
 int bd_set_option(bd_engine *h, const char *name, double value);
 int bd_get_option(bd_engine *h, const char *name, double *value);
 
+/* ---- per-replica walls (the real 100kb interphase model in an ensemble) ---------------------------
+ * The interphase driver moves the wall semiaxes of its system after every step from that system's own
+ * wall reaction (5-sim-genome/src/simulation_interphase/simulation_driver_interphase.cc:70-80:
+ * net = inward.stats.axial_reaction + outward.stats.axial_reaction - spring o semiaxes;
+ * semiaxes += timestep * wall_mobility * net), so in an ensemble every replica has its own geometry.
+ * bd_update_wall_ff (bd_api_decl.inc) sets the geometry of EVERY replica (its center/semiaxes may be NULL
+ * together: table-only update); the calls below address one replica, read all replicas' statistics in one
+ * copy, or hand the relaxation law to the engine so that it runs after every step on the device with no
+ * host round trip (`ffs`: the walls that share the semiaxes, e.g. the inward and the outward ellipsoid;
+ * count = 0 switches it off).  The host-driven and the device-resident feedback give the same trajectory
+ * (tests/test_gpu_parity.py::test_wall_feedback_*). */
+int bd_update_wall_ff_replica(bd_engine *h, int32_t ff, int32_t replica, const double center[3], const double semiaxes[3]);
+int bd_get_wall_geometry(bd_engine *h, int32_t ff, int32_t replica, double center[3], double semiaxes[3]);
+int bd_get_wall_stats_all(bd_engine *h, int32_t ff, double *out /* [n_replicas][4] */);
+int bd_set_wall_relaxation(bd_engine *h, const int32_t *ffs, int32_t count, const double spring[3], double mobility);
+
 /* Device-resident variants used by bench.py's HBM-resident timing: xyz is a DEVICE pointer to
  * [n_replicas][n_beads][3] doubles in original bead order. */
 int bd_set_positions_device(bd_engine *h, const double *d_xyz);
@@ -119,6 +135,17 @@ int bd_refine_spline_device(const double *d_coarse, const int64_t *coarse_ranges
  * returns after the data has arrived. */
 int bd_set_all_positions(bd_engine *h, const double *xyz);
 int bd_get_all_positions(bd_engine *h, double *xyz);
+
+/* ---- statistics of the production noise -----------------------------------------------------------
+ * The engine's step kernel draws counter-based Philox4x32-10 + single-precision Box-Muller normals keyed by
+ * (seed, step, replica, bead) where the reference draws sfc64 + double ziggurat normals from one sequential
+ * stream (MD/simulation/detail/brownian_simulator.hpp:61-70): same distribution, different stream.  This
+ * call draws the 3 * beads * steps normals of beads [0, beads) at steps [first_step, first_step + steps)
+ * exactly as the kernel does and writes 20 doubles: {count, sum z, sum z^2, sum z^3, sum z^4, sum z^6,
+ * max |z|, #(|z| > 1) .. #(|z| > 7), sum z(step) z(step + 1), sum z0 z1, sum z0 z2, sum z1 z2,
+ * sum z0^2 z1^2, triples}.  tests/test_gpu_noise.py holds them against the exact normal values. */
+int bd_noise_statistics(uint64_t seed, int64_t first_step, int64_t steps, int64_t beads, int32_t replica,
+                        int32_t device, double *out, int32_t out_len);
 
 /* Number of kernels launched by this engine since creation (bench.py "gpu_launches"). */
 int bd_get_launch_count(bd_engine *h, int64_t *out);

@@ -5,7 +5,7 @@ import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PKG = os.path.join(ROOT, "2022a-genome-dynamics_b200")
-for p in (PKG, ROOT):
+for p in (PKG, ROOT, os.path.join(ROOT, "oracle")):
     if p not in sys.path:
         sys.path.insert(0, p)
 
@@ -27,18 +27,18 @@ def _built_libraries():
 
 @pytest.fixture(scope="session")
 def oracle():
-    import bdb200
+    import checkers
 
-    return bdb200.load_oracle()
+    return checkers.load_oracle()
 
 
 @pytest.fixture(scope="session")
 def reference():
-    import bdb200
+    import checkers
 
-    if not bdb200.have_reference():
+    if not checkers.have_reference():
         pytest.skip("oracle/_ref/libmicromd_ref.so not built (no /root/reference here)")
-    return bdb200.load_reference()
+    return checkers.load_reference()
 
 
 @pytest.fixture(scope="session")

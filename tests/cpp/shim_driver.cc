@@ -4,7 +4,8 @@
 //   * against the reference's micromd headers (where /root/reference exists) -> expected output,
 //     committed as tests/golden/shim_driver_expected.txt
 //   * against 2022a-genome-dynamics_b200/md/md.hpp, linked with libbd_b200.so (GPU) or, for the
-//     host-logic test without a GPU, with the CPU oracle (-DMD_B200_PREFIX=orc_)
+//     host-logic test without a GPU, with bd_ -> orc_ forwarders and the CPU oracle
+//     (-DSHIM_DRIVER_HOST_QUERIES: the engine-only extensions are not there)
 // and the printed numbers must agree.  Temperature is zero, so the trajectories are deterministic
 // whatever noise generator is behind simulate_brownian_dynamics.
 //
@@ -553,7 +554,7 @@ namespace
         std::vector<std::pair<md::index, md::index>> near;
         std::vector<md::scalar> lengths;
         bool asked_device = false;
-#ifdef MD_B200_ENGINE
+#if defined(MD_B200_ENGINE) && !defined(SHIM_DRIVER_HOST_QUERIES)
         if (device_lists) {
             near = md::b200::search_pairs(system, 0.4);
             lengths = md::b200::pair_distances(system, glues->pairs, true);

@@ -11,8 +11,9 @@ import torch.distributed as dist
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 sys.path.insert(0, os.path.join(ROOT, "2022a-genome-dynamics_b200"))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
 
-import bdb200 as bd  # noqa: E402
+import checkers  # noqa: E402
 import ensemble as en  # noqa: E402
 import scenarios as sc  # noqa: E402
 
@@ -22,7 +23,7 @@ def main():
     dist.init_process_group("gloo")
     rank, world = dist.get_rank(), dist.get_world_size()
     scen = sc.genome_10mb(total=320, bend_energy=0.7)
-    ens = en.ReplicaEnsemble(bd.load_oracle(), scen, n_global, rank=rank, world=world, seed=9)
+    ens = en.ReplicaEnsemble(checkers.load_oracle(), scen, n_global, rank=rank, world=world, seed=9)
     ens.step(steps)
     stats = ens.statistics(device="cpu")
     np.save(os.path.join(out_dir, f"stats_rank{rank}.npy"), stats)

@@ -16,13 +16,15 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, os.path.join(ROOT, "2022a-genome-dynamics_b200"))
 sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
 
 import bdb200 as bd  # noqa: E402
+import checkers  # noqa: E402
 from cases import GOLDEN, GOLDEN_SEED, GOLDEN_STEPS, build  # noqa: E402
 
 
 def main():
-    ref = bd.load_reference()
+    ref = checkers.load_reference()
 
     # RNG stream: first 4096 sfc64 outputs and normals, plus a checksum over 1M normals
     z = ref.normals(GOLDEN_SEED, 1_000_000)

@@ -4,9 +4,10 @@ tests/cpp/shim_driver.cc is a miniature of the paper's drivers written against <
 expected output, tests/golden/shim_driver_expected.txt, was printed by that program compiled against
 the UNMODIFIED micromd headers (regenerated and compared below wherever /root/reference exists).
 
-  * CPU: the same source compiled against md.hpp with the calls bound to the CPU oracle
-    (-DMD_B200_PREFIX=orc_) checks the header's host logic -- class tabulation of the lambdas,
-    parameter refresh between steps, wall statistics feedback, phase changes -- without a GPU.
+  * CPU: the same source compiled against md.hpp and linked with bd_ -> orc_ forwarders generated
+    here from include/bd_api_decl.inc plus the CPU oracle checks the header's host logic -- class
+    tabulation of the lambdas, parameter refresh between steps, wall statistics feedback, phase
+    changes -- without a GPU.  (md.hpp itself only knows the bd_ names.)
   * GPU: compiled against md.hpp + libbd_b200.so, i.e. exactly what a driver links.
 
 Temperature is zero in the driver, so trajectories do not depend on the noise generator.
@@ -66,11 +67,34 @@ def test_expected_output_is_the_reference(tmp_path):
     assert parse(out) and out == open(EXPECTED).read()
 
 
+def oracle_forwarders(tmp_path):
+    """A C file defining every bd_ entry point of include/bd_api_decl.inc as a call of its orc_ twin."""
+    import re
+
+    text = open(os.path.join(ROOT, "include", "bd_api_decl.inc")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    lines = ['#include "bd_types.h"', "typedef struct orc_system orc_system;", "typedef struct bd_engine bd_engine;"]
+    for ret, name, args in re.findall(r"(const char \*|int )BD_FN\((\w+)\)\(([^;]*)\);", text):
+        args = " ".join(args.split())
+        names = [] if args == "void" else [re.sub(r"\[\d*\]", "", a.split()[-1].lstrip("*")) for a in args.split(",")]
+        orc_args = args.replace("BD_HANDLE", "orc_system")
+        bd_args = args.replace("BD_HANDLE", "bd_engine")
+        call = ", ".join(f"(orc_system *) {n}" if n == "h" else (f"(orc_system **) {n}" if n == "out" and name == "create" else n)
+                         for n in names)
+        lines.append(f"{ret}orc_{name}({orc_args});")
+        lines.append(f"{ret}bd_{name}({bd_args}) {{ return orc_{name}({call}); }}")
+    path = str(tmp_path / "bd_on_oracle.c")
+    open(path, "w").write("\n".join(lines) + "\n")
+    obj = str(tmp_path / "bd_on_oracle.o")
+    subprocess.run(["gcc", "-c", "-O1", "-I" + os.path.join(ROOT, "include"), path, "-o", obj], check=True)
+    return obj
+
+
 def test_header_logic_on_oracle_backend(tmp_path):
     oracle_dir = os.path.join(ROOT, "oracle")
     out = build_and_run(tmp_path, "orc_driver", [
-        "-DMD_B200_PREFIX=orc_", "-I" + os.path.join(PKG, "md"), "-I" + os.path.join(ROOT, "include"),
-        "-L" + oracle_dir, "-loracle", "-Wl,-rpath," + oracle_dir])
+        "-DSHIM_DRIVER_HOST_QUERIES", "-I" + os.path.join(PKG, "md"), "-I" + os.path.join(ROOT, "include"),
+        oracle_forwarders(tmp_path), "-L" + oracle_dir, "-loracle", "-Wl,-rpath," + oracle_dir])
     compare(parse(out), parse(open(EXPECTED).read()))
 
 
