@@ -173,6 +173,7 @@ ENGINE_ONLY = {
     "noise_statistics": [C.c_uint64, C.c_int64, C.c_int64, C.c_int64, C.c_int32, C.c_int32, _dbl_p, C.c_int32],
     "set_all_positions": [C.c_void_p, C.c_void_p],
     "get_all_positions": [C.c_void_p, C.c_void_p],
+    "get_all_positions_async": [C.c_void_p, C.c_void_p],
     "set_owned": [C.c_void_p, _u8_p],
     "set_owned_device": [C.c_void_p, C.c_void_p],
     "gather_positions_indexed": [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p],
@@ -557,6 +558,10 @@ class System:
 
     def get_all_positions(self, host_ptr: int):
         self.b.call("get_all_positions", self.h, C.c_void_p(host_ptr))
+
+    def get_all_positions_async(self, host_ptr: int):
+        """enqueue the download into a pinned buffer; complete after sync()"""
+        self.b.call("get_all_positions_async", self.h, C.c_void_p(host_ptr))
 
     def set_owned(self, owned):
         """slab decomposition: 0/1 per bead, None = every bead is advanced by this engine"""

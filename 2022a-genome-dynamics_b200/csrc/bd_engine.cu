@@ -114,7 +114,7 @@ struct bd_engine {
     DevBuf<double> force, wprev, xyz_stage, wall_partial, wall_out, energy_partial, energy_out, dt_prev, dt_last;
     DevBuf<unsigned long long> inter_partial, dt_bits, pair_count;
     DevBuf<uint8_t> d_type, d_pair_mask, d_point_mask, order, d_owned;
-    DevBuf<double> replay, xyz_all, ext;
+    DevBuf<double> replay, xyz_all, xyz_out, ext;
     bool ext_on = false;
 
     // contact map accumulated on the device (bd_contact_*)
@@ -299,16 +299,19 @@ static void compile_bond_rows(bd_engine *h, std::vector<BondRow> &rows)
     h->bonds_compiled = false;
     h->nbond_rows = 0;
     rows.clear();
-    if (!h->specialize) return;
     int const T2 = h->hp.ntypes * h->hp.ntypes;
     int used = 0;
+    // the block of every used forcefield is fixed by the order of registration (the list build resolves
+    // bonds to rows of these blocks: bd_nlist.cuh resolve_bond), whether or not the tables compile
+    for (int f = 0; f < BD_MAX_BOND_FF; f++)
+        if (h->bond[f].used) h->bond_slot[f] = (uint8_t) used++;
+    if (!h->specialize) return;
     for (int f = 0; f < BD_MAX_BOND_FF; f++) {
         if (!h->bond[f].used) continue;
-        h->bond_slot[f] = (uint8_t) used++;
         const DTerm *tab = h->hterms.data() + h->bond[f].term_off;
         int const nterms = h->bond[f].nterms;
         for (int c = 0; c < T2; c++) {
-            BondRow row = {0.0, 0.0, 1.0, BD_TERM_NONE, 0};
+            BondRow row = {0.0, 0.0, 0.0, 0.0};  // none: factor 0
             int live = 0;
             for (int k = 0; k < nterms; k++) {
                 const DTerm &t = tab[c * nterms + k];
@@ -316,9 +319,14 @@ static void compile_bond_rows(bd_engine *h, std::vector<BondRow> &rows)
                 if (++live > 1 || t.cutoff2 != 0.0) return;
                 if (t.kind != BD_TERM_HARMONIC && t.kind != BD_TERM_SPRING && t.kind != BD_TERM_SEMISPRING) return;
                 row.k = t.energy;
-                row.b = t.length;
                 row.factor = t.factor;
-                row.kind = t.kind;
+                if (t.kind == BD_TERM_HARMONIC) {
+                    row.kb = 0.0;
+                    row.b2 = -1.0;
+                } else {
+                    row.kb = t.energy * t.length;  // K * b, as (K * b) / r is evaluated (spring_potential.hpp:37)
+                    row.b2 = t.kind == BD_TERM_SPRING ? 0.0 : t.length * t.length;
+                }
             }
             rows.push_back(row);
         }
@@ -563,7 +571,7 @@ extern "C" int bd_destroy(bd_engine *h)
                     &h->block_sum, &h->plen, &h->nnbr, &h->bond_start, &h->bend_start, &h->bend_adj, &h->triples})
         b->release();
     for (auto *b : {&h->force, &h->wprev, &h->xyz_stage, &h->wall_partial, &h->wall_out, &h->energy_partial,
-                    &h->energy_out, &h->dt_prev, &h->dt_last, &h->bend_energy, &h->replay, &h->xyz_all, &h->ext})
+                    &h->energy_out, &h->dt_prev, &h->dt_last, &h->bend_energy, &h->replay, &h->xyz_all, &h->xyz_out, &h->ext})
         b->release();
     for (auto *b : {&h->inter_partial, &h->dt_bits, &h->pair_count}) b->release();
     for (auto *b : {&h->d_type, &h->d_pair_mask, &h->d_point_mask, &h->bend_ff, &h->order, &h->d_owned}) b->release();
@@ -683,15 +691,24 @@ extern "C" int bd_set_all_positions(bd_engine *h, const double *xyz)
     return scatter_tracked(h, h->xyz_all.p, 0, h->ntot);
 }
 
-extern "C" int bd_get_all_positions(bd_engine *h, double *xyz)
+/* enqueue the download and return: the data is there after bd_sync (xyz must be pinned for the copy to be
+ * asynchronous).  Several engines on their own streams -- chunks of one replica ensemble -- overlap the
+ * upload of one chunk, the step of another and the download of a third this way (ensemble.HostPipeline). */
+extern "C" int bd_get_all_positions_async(bd_engine *h, double *xyz)
 {
     NEED(h);
     if (h->ntot == 0) return 0;
-    if (h->xyz_all.count < 3 * (size_t) h->ntot) CK(h->xyz_all.alloc(3 * (size_t) h->ntot));
-    k_gather_positions<<<blocks_for(h->ntot, 256), 256, 0, h->stream>>>(h->pos[h->cur].p, h->slot_of.p, h->xyz_all.p, 0, h->ntot);
+    if (h->xyz_out.count < 3 * (size_t) h->ntot) CK(h->xyz_out.alloc(3 * (size_t) h->ntot));
+    k_gather_positions<<<blocks_for(h->ntot, 256), 256, 0, h->stream>>>(h->pos[h->cur].p, h->slot_of.p, h->xyz_out.p, 0, h->ntot);
     h->launches++;
     CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(xyz, h->xyz_all.p, 3 * (size_t) h->ntot * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(xyz, h->xyz_out.p, 3 * (size_t) h->ntot * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    return 0;
+}
+
+extern "C" int bd_get_all_positions(bd_engine *h, double *xyz)
+{
+    if (bd_get_all_positions_async(h, xyz)) return 1;
     return sync_and_check(h);
 }
 
@@ -1088,6 +1105,9 @@ static NlistArrays nlist_arrays(bd_engine *h)
     A.bondrow = h->bondrow.p;
     A.bond_start = h->bond_start.p;
     A.bond_adj = h->bond_adj.p;
+    A.type = h->d_type.p;
+    for (int f = 0; f < BD_MAX_BOND_FF; f++) A.bond_slot[f] = h->bond_slot[f];
+    A.ntypes = (uint32_t) h->hp.ntypes;
     A.bond_deg = h->bond_deg;
     A.npad = h->npad;
     A.pstride = h->pstride;
@@ -1180,7 +1200,7 @@ static void launch_force_box(int prog, dim3 grid, cudaStream_t st, const StepArr
 
 static void launch_step(bd_engine *h, const StepArrays &A, const StepScalars &S)
 {
-    dim3 const grid(h->chunks, h->replicas);
+    dim3 const grid((h->chunks + STEP_TILES - 1) / STEP_TILES, h->replicas);
     if (h->hp.box_kind == BD_BOX_PERIODIC) launch_step_box<BD_BOX_PERIODIC>(h->prog, grid, h->stream, A, S);
     else launch_step_box<BD_BOX_OPEN>(h->prog, grid, h->stream, A, S);
 }

@@ -46,6 +46,9 @@ struct NlistArrays {
     uint2 *bondrow;          // [bond_deg][pstride] {partner slot, ff | second << 8}, 0xffffffff slot = none
     const uint32_t *bond_start;  // CSR of all bond forcefields by original index (bd_engine.cu: upload_topology)
     const uint2 *bond_adj;
+    const uint8_t *type;     // [n] bead class by original index
+    uint8_t bond_slot[BD_MAX_BOND_FF];  // bond forcefield -> block of the compiled bond table (bd_step.cuh: BondRow)
+    uint32_t ntypes;
     uint32_t bond_deg;       // largest number of bonds on one bead
     uint32_t npad, pstride;
     DControl *ctl;
@@ -529,6 +532,18 @@ __global__ void __launch_bounds__(ROWS_BLOCK) k_rows(NlistArrays A)
     }
 }
 
+/* one bond of bead `oi` (CSR entry {partner original index, ff | second << 8}) as the step kernel wants it:
+ * {partner slot, row of the compiled bond table | ff << 12 | second << 15} -- classes do not change between
+ * list builds, so the (class_first, class_second) cell of the table is resolved here, once */
+__device__ inline uint2 resolve_bond(const NlistArrays &A, uint32_t replica, uint32_t oi, uint2 adj)
+{
+    uint32_t const f = adj.y & 0xffu, second = (adj.y >> 8) & 1u;
+    uint32_t const ti = A.type[oi], tj = A.type[adj.x];
+    uint32_t const cell = second ? tj * A.ntypes + ti : ti * A.ntypes + tj;
+    uint32_t const row = A.bond_slot[f] * A.ntypes * A.ntypes + cell;
+    return make_uint2(A.slot_of[replica * A.n + adj.x], (row & 0xfffu) | (f << 12) | (second << 15));
+}
+
 /* Thread -> bead assignment of the step kernels.  Inside every tile of BAL_TILE consecutive slots
  * the beads are ranked by row length, so that the 32 rows a warp walks in lockstep end together (row
  * lengths inside one tile of a polymer melt differ by 4x; unranked, half of the lanes idle).  The
@@ -582,11 +597,8 @@ __global__ void __launch_bounds__(BAL_TILE) k_balance(NlistArrays A)
             uint32_t k = 0;
             if (owner) {
                 uint32_t const oi = w_orig(A.bpos[base + from].w);
-                for (uint32_t c = A.bond_start[oi]; c < A.bond_start[oi + 1] && k < A.bond_deg; c++, k++) {
-                    uint2 const adj = A.bond_adj[c];
-                    A.bondrow[(size_t) k * A.pstride + pbase + threadIdx.x] =
-                        make_uint2(A.slot_of[replica * A.n + adj.x], adj.y);
-                }
+                for (uint32_t c = A.bond_start[oi]; c < A.bond_start[oi + 1] && k < A.bond_deg; c++, k++)
+                    A.bondrow[(size_t) k * A.pstride + pbase + threadIdx.x] = resolve_bond(A, replica, oi, A.bond_adj[c]);
             }
             for (; k < A.bond_deg; k++)
                 A.bondrow[(size_t) k * A.pstride + pbase + threadIdx.x] = make_uint2(0xffffffffu, 0u);
@@ -609,10 +621,8 @@ __global__ void __launch_bounds__(BAL_TILE) k_bond_rows(NlistArrays A)
         if (live) {
             uint32_t const from = A.order[base + threadIdx.x];
             uint32_t const oi = w_orig(A.bpos[base + from].w);
-            for (uint32_t c = A.bond_start[oi]; c < A.bond_start[oi + 1] && k < A.bond_deg; c++, k++) {
-                uint2 const adj = A.bond_adj[c];
-                A.bondrow[(size_t) k * A.pstride + pbase + threadIdx.x] = make_uint2(A.slot_of[replica * A.n + adj.x], adj.y);
-            }
+            for (uint32_t c = A.bond_start[oi]; c < A.bond_start[oi + 1] && k < A.bond_deg; c++, k++)
+                A.bondrow[(size_t) k * A.pstride + pbase + threadIdx.x] = resolve_bond(A, replica, oi, A.bond_adj[c]);
         }
         for (; k < A.bond_deg; k++) A.bondrow[(size_t) k * A.pstride + pbase + threadIdx.x] = make_uint2(0xffffffffu, 0u);
     }

@@ -124,11 +124,44 @@ struct __align__(16) PairRow {
     double ca, cb, k2a, k2b;
 };
 
-/* one row of a compiled bond table: a single harmonic / spring / semispring term (or none) */
+/* one row of a compiled bond table: a single harmonic / spring / semispring term (or none), in the form
+ * the kernel evaluates without looking at the kind:
+ *     scalar = factor * (r2 > b2 ? kb / |r| - k : 0)
+ * spring (MD/potential/spring_potential.hpp:32-39):      kb = K b, b2 = 0    (acts unless r = 0)
+ * semispring (semispring_potential.hpp:37-44):           kb = K b, b2 = b^2  (acts beyond b)
+ * harmonic (harmonic_potential.hpp:29-32):               kb = 0,   b2 = -1   (always: scalar = -K factor)
+ * none:                                                  factor = 0 */
 struct __align__(16) BondRow {
-    double k, b, factor;
-    int32_t kind, pad;
+    double kb, k, b2, factor;
 };
+
+/* bondrow[].y: row of the compiled bond table (bits 0-11, resolved at the list build: bd_nlist.cuh),
+ * forcefield (bits 12-14), "this bead is the second of the pair" (bit 15) */
+constexpr uint32_t BOND_ROW_MASK = 0xfffu;
+__host__ __device__ inline uint32_t bond_word(uint32_t row, uint32_t ff, uint32_t second)
+{
+    return (row & BOND_ROW_MASK) | (ff << 12) | (second << 15);
+}
+
+/* shared memory through 32-bit shared-space addresses: the generic-pointer forms make the compiler rebuild
+ * the shared window base inside the pair loops (S2R SR_CgaCtaId + LEA per access in the round-1 SASS) */
+__device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t) __cvta_generic_to_shared(p); }
+__device__ __forceinline__ void sts_u32(uint32_t addr, uint32_t v)
+{
+    asm volatile("st.shared.u32 [%0], %1;" :: "r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ double lds_f64(uint32_t addr)  // read-only tables: free to be scheduled
+{
+    double v;
+    asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+    return v;
+}
 
 template <int BOX>
 __device__ __forceinline__ d3 displacement_t(const DParams &P, double ax, double ay, double az, double bx,
@@ -168,6 +201,9 @@ struct StepShared {
     alignas(16) DParams P;
     alignas(16) DGrid G;
     float filter2;  // widened cutoff^2 of the shadow pre-filter
+    uint32_t bond_on, bond_image;  // per bond forcefield (bit f): selected and enabled / uses the box
+    // per bead class, for the timestep of this launch (fused kernel): mobility * dt, noise amplitudes
+    double mu_dt[BD_MAX_TYPES], sigma[BD_MAX_TYPES], sigma_prev[BD_MAX_TYPES];
     uint32_t hits[HIT_CAP][STEP_BLOCK];
     double wall_red[STEP_BLOCK / 32][BD_MAX_WALL_FF][WALL_STATS];
 };
@@ -202,8 +238,21 @@ __device__ __forceinline__ void pair_forces(const StepArrays &A, StepShared &sh,
     uint32_t const m = (A.plen[pos] + ROW_PAD - 1) & ~(ROW_PAD - 1);  // rows are padded with the sentinel
     float4 const ms = A.shadow[s];
     const uint4 *col = A.nbr4 + pos;
-    uint32_t *queue = &sh.hits[0][threadIdx.x];
+    // the thread's queue column and its row of the compiled pair table, as shared-space addresses
+    constexpr uint32_t QSTEP = STEP_BLOCK * 4u;  // bytes between consecutive entries of one thread's queue
+    uint32_t const queue = smem_addr(&sh.hits[0][threadIdx.x]);
+    uint32_t const qfull = queue + (HIT_CAP - ROW_PAD) * QSTEP;
+    uint32_t const cav = smem_addr(dyn_smem) + ti * (uint32_t) T * 8u;  // uniform tables: ca[T*T] then cb[T*T]
 
+#ifdef EXP_SMEM_P1
+    __shared__ float4 exp_fake[1024];
+    for (uint32_t i = threadIdx.x; i < 1024; i += blockDim.x) exp_fake[i] = A.shadow[min((s & ~127u) + i, A.ntot)];
+#ifdef EXP_SMEM_P2
+    __shared__ bead4 exp_fake2[512];
+    for (uint32_t i = threadIdx.x; i < 512; i += blockDim.x) exp_fake2[i] = A.pos[min((s & ~127u) + i, A.ntot)];
+#endif
+    __syncthreads();
+#endif
     uint32_t k = 0;
     uint32_t j[ROW_PAD], jn[ROW_PAD];
     if (m) {
@@ -214,12 +263,15 @@ __device__ __forceinline__ void pair_forces(const StepArrays &A, StepShared &sh,
         // ---- phase 1: single-precision filter ------------------------------------------------
         // the indices of the next group are requested together with the shadows of this one, so
         // only the gather itself is on the dependent path
-        uint32_t *qp = queue;
-        uint32_t *const qfull = queue + (HIT_CAP - ROW_PAD) * STEP_BLOCK;
+        uint32_t qp = queue;
         while (k < m && qp <= qfull) {
             float4 q[ROW_PAD];
 #pragma unroll
+#ifdef EXP_SMEM_P1
+            for (int u = 0; u < (int) ROW_PAD; u++) q[u] = exp_fake[j[u] & 1023u];
+#else
             for (int u = 0; u < (int) ROW_PAD; u++) q[u] = __ldg(A.shadow + j[u]);
+#endif
             col += stride;
             k += ROW_PAD;
             if (k < m) {
@@ -229,23 +281,30 @@ __device__ __forceinline__ void pair_forces(const StepArrays &A, StepShared &sh,
 #pragma unroll
             for (int u = 0; u < (int) ROW_PAD; u++) {
                 bool near = shadow_dist2<BOX>(ms, q[u], scale) <= filter2;
+#ifdef EXP_SMEM_P1
+                near = (near && q[u].w == 12345.0f) || (((j[u] * 2654435761u) >> 24) < 83u && j[u] < A.ntot);
+#endif
                 if (BOX == BD_BOX_PERIODIC) near = near && j[u] < A.ntot;  // fixed point has no NaN
                 if (near) {
-                    *qp = j[u];
-                    qp += STEP_BLOCK;
+                    sts_u32(qp, j[u]);
+                    qp += QSTEP;
                 }
             }
 #pragma unroll
             for (int u = 0; u < (int) ROW_PAD; u++) j[u] = jn[u];
         }
-        uint32_t const cnt = (uint32_t) (qp - queue) / STEP_BLOCK;
-        if (cnt & 1u) queue[cnt * STEP_BLOCK] = A.ntot;  // phase 2 takes the queue two at a time
+        if (((qp - queue) / QSTEP) & 1u) sts_u32(qp, A.ntot);  // phase 2 takes the queue two at a time
 
         // ---- phase 2: exact evaluation -------------------------------------------------------
-        for (uint32_t c = 0; c < cnt; c += 2) {
-            uint32_t const j0 = queue[c * STEP_BLOCK], j1 = queue[(c + 1) * STEP_BLOCK];
+        for (uint32_t qa = queue; qa < qp; qa += 2 * QSTEP) {
+            uint32_t const j0 = lds_u32(qa), j1 = lds_u32(qa + QSTEP);
+#ifdef EXP_SMEM_P2
+            bead4 const o0 = exp_fake2[j0 & 511u];
+            bead4 const o1 = exp_fake2[j1 & 511u];
+#else
             bead4 const o0 = load_bead(A.pos + j0);
             bead4 const o1 = load_bead(A.pos + j1);
+#endif
 #pragma unroll
             for (int u = 0; u < 2; u++) {
                 const bead4 &o = u == 0 ? o0 : o1;
@@ -253,16 +312,15 @@ __device__ __forceinline__ void pair_forces(const StepArrays &A, StepShared &sh,
                 double const r2 = sqnorm_exact(r.x, r.y, r.z);  // NaN for the sentinel: every test fails
                 if (PROG != PROG_GENERIC) {
                     if (r2 <= dcut2) {
-                        const PairRow &row = mine[w_type(o.w)];
                         double sc;
                         if (A.k2_uniform) {
                             // uniform tables are stored as two arrays of doubles, ca[T*T] then cb[T*T]: 8-byte
                             // reads of 16 or fewer distinct rows never collide on a shared-memory bank
-                            uint32_t const cell = ti * (uint32_t) T + w_type(o.w);
-                            const double *cav = reinterpret_cast<const double *>(dyn_smem);
-                            sc = compiled_pair_scalar<PROG>(cav[cell], PROG == PROG_SC23_SC83 ? cav[A.ntypes2 + cell] : 0.0,
+                            uint32_t const at = cav + w_type(o.w) * 8u;
+                            sc = compiled_pair_scalar<PROG>(lds_f64(at), PROG == PROG_SC23_SC83 ? lds_f64(at + A.ntypes2 * 8u) : 0.0,
                                                             A.k2a, A.k2b, r2);
                         } else {
+                            const PairRow &row = mine[w_type(o.w)];
                             sc = compiled_pair_scalar<PROG>(row.ca, row.cb, row.k2a, row.k2b, r2);
                         }
                         F.x += sc * r.x; F.y += sc * r.y; F.z += sc * r.z;
@@ -289,17 +347,19 @@ __device__ __forceinline__ void pair_forces(const StepArrays &A, StepShared &sh,
 }
 
 /* bonded pairs, bending triples and point sources acting on one bead */
-__device__ __forceinline__ void bonded_forces(const StepArrays &A, const DParams &P, Select sel,
+__device__ __forceinline__ void bonded_forces(const StepArrays &A, const StepShared &sh, Select sel,
                                               uint32_t replica, uint32_t pos, const bead4 &me, d3 &F)
 {
+    const DParams &P = sh.P;
     uint32_t const oi = w_orig(me.w), ti = w_type(me.w);
     int const T = P.ntypes;
     uint32_t const base = replica * A.n;
 
     // bonded pairs (no minimum image: bonded_pairwise_forcefield.hpp:64); the partners were resolved
-    // to slots at the last rebuild (bd_nlist.cuh: k_balance)
+    // to slots, and their rows of the compiled table chosen, at the last rebuild (bd_nlist.cuh: k_balance)
     {
-        const BondRow *brows = reinterpret_cast<const BondRow *>(dyn_smem + A.ntypes2 * sizeof(PairRow));
+        uint32_t const brows = smem_addr(dyn_smem) + A.ntypes2 * (uint32_t) sizeof(PairRow);
+        uint32_t const on_mask = sh.bond_on, image_mask = sh.bond_image;
         // software pipeline: the next bond's row entry and partner record are requested while this
         // bond is evaluated (the loop was bound by these two dependent loads)
         const uint2 *col = A.bondrow + pos;
@@ -313,34 +373,32 @@ __device__ __forceinline__ void bonded_forces(const StepArrays &A, const DParams
             col += A.pstride;
             adj_next = k + 1 < A.bond_deg ? *col : make_uint2(0xffffffffu, 0u);
             if (adj_next.x != 0xffffffffu) o_next = load_bead(A.pos + adj_next.x);
-            int const f = adj.y & 0xff;
-            const DBond &bf = P.bond[f];
-            if (!ff_on(sel, BD_FF_BOND, f, bf.enabled)) continue;
-            uint32_t const tj = w_type(o.w);
-            bool const second = (adj.y >> 8) & 1u;
+            uint32_t const f = (adj.y >> 12) & 7u;
+            if (!((on_mask >> f) & 1u)) continue;
             // the force on this bead is scalar * (x_me - x_partner) whichever end it is; only the
             // table row depends on the order (type_first, type_second)
             double rx = me.x - o.x, ry = me.y - o.y, rz = me.z - o.z;
-            if (bf.min_image) {  // a dynamic pair list of glue_forcefield's kind (glue_forcefield.cpp:40)
+            if ((image_mask >> f) & 1u) {  // a dynamic pair list of glue_forcefield's kind (glue_forcefield.cpp:40)
                 d3 const r = displacement(P, me.x, me.y, me.z, o.x, o.y, o.z);
                 rx = r.x; ry = r.y; rz = r.z;
             }
             double const r2 = rx * rx + ry * ry + rz * rz;
-            int const cell = second ? (int) (tj * T + ti) : (int) (ti * T + tj);
             double sc;
             if (A.bonds_compiled) {
-                // single-term tables compiled on the host; same arithmetic as term_force_scalar
-                BondRow const row = brows[A.bond_slot[f] * A.ntypes2 + cell];
+                // single-term tables compiled on the host (BondRow): K b / |r| - K through rsqrt
+                uint32_t const at = brows + (adj.y & BOND_ROW_MASK) * (uint32_t) sizeof(BondRow);
+                double const kb = lds_f64(at), kk = lds_f64(at + 8), b2 = lds_f64(at + 16);
                 double v = 0.0;
-                if (row.kind == BD_TERM_HARMONIC) {
-                    v = -row.k;
-                } else if (row.kind != BD_TERM_NONE) {
-                    double const r1 = sqrt(r2);
-                    bool const on = row.kind == BD_TERM_SPRING ? r1 != 0.0 : r1 > row.b;
-                    if (on) v = row.k * row.b / r1 - row.k;
+                if (r2 > b2) {
+                    v = -kk;
+                    if (kb != 0.0) v = kb * rsqrt(r2) - kk;
                 }
-                sc = row.factor * v;
+                sc = lds_f64(at + 24) * v;
             } else {
+                const DBond &bf = P.bond[f];
+                uint32_t const tj = w_type(o.w);
+                bool const second = (adj.y >> 15) & 1u;
+                int const cell = second ? (int) (tj * T + ti) : (int) (ti * T + tj);
                 sc = pot_force_scalar(A.terms + bf.term_off + cell * bf.nterms, bf.nterms, r2);
             }
             F.x += sc * rx; F.y += sc * ry; F.z += sc * rz;
@@ -486,6 +544,13 @@ __device__ __forceinline__ void load_shared(StepShared &sh, const StepArrays &A,
             if (ff_on(sel, BD_FF_PAIR, f, sh.P.pair[f].enabled)) dcut = fmax(dcut, sh.P.pair[f].dcut);
         double const wide = dcut + sh.G.shadow_eps;
         sh.filter2 = __double2float_ru(wide * wide * (1.0 + 4e-6));
+        uint32_t on = 0, image = 0;
+        for (int f = 0; f < BD_MAX_BOND_FF; f++) {
+            if (ff_on(sel, BD_FF_BOND, f, sh.P.bond[f].enabled)) on |= 1u << f;
+            if (sh.P.bond[f].min_image) image |= 1u << f;
+        }
+        sh.bond_on = on;
+        sh.bond_image = image;
     }
     __syncthreads();
 }
@@ -502,7 +567,7 @@ __device__ __forceinline__ d3 block_forces(const StepArrays &A, StepShared &sh, 
     uint32_t const pos = replica * A.npad + chunk * STEP_BLOCK + threadIdx.x;
     if (live) {
         pair_forces<BOX, PROG>(A, sh, sel, s, pos, me, F, interactions);
-        bonded_forces(A, P, sel, replica, pos, me, F);
+        bonded_forces(A, sh, sel, replica, pos, me, F);
         if (A.ext && sel.ff_class == BD_FF_ALL) {
             const double *e = A.ext + 3 * ((size_t) replica * A.n + w_orig(me.w));
             F.x += e[0]; F.y += e[1]; F.z += e[2];
@@ -516,11 +581,17 @@ __device__ __forceinline__ d3 block_forces(const StepArrays &A, StepShared &sh, 
         any_wall = true;
         double st[WALL_STATS] = {0.0, 0.0, 0.0, 0.0};
         if (live) wall_force(A, wf, me, F, st);
-        if (!want_stats) continue;  // block-uniform: only the last step of a call is observable
+        if (!want_stats) continue;  // block-uniform: the last step of a call, or every step with wall relaxation
+        // most warps are nowhere near the wall: all their statistics are exactly zero and need no reduction
+        bool const touched = st[0] != 0.0 || st[1] != 0.0 || st[2] != 0.0 || st[3] != 0.0;
+        if (__any_sync(0xffffffffu, touched)) {
 #pragma unroll
-        for (int c = 0; c < WALL_STATS; c++) {
-            for (int o = 16; o > 0; o >>= 1) st[c] += __shfl_xor_sync(0xffffffffu, st[c], o);
-            if ((threadIdx.x & 31) == 0) sh.wall_red[threadIdx.x >> 5][f][c] = st[c];
+            for (int c = 0; c < WALL_STATS; c++)
+                for (int o = 16; o > 0; o >>= 1) st[c] += __shfl_xor_sync(0xffffffffu, st[c], o);
+        }
+        if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+            for (int c = 0; c < WALL_STATS; c++) sh.wall_red[threadIdx.x >> 5][f][c] = st[c];
         }
     }
     if (any_wall && want_stats) {
@@ -533,6 +604,7 @@ __device__ __forceinline__ d3 block_forces(const StepArrays &A, StepShared &sh, 
                 A.wall_partial[(((size_t) replica * A.chunks + chunk) * BD_MAX_WALL_FF + f) * WALL_STATS + c] = t;
             }
         }
+        __syncthreads();  // the fused kernel comes back with the block's next tile
     }
     return F;
 }
@@ -546,17 +618,16 @@ __device__ inline void load_params(DParams &P, const DParams *src)
 
 
 /* MD/simulation/detail/brownian_simulator.hpp:57-75 for one bead; returns the squared distance
- * from the bead's position at the last list build (neighbor_list.hpp:138-157) */
+ * from the bead's position at the last list build (neighbor_list.hpp:138-157).
+ * mu_dt = timestep * mobility, sigma = sqrt(2 kT mu_dt), sigma_prev the same for the previous step
+ * (brownian_simulator.hpp:57-62): per bead class, computed by the caller. */
 template <int BOX>
 __device__ __forceinline__ double integrate_bead(const StepArrays &A, const DParams &P, const DGrid &G,
                                                  const StepScalars &S,
                                                  uint32_t s, uint32_t replica, const bead4 &me, d3 F,
-                                                 double dt, double dt_prev)
+                                                 double mu_dt, double sigma, double sigma_prev)
 {
     uint32_t const oi = w_orig(me.w);
-    double const mu = P.mobility[w_type(me.w)];
-    double const mu_dt = dt * mu;
-    double const sigma = sqrt(2.0 * S.kT * mu_dt);
     double wx, wy, wz, px, py, pz;
     size_t const g = (size_t) replica * A.n + oi;
     if (S.replay) {
@@ -568,9 +639,8 @@ __device__ __forceinline__ double integrate_bead(const StepArrays &A, const DPar
         philox_normals(S.seed, (uint64_t) S.step, S.replica_base + replica * S.replica_stride, oi, z);
         wx = sigma * z[0]; wy = sigma * z[1]; wz = sigma * z[2];
         if (S.step > 1) {
-            double const sp = sqrt(2.0 * S.kT_prev * (dt_prev * mu));
             philox_normals(S.seed, (uint64_t) (S.step - 1), S.replica_base + replica * S.replica_stride, oi, z);
-            px = sp * z[0]; py = sp * z[1]; pz = sp * z[2];
+            px = sigma_prev * z[0]; py = sigma_prev * z[1]; pz = sigma_prev * z[2];
         } else {
             px = py = pz = 0.0;
         }
@@ -607,30 +677,52 @@ __device__ __forceinline__ void publish_displacement(const StepArrays &A, double
         atomicMax(&A.ctl->max_disp2_bits, (unsigned long long) __double_as_longlong(moved2));
 }
 
-/* the hot kernel: forces + Brownian update + skin test, fixed timestep */
+/* the hot kernel: forces + Brownian update + skin test, fixed timestep.
+ * One block advances STEP_TILES consecutive 128-bead tiles of one replica, so that the per-block set-up
+ * (parameter block, this replica's walls, compiled tables, noise amplitudes per class: 7 % of the
+ * instructions of the one-tile-per-block kernel) is paid once per STEP_TILES * 128 beads. */
+#ifndef STEP_TILES_PER_BLOCK
+#define STEP_TILES_PER_BLOCK 1
+#endif
+constexpr int STEP_TILES = STEP_TILES_PER_BLOCK;
+
 template <int BOX, int PROG>
 __global__ void __launch_bounds__(STEP_BLOCK, STEP_MIN_BLOCKS) k_step_fused(StepArrays A, StepScalars S)
 {
     __shared__ StepShared sh;
     Select const all = {BD_FF_ALL, -1};
     load_shared<PROG>(sh, A, all);
-    uint32_t const replica = blockIdx.y, chunk = blockIdx.x;
-    bool const live = chunk * STEP_BLOCK + threadIdx.x < A.n;
-    // threads take the tile's beads in order of row length, so that the rows of a warp end together
-    uint32_t const s = replica * A.n
-        + (live ? chunk * STEP_BLOCK + A.order[replica * A.n + chunk * STEP_BLOCK + threadIdx.x] : 0u);
-    uint32_t inter = 0;
+    uint32_t const replica = blockIdx.y;
+    if (threadIdx.x < (uint32_t) sh.P.ntypes) {
+        // brownian_simulator.hpp:57-62, once per bead class instead of once per bead
+        double const mu = sh.P.mobility[threadIdx.x];
+        double const mu_dt = S.dt * mu;
+        sh.mu_dt[threadIdx.x] = mu_dt;
+        sh.sigma[threadIdx.x] = sqrt(2.0 * S.kT * mu_dt);
+        sh.sigma_prev[threadIdx.x] = sqrt(2.0 * S.kT_prev * (S.dt_prev * mu));
+    }
+    __syncthreads();
     double const known = __longlong_as_double((long long) A.ctl->max_disp2_bits);
-    bead4 const me = load_bead(A.pos + s);
-    bool const active = live && !w_ghost(me.w);
-    d3 const F = block_forces<BOX, PROG>(A, sh, all, active, S.want_stats != 0, s, replica, chunk, me, inter);
     double moved2 = 0.0;
-    if (active) moved2 = integrate_bead<BOX>(A, sh.P, sh.G, S, s, replica, me, F, S.dt, S.dt_prev);
-    else if (live) moved2 = carry_ghost<BOX>(A, sh.P, sh.G, s, me);
+    uint32_t const last = min((blockIdx.x + 1) * STEP_TILES, A.chunks);
+    for (uint32_t chunk = blockIdx.x * STEP_TILES; chunk < last; chunk++) {
+        bool const live = chunk * STEP_BLOCK + threadIdx.x < A.n;
+        // threads take the tile's beads in order of row length, so that the rows of a warp end together
+        uint32_t const s = replica * A.n
+            + (live ? chunk * STEP_BLOCK + A.order[replica * A.n + chunk * STEP_BLOCK + threadIdx.x] : 0u);
+        uint32_t inter = 0;
+        bead4 const me = load_bead(A.pos + s);
+        bool const active = live && !w_ghost(me.w);
+        d3 const F = block_forces<BOX, PROG>(A, sh, all, active, S.want_stats != 0, s, replica, chunk, me, inter);
+        uint32_t const t = w_type(me.w);
+        if (active) moved2 = fmax(moved2, integrate_bead<BOX>(A, sh.P, sh.G, S, s, replica, me, F, sh.mu_dt[t], sh.sigma[t],
+                                                             sh.sigma_prev[t]));
+        else if (live) moved2 = fmax(moved2, carry_ghost<BOX>(A, sh.P, sh.G, s, me));
+        for (int o = 16; o > 0; o >>= 1) inter += __shfl_xor_sync(0xffffffffu, inter, o);
+        if ((threadIdx.x & 31) == 0)  // one private counter per warp: no barrier, no atomics
+            A.inter_partial[((size_t) replica * A.chunks + chunk) * (STEP_BLOCK / 32) + (threadIdx.x >> 5)] += inter;
+    }
     publish_displacement(A, moved2, known);
-    for (int o = 16; o > 0; o >>= 1) inter += __shfl_xor_sync(0xffffffffu, inter, o);
-    if ((threadIdx.x & 31) == 0)  // one private counter per warp: no barrier, no atomics
-        A.inter_partial[((size_t) replica * A.chunks + chunk) * (STEP_BLOCK / 32) + (threadIdx.x >> 5)] += inter;
 }
 
 /* forces only (compute_forces, and the first pass of an adaptive-timestep step) */
@@ -688,8 +780,14 @@ __global__ void __launch_bounds__(STEP_BLOCK) k_integrate(StepArrays A, StepScal
         bead4 const me = load_bead(A.pos + s);
         d3 const F = {A.force[3 * (size_t) s], A.force[3 * (size_t) s + 1], A.force[3 * (size_t) s + 2]};
         double const dt = __longlong_as_double((long long) A.dt_bits[replica]);
-        if (w_ghost(me.w)) moved2 = carry_ghost<BOX>(A, P, G, s, me);
-        else moved2 = integrate_bead<BOX>(A, P, G, S, s, replica, me, F, dt, A.dt_prev[replica]);
+        if (w_ghost(me.w)) {
+            moved2 = carry_ghost<BOX>(A, P, G, s, me);
+        } else {
+            double const mu = P.mobility[w_type(me.w)];
+            double const mu_dt = dt * mu;
+            moved2 = integrate_bead<BOX>(A, P, G, S, s, replica, me, F, mu_dt, sqrt(2.0 * S.kT * mu_dt),
+                                         sqrt(2.0 * S.kT_prev * (A.dt_prev[replica] * mu)));
+        }
     }
     publish_displacement(A, moved2, known);
 }

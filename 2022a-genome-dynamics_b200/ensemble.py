@@ -145,3 +145,79 @@ class ReplicaEnsemble:
         for s in self.systems:
             s.close()
         self.systems = []
+
+
+class HostPipeline:
+    """A replica ensemble driven through HOST buffers every step -- the path of a driver whose per-step
+    callback reads and may rewrite all positions (MD/simulation/brownian_dynamics.hpp:66-72) -- with the
+    PCIe copies hidden behind the compute.
+
+    The local replicas are split into `chunks` engines, each on its own CUDA stream.  One step is, per
+    chunk, upload -> bd_step(1) -> download, all enqueued without waiting; the copy engines move chunk
+    k + 1 in and chunk k - 1 out while chunk k computes (PCIe is full duplex, replicas are independent),
+    and one synchronisation at the end of the step hands the host buffer back to the caller.  Noise keys
+    are the global replica ids, so the trajectories equal those of the single-engine ensemble.
+
+    host_in / host_out are pinned [n_local, n, 3] float64 buffers (torch tensors or anything with
+    data_ptr()); they may be the same buffer."""
+
+    def __init__(self, backend: bd.Backend, scenario, n_local: int, chunks: int = 8, rank: int = 0, world: int = 1,
+                 device: int = 0, seed: int = 0, setup=None):
+        if backend.prefix != "bd_":
+            raise ValueError("HostPipeline drives the B200 engine")
+        import torch
+
+        self.scenario, self.n_local, self.seed = scenario, int(n_local), int(seed)
+        chunks = max(1, min(int(chunks), self.n_local))
+        per = -(-self.n_local // chunks)
+        self.spans = [(a, min(a + per, self.n_local)) for a in range(0, self.n_local, per)]
+        self.systems, self.streams, self.ids = [], [], []
+        for a, b in self.spans:
+            s = bd.System(backend, scenario.n, b - a, device=device)
+            ids = scenario.apply(s, replicas=[])
+            st = torch.cuda.Stream(device=device)
+            s.set_stream(st.cuda_stream)
+            s.set_option("replica_id_base", rank + world * a)
+            s.set_option("replica_id_stride", world)
+            if setup is not None:
+                setup(s, ids)
+            self.systems.append(s)
+            self.streams.append(st)
+            self.ids.append(ids)
+        self.bytes_per_replica = scenario.n * 24
+        self.steps_done = 0
+
+    def upload(self, host):
+        for s, (a, _) in zip(self.systems, self.spans):
+            s.set_all_positions(host.data_ptr() + a * self.bytes_per_replica)
+
+    def step_resident(self, steps: int, timestep: float, temperature: float):
+        """steps without touching the host (relaxation, warm-up)"""
+        for s in self.systems:
+            s.step(steps, timestep, temperature, seed=self.seed, first_step=self.steps_done + 1)
+        self.steps_done += steps
+
+    def step_through_host(self, host_in, host_out, timestep: float, temperature: float, before_step=None):
+        """one BD step of every replica: positions come from host_in and arrive in host_out"""
+        first = self.steps_done + 1
+        for s, ids, (a, _) in zip(self.systems, self.ids, self.spans):
+            s.set_all_positions(host_in.data_ptr() + a * self.bytes_per_replica)
+            if before_step is not None:
+                before_step(s, ids)
+            s.step(1, timestep, temperature, seed=self.seed, first_step=first)
+            s.get_all_positions_async(host_out.data_ptr() + a * self.bytes_per_replica)
+        for s in self.systems:
+            s.sync()
+        self.steps_done += 1
+
+    def sync(self):
+        for s in self.systems:
+            s.sync()
+
+    def launch_count(self) -> int:
+        return sum(s.get_launch_count() for s in self.systems)
+
+    def close(self):
+        for s in self.systems:
+            s.close()
+        self.systems = []

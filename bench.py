@@ -40,29 +40,83 @@ def parse():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--replicas", type=int, default=64, help="replicas per GPU")
-    ap.add_argument("--beads", type=int, default=62000, help="chromatin beads per replica")
+    ap.add_argument("--replicas", type=int, default=None, help="replicas per GPU (default: per workload)")
+    ap.add_argument("--beads", type=int, default=62000, help="genome100kb: chromatin beads per replica")
     ap.add_argument("--relax", type=int, default=400, help="untimed relaxation steps before warm-up")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--workload", default="genome100kb", choices=["genome100kb", "slab1kb"],
-                    help="genome100kb: the headline replica ensemble (weak scaling); slab1kb: ONE 1kb chromatin system "
-                         "split into x-slabs with a per-step NCCL halo exchange (strong scaling, BASELINE configs[4])")
-    ap.add_argument("--chains", type=int, default=600, help="slab1kb: chains")
-    ap.add_argument("--chain-len", type=int, default=10000, help="slab1kb: beads per chain")
+    ap.add_argument("--no-parity", action="store_true", help="skip the force / pair-set check against the reference")
+    ap.add_argument("--chunks", type=int, default=8, help="e2e: engines (replica chunks) of the host pipeline")
+    ap.add_argument("--frozen-walls", action="store_true",
+                    help="genome100kb: keep the wall semiaxes fixed (round-1 workload) instead of the driver's per-step feedback")
+    ap.add_argument("--verlet-factor", type=float, default=None, help="list radius / dcut (engine option; reference 1.5)")
+    ap.add_argument("--workload", default="genome100kb", choices=sorted(WORKLOADS) + ["slab1kb"],
+                    help="genome100kb: the headline replica ensemble (weak scaling); ab_box / ab_sphere / genome10mb / "
+                         "chromatin1kb: the other BASELINE.json configurations on one engine per GPU; slab1kb: ONE 1kb "
+                         "chromatin system split into x-slabs with a per-step NCCL halo exchange (strong scaling)")
+    ap.add_argument("--chains", type=int, default=600, help="chromatin1kb / slab1kb: chains")
+    ap.add_argument("--chain-len", type=int, default=10000, help="chromatin1kb / slab1kb: beads per chain")
     ap.add_argument("--migrate-every", type=int, default=40, help="slab1kb: steps between ownership migrations")
     return ap.parse_args()
 
 
-def scenario(args, distinct, seed):
+# BASELINE.json configs[0..4] as bench workloads: builder(args, distinct, seed), replicas per GPU, label
+def _w_genome100kb(args, distinct, seed):
     import scenarios as sc
-
     return sc.genome_100kb(total=args.beads, n_nor=300, seed=seed, replicas=distinct)
 
 
+def _w_ab_box(args, distinct, seed):
+    import scenarios as sc
+    return sc.ab_box(200, 20, seed=seed, replicas=distinct)
+
+
+def _w_ab_sphere(args, distinct, seed):
+    import scenarios as sc
+    return sc.ab_sphere(200, 20, seed=seed, replicas=distinct)
+
+
+def _w_genome10mb(args, distinct, seed):
+    import scenarios as sc
+    return sc.genome_10mb(640, seed=seed, replicas=distinct, bend_energy=0.7)
+
+
+def _w_chromatin1kb(args, distinct, seed):
+    import scenarios as sc
+    return sc.chromatin_1kb(args.chains, args.chain_len, seed=seed, replicas=1)
+
+
+WORKLOADS = {
+    "genome100kb": dict(make=_w_genome100kb, replicas=64, label="5-sim-genome 100kb interphase"),
+    "ab_box": dict(make=_w_ab_box, replicas=1024, label="4-sim-ab/box A/B blend, periodic"),
+    "ab_sphere": dict(make=_w_ab_sphere, replicas=1024, label="4-sim-ab/sphere A/B blend in a spherical wall"),
+    "genome10mb": dict(make=_w_genome10mb, replicas=1024, label="5-sim-genome 10Mb ana/telophase"),
+    "chromatin1kb": dict(make=_w_chromatin1kb, replicas=1, label="3-sim-1kb chromatin, one periodic system"),
+}
+
+
+def scenario(args, distinct, seed):
+    return WORKLOADS[args.workload]["make"](args, distinct, seed)
+
+
+def replicas_of(args):
+    return args.replicas if args.replicas else WORKLOADS[args.workload]["replicas"]
+
+
+def wall_feedback(args, scen):
+    """the interphase driver moves the wall semiaxes after every step from the wall reaction of that system
+    (5-sim-genome/src/simulation_interphase/simulation_driver_interphase.cc:70-80); spring and mobility are the
+    reference's defaults (config_entries.inc:33,37)"""
+    if args.workload != "genome100kb" or args.frozen_walls:
+        return None
+    p = scen.params
+    return dict(spring=np.full(3, p["wall_semiaxes_spring"]), mobility=p["wall_mobility"])
+
+
 def workload_name(args, scen):
-    return f"5-sim-genome 100kb interphase, {scen.n} beads x {args.replicas} replicas per GPU"
+    tail = ", per-step wall feedback" if wall_feedback(args, scen) else ""
+    return f"{WORKLOADS[args.workload]['label']}, {scen.n} beads x {replicas_of(args)} replicas per GPU{tail}"
 
 
 class ClockSampler:
@@ -120,24 +174,91 @@ def cpu_backend():
     return checkers.load_oracle(), "port"
 
 
-def cpu_time_steps(backend, scen, start_positions, steps, threads, warm):
-    """`threads` independent replicas, each advanced `steps` BD steps by the single-threaded
-    reference code; returns wall seconds (ctypes releases the GIL, so replicas run in parallel)."""
-    import bdb200 as bd
+class _GenericReplica:
+    """one replica on the generic C entry points (oracle/_ref/libmicromd_ref.so or the oracle port); with
+    `feedback` it runs the interphase driver's per-step callback: read both walls' reaction, move the
+    semiaxes, hand them back to both walls"""
 
-    systems = []
-    for t in range(threads):
-        s = bd.System(backend, scen.n)
-        scen.apply(s, replicas=[0])
-        s.set_positions(start_positions[t % len(start_positions)])
-        systems.append(s)
+    def __init__(self, backend, scen, x, feedback):
+        import bdb200 as bd
 
-    def run(s, k, first):
+        self.s, self.scen, self.feedback = bd.System(backend, scen.n), scen, feedback
+        ids = scen.apply(self.s, replicas=[0])
+        self.s.set_positions(x)
+        self.walls = ids["wall"]
+        self.semi = np.array(scen.params["semiaxes"], dtype=np.float64) if feedback else None
+        self.done = 0
+
+    def run(self, k):
+        scen, s = self.scen, self.s
+        if k <= 0:
+            return
+        if not self.feedback:
+            s.step(k, scen.timestep, scen.temperature, seed=1, first_step=self.done + 1)
+        else:
+            for q in range(k):
+                s.step(1, scen.timestep, scen.temperature, seed=1, first_step=self.done + q + 1)
+                net = (s.get_wall_stats(self.walls[0])[1:] + s.get_wall_stats(self.walls[1])[1:]
+                       - self.feedback["spring"] * self.semi)
+                self.semi = self.semi + scen.timestep * self.feedback["mobility"] * net
+                for w in self.walls:
+                    s.update_wall_ff(w, (0, 0, 0), self.semi)
+        self.done += k
+
+    def positions(self):
+        return self.s.get_positions()
+
+    def close(self):
+        self.s.close()
+
+
+class _DriverReplica:
+    """one replica of the 100kb model registered the way the reference driver registers it -- compile-time
+    expression-template potentials, the wall feedback as the simulate_brownian_dynamics callback
+    (oracle/ref_drivers.cc, oracle/checkers.DriverC4)"""
+
+    def __init__(self, scen, x, feedback, flavour):
+        import checkers
+
+        self.d, self.feedback, self.calls = checkers.DriverC4(scen, x, flavour), feedback, 0
+
+    def run(self, k):
         if k > 0:
-            s.step(k, scen.timestep, scen.temperature, seed=1, first_step=first)
+            self.calls += 1
+            self.d.run(k, seed=self.calls, feedback=bool(self.feedback))
 
-    def fan(k, first):
-        th = [threading.Thread(target=run, args=(s, k, first)) for s in systems]
+    def positions(self):
+        return self.d.get()[0]
+
+    def close(self):
+        self.d.close()
+
+
+def cpu_flavours(args, backend_kind):
+    """the CPU builds to time: the drivers' own code path where oracle/_ref has it (genome100kb), else the
+    generic entry points"""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import checkers
+
+    if args.workload == "genome100kb" and backend_kind == "reference" and checkers.have_driver_baseline("O3"):
+        return ["driver-O3", "driver-O2", "generic"]
+    return ["generic"]
+
+
+def cpu_time_steps(backend, scen, start_positions, steps, threads, warm, feedback=None, flavour="generic"):
+    """`threads` independent replicas, each advanced `steps` BD steps by the single-threaded reference code
+    after `warm` untimed ones; returns (wall seconds, final positions of replica 0) (ctypes releases the
+    GIL, so the replicas run in parallel)."""
+    reps = []
+    for t in range(threads):
+        x = start_positions[t % len(start_positions)]
+        if flavour.startswith("driver-"):
+            reps.append(_DriverReplica(scen, x, feedback, flavour.split("-")[1]))
+        else:
+            reps.append(_GenericReplica(backend, scen, x, feedback))
+
+    def fan(k):
+        th = [threading.Thread(target=r.run, args=(k,)) for r in reps]
         t0 = time.perf_counter()
         for x in th:
             x.start()
@@ -145,11 +266,12 @@ def cpu_time_steps(backend, scen, start_positions, steps, threads, warm):
             x.join()
         return time.perf_counter() - t0
 
-    fan(warm, 1)
-    dt = fan(steps, warm + 1)
-    for s in systems:
-        s.close()
-    return dt
+    fan(warm)
+    dt = fan(steps)
+    final = reps[0].positions()
+    for r in reps:
+        r.close()
+    return dt, final
 
 
 def run_reference(args):
@@ -157,14 +279,18 @@ def run_reference(args):
     if rank != 0:
         return
     backend, kind = cpu_backend()
-    scen = scenario(args, 1, 4)
     threads = os.cpu_count() or 1
+    scen = scenario(args, min(threads, 4), 4)
+    feedback = wall_feedback(args, scen)
     K, W = max(args.steps, 1), max(args.warmup, 0)
-    # size the per-step sample from a short probe so that the whole run stays within ~2 minutes
-    probe = cpu_time_steps(backend, scen, scen.positions, 3, threads, 1) / 3
+    # size the per-step sample from a short probe so that the whole run stays within a few minutes; the
+    # relaxation (the same number of steps the engine arm relaxes for) is done by the reference itself
+    flavour = cpu_flavours(args, kind)[0]
+    probe = cpu_time_steps(backend, scen, scen.positions, 3, threads, 1, feedback, flavour)[0] / 3
+    relax = min(args.relax, max(10, int(60.0 / max(probe, 1e-6))))
     inner = max(1, int(100.0 / max(probe, 1e-6) / (K + W)))
     inner = min(inner, 50)
-    wall = cpu_time_steps(backend, scen, scen.positions, K * inner, threads, W * inner)
+    wall, _ = cpu_time_steps(backend, scen, scen.positions, K * inner, threads, relax + W * inner, feedback, flavour)
     units = threads * scen.n * inner * K
     value = units / wall
     line = {
@@ -172,9 +298,11 @@ def run_reference(args):
         "n_gpus": args.gpus, "steps": K, "warmup": W, "ms_per_step": 1e3 * wall / K,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": workload_name(args, scen),
-                   "sample": f"{threads} replicas (one per host thread), {inner} BD steps of each per bench step"},
-        "cpu_baseline": {"value": value, "unit": "bead-steps/s", "cores": threads, "kind": kind,
-                         "sample": f"{threads} independent replicas x {inner * K} BD steps, micromd single-threaded per replica"},
+                   "sample": f"{threads} replicas (one per host thread), {inner} BD steps of each per bench step, "
+                             f"after {relax} relaxation steps by the reference itself"},
+        "cpu_baseline": {"value": value, "unit": "bead-steps/s", "cores": threads, "kind": kind, "build": flavour,
+                         "sample": f"{threads} independent replicas x {inner * K} BD steps, micromd single-threaded per replica"
+                                   + (", per-step wall feedback through the C entry points" if feedback else "")},
         "e2e": {"value": value, "unit": "bead-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -183,11 +311,46 @@ def run_reference(args):
 
 # ---- B200 arm ------------------------------------------------------------------------------------
 
+def parity_check(eng, sysm, scen, R, ids):
+    """Replica 0 and replica R-1 of the state about to be timed against the reference's own code (the
+    unmodified micromd where oracle/_ref was built, else the CPU restatement): per-bead forces, and the
+    Verlet pair set of a fresh list build on the same positions.  The checker is used as a checker only."""
+    import bdb200 as bd
+
+    backend, kind = cpu_backend()
+    out = {"checker": kind, "replicas": sorted({0, R - 1}), "force_rel_err": 0.0, "pairs_equal": True}
+    for r in out["replicas"]:
+        x = sysm.get_positions(r)
+        ref = bd.System(backend, scen.n)
+        rids = scen.apply(ref, replicas=[0])
+        ref.set_positions(x)
+        for w_ref, w_eng in zip(rids["wall"], ids["wall"]):  # this replica's walls where the feedback has moved them
+            ref.update_wall_ff(w_ref, *sysm.get_wall_geometry(w_eng, r))
+        fr = ref.compute_forces()
+        fe = sysm.compute_forces(r)
+        scale = np.linalg.norm(fr, axis=1).max()
+        out["force_rel_err"] = max(out["force_rel_err"], float(np.linalg.norm(fe - fr, axis=1).max() / scale))
+        fresh = bd.System(eng, scen.n, 1, device=sysm.device)
+        scen.apply(fresh, replicas=[0])
+        fresh.set_positions(x)
+        a, b = fresh.get_neighbor_list(), ref.get_neighbor_list()
+        key = lambda p: np.sort((np.minimum(p[:, 0], p[:, 1]).astype(np.uint64) << np.uint64(32))
+                                | np.maximum(p[:, 0], p[:, 1]).astype(np.uint64))
+        out["pairs_equal"] = bool(out["pairs_equal"] and np.array_equal(key(a), key(b)))
+        out["listed_pairs"] = int(len(b))
+        fresh.close()
+        ref.close()
+    if not (out["force_rel_err"] <= 1e-6 and out["pairs_equal"]):
+        raise SystemExit(f"bench.py: parity check failed: {out}")
+    return out
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
 
     import bdb200 as bd
+    import ensemble as en
 
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -204,12 +367,18 @@ def run_b200(args):
         torch.cuda.synchronize()
 
     eng = bd.load_engine()
-    R = args.replicas
+    R = replicas_of(args)
     distinct = min(R, 4)
     scen = scenario(args, distinct, 4 + rank)  # every rank simulates its own replicas (weak scaling)
     n, ntot = scen.n, scen.n * R
+    feedback = wall_feedback(args, scen)
     sysm = bd.System(eng, n, R, device=local)
-    scen.apply(sysm, replicas=[])
+    ids = scen.apply(sysm, replicas=[])
+    sysm.device = local
+    if feedback:
+        sysm.set_wall_relaxation(ids["wall"], feedback["spring"], feedback["mobility"])
+    if args.verlet_factor:
+        sysm.set_option("verlet_factor", args.verlet_factor)
     stream = torch.cuda.Stream()
     sysm.set_stream(stream.cuda_stream)
     host = torch.empty((R, n, 3), dtype=torch.float64).pin_memory()
@@ -226,6 +395,9 @@ def run_b200(args):
     advance(args.relax)
     advance(max(args.warmup, 3))
     sysm.sync()
+    parity = None
+    if rank == 0 and not args.no_parity:
+        parity = parity_check(eng, sysm, scen, R, ids)
     c0 = sysm.get_counters()
     l0 = sysm.get_launch_count()
     sampler = ClockSampler(local)
@@ -243,30 +415,45 @@ def run_b200(args):
     c1 = sysm.get_counters()
     inter = c1.pair_interactions - c0.pair_interactions
     rebuilds = c1.list_rebuilds - c0.list_rebuilds
+    semi_now = sysm.get_wall_geometry(ids["wall"][0], 0)[1].tolist() if feedback else None
 
     # the dominant kernel alone, CUDA events around every launch
     sysm.set_option("time_kernel", 1)
     advance(min(args.steps, 50))
     kernel_ms = sysm.get_option("kernel_ms_avg")
     sysm.set_option("time_kernel", 0)
+    sysm.get_all_positions(host.data_ptr())
+    sysm.close()
 
-    # end to end through the C ABI with pinned host buffers, every step
+    # end to end through the C ABI with pinned HOST buffers every step: the replicas as `chunks` engines on
+    # their own streams, upload -> bd_step(1) -> download per chunk, one synchronisation per step
     e2e = None
     if not args.no_e2e:
         ke = max(3, min(args.steps, 20))
-        sysm.get_all_positions(host.data_ptr())
+
+        def setup(s, fids):
+            if feedback:
+                s.set_wall_relaxation(fids["wall"], feedback["spring"], feedback["mobility"])
+            if args.verlet_factor:
+                s.set_option("verlet_factor", args.verlet_factor)
+
+        pipe = en.HostPipeline(eng, scen, R, chunks=args.chunks, rank=rank, world=world, device=local, seed=1234 + rank,
+                               setup=setup)
+        pipe.steps_done = step_no[0] - 1
+        pipe.upload(host)
+        pipe.step_resident(3, dt, kT)  # builds the lists; the timed steps below start from host memory
+        for s in pipe.systems:
+            s.sync()
+        le0 = pipe.launch_count()
         barrier()
-        with torch.cuda.stream(stream):
-            f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            f0.record(stream)
-            for _ in range(ke):
-                sysm.set_all_positions(host.data_ptr())
-                advance(1)
-                sysm.get_all_positions(host.data_ptr())
-            f1.record(stream)
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        for _ in range(ke):
+            pipe.step_through_host(host, host, dt, kT)
+        f1.record()
         barrier()
-        e2e_ms = f0.elapsed_time(f1)
-        e2e = (ke, e2e_ms)
+        e2e = (ke, f0.elapsed_time(f1), (pipe.launch_count() - le0) / ke, len(pipe.systems))
+        pipe.close()
 
     t = torch.tensor([ms, e2e[1] if e2e else 0.0, float(inter), kernel_ms], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -285,10 +472,11 @@ def run_b200(args):
             peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)"
         else:
             peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-        traffic = None
+        traffic, traffic_src = None, None
         tp = os.path.join(ROOT, "profiles", "roofline_traffic.json")
-        if os.path.exists(tp):
-            traffic = json.load(open(tp)).get("k_step_fused_dram_bytes_per_launch")
+        if os.path.exists(tp) and args.workload == "genome100kb" and R == 64:
+            tj = json.load(open(tp))
+            traffic, traffic_src = tj.get("k_step_fused_dram_bytes_per_launch"), tj.get("source")
         achieved = ALGO_BYTES_PER_BEAD_STEP * ntot / (kernel_ms * 1e-3) / 1e9 if kernel_ms > 0 else 0.0
         value = world * ntot * args.steps / (ms * 1e-3)
         line = {
@@ -298,6 +486,8 @@ def run_b200(args):
             "data": "synthetic",
             "config": {"workload": workload_name(args, scen), "beads_per_replica": n, "replicas_per_gpu": R,
                        "timestep": dt, "temperature": kT, "noise": "philox4x32-10",
+                       "wall_feedback": ("every step, per replica, on the device (bd_set_wall_relaxation)" if feedback
+                                         else "none"),
                        "l2": "working set %.2f GB per GPU > 126 MB L2 (no flush needed)" % (ntot * 32 * 3 / 1e9 + ntot * 4 * 8 / 1e9),
                        "relax_steps": args.relax, "list_rebuilds_in_timed_region": rebuilds,
                        "parallelism": f"replica shards, {world} GPU(s), no data-path collective"},
@@ -306,25 +496,41 @@ def run_b200(args):
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic, "kernel": "k_step_fused",
+                         "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                         "kernel": "k_step_fused",
                          "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": ALGO_BYTES_PER_BEAD_STEP * ntot,
                          "peak_source": peak_src},
         }
+        if parity:
+            line["parity_check"] = parity
+        if semi_now:
+            line["config"]["wall_semiaxes_replica0_after_timed_region"] = semi_now
         if e2e:
             line["e2e"] = {"value": world * ntot * e2e[0] / (e2e_ms_max * 1e-3), "unit": "bead-steps/s",
                            "h2d_bytes_per_step": ntot * 24, "d2h_bytes_per_step": ntot * 24,
-                           "steps": e2e[0], "ms_per_step": e2e_ms_max / e2e[0],
-                           "path": "bd_set_all_positions -> bd_step(1) -> bd_get_all_positions, pinned host buffers"}
+                           "steps": e2e[0], "ms_per_step": e2e_ms_max / e2e[0], "gpu_launches_per_step": e2e[2],
+                           "path": f"ensemble.HostPipeline: {e2e[3]} engines (replica chunks) on their own streams, per chunk "
+                                   "bd_set_all_positions -> bd_step(1) -> bd_get_all_positions_async from / to one pinned "
+                                   "host buffer, one synchronisation per step"}
         if world == 1 and not args.no_cpu_baseline:
             backend, kind = cpu_backend()
             start = host.numpy()[:1].copy()  # GPU-relaxed configuration: the same work per step
-            probe = cpu_time_steps(backend, scen, start, 3, 1, 1) / 3
-            s = max(5, int(args.cpu_seconds / max(probe, 1e-6)))
-            wall = cpu_time_steps(backend, scen, start, s, 1, 2)
-            line["cpu_baseline"] = {"value": n * s / wall, "unit": "bead-steps/s", "cores": 1, "kind": kind,
-                                    "sample": f"1 replica ({n} beads) x {s} BD steps from the GPU-relaxed state, single thread"}
+            builds = {}
+            for flavour in cpu_flavours(args, kind):
+                probe = cpu_time_steps(backend, scen, start, 3, 1, 1, feedback, flavour)[0] / 3
+                s = max(5, int(args.cpu_seconds / len(cpu_flavours(args, kind)) / max(probe, 1e-6)))
+                wall, _ = cpu_time_steps(backend, scen, start, s, 1, 2, feedback, flavour)
+                builds[flavour] = {"value": n * s / wall, "steps": s}
+            best = max(builds, key=lambda k: builds[k]["value"])
+            line["cpu_baseline"] = {
+                "value": builds[best]["value"], "unit": "bead-steps/s", "cores": 1, "kind": kind, "build": best,
+                "builds": {k: v["value"] for k, v in builds.items()},
+                "build_notes": "driver-O3 / driver-O2: micromd with the drivers' compile-time potentials and callback "
+                               "(oracle/ref_drivers.cc; g++ -O3 -march=x86-64-v3 / -O2); generic: micromd behind the C entry "
+                               "points (oracle/ref_harness.cc, -O2 -ffp-contract=off, the parity build)",
+                "sample": f"1 replica ({n} beads) x {builds[best]['steps']} BD steps from the GPU-relaxed state, single thread"
+                          + (", per-step wall feedback" if feedback else "")}
         print(json.dumps(line), flush=True)
-    sysm.close()
     if world > 1:
         dist.destroy_process_group()
 
@@ -354,6 +560,8 @@ def run_slab(args):
     dcut = max(ff["dcut"] for ff in scen.pair_ffs)
     sysm = bd.System(eng, scen.n, 1, device=local)
     scen.apply(sysm)
+    if args.verlet_factor:
+        sysm.set_option("verlet_factor", args.verlet_factor)
     dt, kT, seed = scen.timestep, scen.temperature, 77
     sampler = ClockSampler(local)
     K, W = args.steps, max(args.warmup, 3)

@@ -135,6 +135,9 @@ int bd_refine_spline_device(const double *d_coarse, const int64_t *coarse_ranges
  * returns after the data has arrived. */
 int bd_set_all_positions(bd_engine *h, const double *xyz);
 int bd_get_all_positions(bd_engine *h, double *xyz);
+/* the download only enqueued (pinned xyz): complete after bd_sync.  Engines that hold chunks of one replica
+ * ensemble on their own streams overlap upload, step and download of different chunks this way. */
+int bd_get_all_positions_async(bd_engine *h, double *xyz);
 
 /* ---- statistics of the production noise -----------------------------------------------------------
  * The engine's step kernel draws counter-based Philox4x32-10 + single-precision Box-Muller normals keyed by

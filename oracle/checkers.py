@@ -36,3 +36,64 @@ def load_reference() -> "bdb200.Backend":
 
 def have_reference() -> bool:
     return os.path.exists(REFERENCE_LIB)
+
+
+# ---- the 100kb interphase model set up as the reference driver sets it up (oracle/ref_drivers.cc) --------
+
+import ctypes as _C
+
+import numpy as _np
+
+DRIVER_LIBS = {"O2": os.path.join(ROOT, "oracle", "_ref", "libmicromd_drv_O2.so"),
+               "O3": os.path.join(ROOT, "oracle", "_ref", "libmicromd_drv_O3.so")}
+
+
+def have_driver_baseline(flavour="O2") -> bool:
+    return os.path.exists(DRIVER_LIBS[flavour])
+
+
+class DriverC4:
+    """One system of scenarios.genome_100kb on the unmodified micromd with compile-time potentials and the
+    driver's per-step wall feedback as the simulate_brownian_dynamics callback.  TIMING ONLY."""
+
+    def __init__(self, scen, positions, flavour="O2"):
+        import scenarios as sc
+
+        lib = _C.CDLL(DRIVER_LIBS[flavour])
+        lib.drv_c4_create.restype = _C.c_void_p
+        lib.drv_c4_create.argtypes = [_C.c_int64, _C.c_void_p, _C.c_void_p, _C.c_int64, _C.c_void_p, _C.c_int64,
+                                      _C.c_void_p, _C.c_void_p, _C.c_int64]
+        lib.drv_c4_run.argtypes = [_C.c_void_p, _C.c_int64, _C.c_double, _C.c_double, _C.c_uint64, _C.c_int32]
+        lib.drv_c4_get.argtypes = [_C.c_void_p, _C.c_void_p, _C.c_void_p]
+        lib.drv_c4_destroy.argtypes = [_C.c_void_p]
+        self.lib, self.scen = lib, scen
+        p = scen.params
+        ab = _np.ascontiguousarray(sc.C4_AB[scen.types], dtype=_np.float64)
+        chains = _np.ascontiguousarray(scen.chains, dtype=_np.int64)
+        nuc = _np.ascontiguousarray(scen.bond_ffs[2]["pairs"], dtype=_np.int64)
+        params = _np.array([p["a_core_diameter"], p["b_core_diameter"], p["a_core_repulsion"], p["b_core_repulsion"],
+                            p["a_core_bond_spring"], p["a_core_bond_length"], p["b_core_bond_spring"], p["b_core_bond_length"],
+                            p["a_core_2nd_bond_spring"], p["b_core_2nd_bond_spring"],
+                            p["nucleolus_bond_spring"], p["nucleolus_bond_length"],
+                            p["wall_packing_spring"], p["wall_a_factor"], p["wall_b_factor"],
+                            p["wall_mobility"], p["wall_semiaxes_spring"], *p["semiaxes"],
+                            p.get("bead_scale", 1.0), p.get("bond_scale", 1.0)], dtype=_np.float64)
+        x = _np.ascontiguousarray(positions, dtype=_np.float64)
+        self.h = lib.drv_c4_create(scen.n, ab.ctypes.data, chains.ctypes.data, len(chains), nuc.ctypes.data, len(nuc),
+                                   x.ctypes.data, params.ctypes.data, len(params))
+        if not self.h:
+            raise RuntimeError("drv_c4_create failed (parameter block mismatch)")
+
+    def run(self, steps, seed=1, feedback=True):
+        self.lib.drv_c4_run(self.h, int(steps), float(self.scen.temperature), float(self.scen.timestep), int(seed),
+                            1 if feedback else 0)
+
+    def get(self):
+        x, s = _np.zeros((self.scen.n, 3)), _np.zeros(3)
+        self.lib.drv_c4_get(self.h, x.ctypes.data, s.ctypes.data)
+        return x, s
+
+    def close(self):
+        if self.h:
+            self.lib.drv_c4_destroy(self.h)
+            self.h = None

@@ -57,3 +57,37 @@ def sort_pairs(p):
     p = np.stack([p.min(axis=1), p.max(axis=1)], axis=1)
     order = np.lexsort((p[:, 1], p[:, 0]))
     return p[order]
+
+
+# ---- the sizes BASELINE.json names (N = 4 000, 640 x 1 024 replicas, 62 600, 10^6) ----------
+
+NAMED = {
+    "ab_box_4000": lambda: sc.ab_box(200, 20),                       # C1
+    "ab_sphere_4000": lambda: sc.ab_sphere(200, 20),                 # C2
+    "genome_10mb_640": lambda: sc.genome_10mb(640, bend_energy=0.7),  # C3 (one of the 1 024 replicas)
+    "genome_100kb_62600": lambda: sc.genome_100kb(62000, 300),       # C4
+    "chromatin_1kb_1M": lambda: sc.chromatin_1kb(100, 10000),        # C5 at 10^6 beads
+}
+NAMED_STEPS = 10
+NAMED_SEED = 23
+NAMED_SAMPLE = 1000
+
+
+def sample_beads(n):
+    """the beads whose forces / positions the full-size fixtures store (fixed, spread over the chains)"""
+    return np.unique(np.linspace(0, n - 1, min(n, NAMED_SAMPLE)).astype(np.int64))
+
+
+def digest(a):
+    """sha256 of an array's bytes: bit-exact identity of a full-size result"""
+    import hashlib
+
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def pair_digest(pairs):
+    """order-independent identity of a pair set: count, sum and xor of the 64-bit keys i << 32 | j"""
+    p = sort_pairs(pairs).astype(np.uint64)
+    key = (p[:, 0] << np.uint64(32)) | p[:, 1]
+    return np.array([len(key), int(key.sum(dtype=np.uint64)), int(np.bitwise_xor.reduce(key)) if len(key) else 0],
+                    dtype=np.uint64)

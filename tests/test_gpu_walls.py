@@ -47,7 +47,7 @@ def setup(engine, oracle):
         singles.append(so)
     semi0 = np.array(scen.params["semiaxes"])
     # every replica starts with its own ellipsoid (squeezed differently, so that beads press on the walls)
-    semis = np.stack([semi0 * (0.93 + 0.02 * r) * np.array([1.0, 1.0 - 0.01 * r, 1.0 + 0.01 * r]) for r in range(R)])
+    semis = np.stack([semi0 * (0.86 + 0.02 * r) * np.array([1.0, 1.0 - 0.01 * r, 1.0 + 0.01 * r]) for r in range(R)])
     for r in range(R):
         for w in ids["wall"]:
             ens.update_wall_ff(w, (0, 0, 0), semis[r], replica=r)

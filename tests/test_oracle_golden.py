@@ -50,3 +50,26 @@ def test_scenario_golden(oracle, name):
     s.step(GOLDEN_STEPS, scen.timestep, scen.temperature, seed=GOLDEN_SEED)
     assert np.array_equal(s.get_positions(), g["positions_after"])
     assert s.compute_energy() == g["energy_after"]
+
+
+# ---- the sizes BASELINE.json names, against full-size fixtures of the reference --------------------------
+
+from cases import NAMED, NAMED_SEED, NAMED_STEPS, digest, pair_digest, sample_beads  # noqa: E402
+
+
+@pytest.mark.parametrize("name", sorted(NAMED))
+def test_named_size_golden(oracle, name):
+    """4 000, 640, 62 600 and 10^6 beads: the oracle reproduces the reference's full arrays bit for bit
+    (sha256), its Verlet pair set and a 10-step trajectory (tests/golden/make_named_golden.py)."""
+    g = np.load(os.path.join(GOLD, "named_sizes.npz"))
+    scen = NAMED[name]()
+    assert scen.n == int(g[f"{name}.n"])
+    assert digest(scen.positions[0]) == str(g[f"{name}.positions_sha"]), "scenario generator drifted from the fixture"
+    s, _ = build(oracle, scen)
+    f = s.compute_forces()
+    assert digest(f) == str(g[f"{name}.forces_sha"])
+    assert np.array_equal(f[sample_beads(scen.n)], g[f"{name}.forces_sample"])
+    assert s.compute_energy() == float(g[f"{name}.energy"])
+    assert np.array_equal(pair_digest(s.get_neighbor_list()), g[f"{name}.pairs"])
+    s.step(NAMED_STEPS, scen.timestep, scen.temperature, seed=NAMED_SEED)
+    assert digest(s.get_positions()) == str(g[f"{name}.after_sha"])
