@@ -126,6 +126,8 @@ struct DControl {
     uint32_t doing_rebuild;  // latched copy for the kernels of one rebuild chain
     uint32_t overflow;       // beads whose ELL row overflowed (sticky)
     uint32_t max_row;        // longest ELL row at the last build
+    uint32_t stage_overflow; // tiles whose neighbourhood did not fit the staging tables (sticky; bd_nlist.cuh)
+    uint32_t max_stage;      // largest staged neighbourhood (beads) of a tile at the last build
     unsigned long long rebuilds;
     unsigned long long max_disp2_bits;  // bits of max_i |x_i - x_i(build)|^2, kept by the step kernel
     unsigned long long listed_entries;  // sum of row lengths at the last build (2 x listed pairs)
@@ -289,6 +291,107 @@ __device__ inline double pot_energy(const DTerm *__restrict__ row, int nterms, d
     return e;
 }
 
+// ---- tile staging ---------------------------------------------------------------------------------
+//
+// The step kernel advances tiles of 128 slot-consecutive beads.  After the Morton sort the neighbourhood
+// of a tile -- every cell any of its beads lists from -- is a few dozen contiguous slot RUNS.  At a list
+// build the runs of every tile are written down and the Verlet rows store 16-bit positions inside the
+// concatenated runs; at every step a block copies the 16-byte shadows of its runs into shared memory with
+// bulk asynchronous copies (no LSU traffic) and the pair walk gathers from there.  A gather of 32
+// scattered shadows costs the L1 one wavefront per touched line when it goes to global memory, and a
+// quarter of that from shared memory; that gather was what bound the round-1 kernel (75 % of peak
+// L1 wavefronts).
+constexpr uint32_t STAGE_RUNS = 254;          // runs per tile (adjacent cells merge)
+constexpr uint32_t STAGE_CELLS = 512;         // distinct cells in the neighbourhood of a tile
+constexpr uint32_t STAGE_HASH = 1024;         // open-addressing table that deduplicates them
+constexpr uint32_t STAGE_MAX_BEADS = 65000;   // 16-bit row entries
+
+struct TileRuns {
+    uint32_t nruns, total;                    // total = staged beads; row entries are in [0, total], total = padding
+    uint32_t start[STAGE_RUNS];               // first slot of run r
+    uint32_t off[STAGE_RUNS];                 // its position in the staged array
+};
+static_assert(sizeof(TileRuns) == 2040, "TileRuns layout");
+
+/* staged position -> slot (the rare consumers of the rows that do not stage: energy, list export) */
+__device__ inline uint32_t staged_to_slot(const TileRuns &t, uint32_t local)
+{
+    uint32_t lo = 0, hi = t.nruns;  // last run with off <= local
+    while (hi - lo > 1) {
+        uint32_t const mid = (lo + hi) >> 1;
+        if (t.off[mid] <= local) lo = mid; else hi = mid;
+    }
+    return t.start[lo] + (local - t.off[lo]);
+}
+
+/* entry k of the row at thread position p, as a slot, in either row format (for the consumers that do not
+ * stage: list export, energy).  tile = the tile the position belongs to. */
+__device__ inline uint32_t row_entry_slot(const uint4 *nbr4, const TileRuns *tile_runs, uint32_t staged, size_t pstride,
+                                          uint32_t p, uint32_t tile, uint32_t k)
+{
+    if (!staged) {
+        uint4 const grp = nbr4[(size_t) (k / ROW_PAD) * pstride + p];
+        return k % ROW_PAD == 0 ? grp.x : k % ROW_PAD == 1 ? grp.y : k % ROW_PAD == 2 ? grp.z : grp.w;
+    }
+    uint2 const grp = reinterpret_cast<const uint2 *>(nbr4)[(size_t) (k / ROW_PAD) * pstride + p];
+    uint32_t const word = k % ROW_PAD < 2 ? grp.x : grp.y;
+    return staged_to_slot(tile_runs[tile], (k & 1u) ? word >> 16 : word & 0xffffu);
+}
+
+// ---- bulk asynchronous copies global -> shared (sm_90+: cp.async.bulk, completion on an mbarrier) ------
+
+__device__ __forceinline__ uint32_t shared_u32(const void *p) { return (uint32_t) __cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t arrivals)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(shared_u32(bar)), "r"(arrivals) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+
+__device__ __forceinline__ void mbar_expect(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(shared_u32(bar)), "r"(bytes) : "memory");
+}
+
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" :: "r"(shared_u32(bar)), "r"(parity) : "memory");
+}
+
+/* bytes is a positive multiple of 16; both addresses are 16-byte aligned */
+__device__ __forceinline__ void bulk_g2s(void *dst_shared, const void *src_global, uint32_t bytes, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(shared_u32(dst_shared)), "l"(src_global), "r"(bytes), "r"(shared_u32(bar)) : "memory");
+}
+
+/* Copy the shadows of a tile's runs into `stage` (all threads of the block call this; `runs` is the
+ * shared-memory copy of the tile's table).  One thread announces the byte count, the runs are issued
+ * round-robin by the threads, everybody waits for the data.  stage[total] gets the padding entry. */
+__device__ __forceinline__ void stage_runs(float4 *stage, const float4 *shadow, const TileRuns &runs, uint64_t *bar,
+                                           uint32_t parity, uint32_t pad_slot)
+{
+    uint32_t const n = runs.nruns, total = runs.total;
+    if (threadIdx.x == 0) {
+        mbar_expect(bar, total * 16u);
+        float const fnan = __uint_as_float(0x7fc00000u);
+        stage[total] = make_float4(fnan, fnan, fnan, __uint_as_float(pad_slot));
+    }
+    for (uint32_t r = threadIdx.x; r < n; r += blockDim.x) {
+        uint32_t const end = r + 1 < n ? runs.off[r + 1] : total;
+        bulk_g2s(stage + runs.off[r], shadow + runs.start[r], (end - runs.off[r]) * 16u, bar);
+    }
+    mbar_wait(bar, parity);
+}
+
 // ---- cell keys ----------------------------------------------------------------------------------
 
 /* Morton interleave of cell coordinates with per-axis bit counts */
@@ -332,8 +435,10 @@ __device__ inline void cell_coords(const DParams &P, const DGrid &G, double x, d
 // shadow.  Open box: float offsets from the grid origin.  Periodic box: 32-bit fixed-point
 // fractions of the period, whose wrapping difference IS the minimum image.
 
+/* .w carries the bead's own slot (as bits): a kernel that reads a shadow from a staged shared-memory copy
+ * (bd_step.cuh: tile staging) learns from it where the bead's fp64 record lives */
 template <int BOX>
-__device__ __forceinline__ float4 make_shadow(const DParams &P, const DGrid &G, double x, double y, double z)
+__device__ __forceinline__ float4 make_shadow(const DParams &P, const DGrid &G, double x, double y, double z, uint32_t slot)
 {
     float4 q;
     if (BOX == BD_BOX_PERIODIC) {
@@ -353,7 +458,7 @@ __device__ __forceinline__ float4 make_shadow(const DParams &P, const DGrid &G, 
         q.y = (float) (y - G.origin[1]);
         q.z = (float) (z - G.origin[2]);
     }
-    q.w = 0.0f;
+    q.w = __uint_as_float(slot);
     return q;
 }
 

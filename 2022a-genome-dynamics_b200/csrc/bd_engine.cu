@@ -23,6 +23,8 @@
 using namespace bd;
 
 static_assert(BAL_TILE == STEP_BLOCK, "k_balance ranks the beads of one step-kernel block");
+static_assert(ROWS_BLOCK == STEP_BLOCK, "k_rows_staged writes the run table of one step-kernel tile");
+constexpr uint32_t STAGE_CAP_CEILING = 2048;  // shadows a step-kernel block stages at most (32 KB)
 
 // ---- errors --------------------------------------------------------------------------------------
 
@@ -91,6 +93,10 @@ struct bd_engine {
     int cur = 0;
     DevBuf<uint32_t> slot_of, cellkey, rank, stage, cell_count, cell_start, block_sum, nnbr, plen;
     DevBuf<uint4> nbr4;       // Verlet rows by thread position, ROW_PAD indices per group
+    DevBuf<TileRuns> tile_runs;  // staged neighbourhood of every tile (bd_device.cuh: tile staging)
+    bool staged = false;      // rows hold 16-bit staged positions (option "staged"); false = rows of slots, global gathers
+    bool stage_auto = true;   // the block's staging capacity follows the largest tile (bd_set_option stage_capacity fixes it)
+    uint32_t stage_cap = 512; // shadows a block of the step kernel stages
     DevBuf<uint2> bondrow;    // bonded partners by thread position, resolved to slots at every rebuild
     DevBuf<BondRow> d_bond_rows;
     uint32_t npad = 0, pstride = 0, bond_deg = 0;
@@ -168,6 +174,8 @@ struct bd_engine {
 };
 
 static int sync_and_check(bd_engine *h);
+static void opt_in_shared_memory();
+static size_t table_bytes(uint32_t ntypes2, uint32_t nbond_rows);
 
 // ---- small helpers -------------------------------------------------------------------------------
 
@@ -477,6 +485,7 @@ extern "C" int bd_create(int64_t n_beads, int32_t n_replicas, int32_t device, bd
     if (device < 0 || device >= ndev) return fail("bd_create: bad device ordinal");
     CK(cudaSetDevice(device));
 
+    opt_in_shared_memory();
     bd_engine *h = new bd_engine();
     h->device = device;
     h->n = (uint32_t) n_beads;
@@ -533,7 +542,8 @@ extern "C" int bd_create(int64_t n_beads, int32_t n_replicas, int32_t device, bd
         && h->d_type.alloc(h->n) == cudaSuccess && h->d_pair_mask.alloc(h->n) == cudaSuccess
         && h->d_point_mask.alloc(h->n) == cudaSuccess && h->order.alloc(nt) == cudaSuccess && h->plen.alloc(h->pstride) == cudaSuccess
         && h->d_bond_rows.alloc(BD_MAX_TYPES * BD_MAX_TYPES) == cudaSuccess
-        && h->nbr4.alloc((size_t) (h->cap / ROW_PAD) * h->pstride) == cudaSuccess;
+        && h->nbr4.alloc((size_t) (h->cap / ROW_PAD) * h->pstride) == cudaSuccess
+        && h->tile_runs.alloc((size_t) h->chunks * h->replicas) == cudaSuccess;
     if (!ok) {
         bd_destroy(h);
         return fail(std::string("bd_create: device allocation failed: ") + cudaGetErrorString(cudaGetLastError()));
@@ -582,6 +592,7 @@ extern "C" int bd_destroy(bd_engine *h)
     h->d_pair_rows.release();
     h->bond_adj.release();
     h->nbr4.release();
+    h->tile_runs.release();
     h->bondrow.release();
     h->d_bond_rows.release();
     if (h->contact_search) bd_destroy(h->contact_search);
@@ -1109,6 +1120,8 @@ static NlistArrays nlist_arrays(bd_engine *h)
     for (int f = 0; f < BD_MAX_BOND_FF; f++) A.bond_slot[f] = h->bond_slot[f];
     A.ntypes = (uint32_t) h->hp.ntypes;
     A.bond_deg = h->bond_deg;
+    A.tile_runs = h->tile_runs.p;
+    A.staged = h->staged;
     A.npad = h->npad;
     A.pstride = h->pstride;
     A.ctl = h->ctl.p;
@@ -1132,6 +1145,9 @@ static StepArrays step_arrays(bd_engine *h)
     A.bpos = h->bpos.p;
     A.slot_of = h->slot_of.p;
     A.nbr4 = h->nbr4.p;
+    A.tile_runs = h->tile_runs.p;
+    A.staged = h->staged;
+    A.stage_cap = h->stage_cap;
     A.plen = h->plen.p;
     A.bondrow = h->bondrow.p;
     A.bond_deg = h->bond_deg;
@@ -1164,6 +1180,7 @@ static StepArrays step_arrays(bd_engine *h)
     A.dt_prev = h->dt_prev.p;
     A.pair_rows = h->d_pair_rows.p;
     A.ntypes2 = (uint32_t) (h->hp.ntypes * h->hp.ntypes);
+    A.stage_off = (uint32_t) table_bytes(A.ntypes2, (uint32_t) h->nbond_rows);
     A.fast_ff = h->fast_ff;
     A.k2_uniform = h->prog != PROG_GENERIC && h->k2_uniform;
     A.k2a = h->k2a;
@@ -1175,10 +1192,49 @@ static StepArrays step_arrays(bd_engine *h)
     return A;
 }
 
+/* dynamic shared memory of the step kernels: compiled pair rows, compiled bond rows, then the staged shadows */
+static size_t table_bytes(uint32_t ntypes2, uint32_t nbond_rows)
+{
+    return ((size_t) ntypes2 * sizeof(PairRow) + (size_t) nbond_rows * sizeof(BondRow) + 15) & ~(size_t) 15;
+}
+
+static size_t step_smem_bytes(const StepArrays &A)
+{
+    return A.stage_off + (A.staged ? STAGE_TABLE_BYTES + ((size_t) A.stage_cap + 1) * sizeof(float4) : 0);
+}
+
+constexpr int STEP_SMEM_OPT_IN = 160 * 1024;  // dynamic shared memory the step kernels may ask for
+
+template <typename K>
+static void allow_big_smem(K kernel)
+{
+    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, STEP_SMEM_OPT_IN);
+}
+
+static void opt_in_shared_memory()
+{
+    static bool done = false;  // per process; attributes are per device function
+    if (done) return;
+    done = true;
+    allow_big_smem(k_step_fused<BD_BOX_OPEN, PROG_GENERIC>);
+    allow_big_smem(k_step_fused<BD_BOX_OPEN, PROG_SC23_SC83>);
+    allow_big_smem(k_step_fused<BD_BOX_OPEN, PROG_SC23>);
+    allow_big_smem(k_step_fused<BD_BOX_PERIODIC, PROG_GENERIC>);
+    allow_big_smem(k_step_fused<BD_BOX_PERIODIC, PROG_SC23_SC83>);
+    allow_big_smem(k_step_fused<BD_BOX_PERIODIC, PROG_SC23>);
+    allow_big_smem(k_force<BD_BOX_OPEN, PROG_GENERIC>);
+    allow_big_smem(k_force<BD_BOX_OPEN, PROG_SC23_SC83>);
+    allow_big_smem(k_force<BD_BOX_OPEN, PROG_SC23>);
+    allow_big_smem(k_force<BD_BOX_PERIODIC, PROG_GENERIC>);
+    allow_big_smem(k_force<BD_BOX_PERIODIC, PROG_SC23_SC83>);
+    allow_big_smem(k_force<BD_BOX_PERIODIC, PROG_SC23>);
+    allow_big_smem(k_rows_staged);
+}
+
 template <int BOX>
 static void launch_step_box(int prog, dim3 grid, cudaStream_t st, const StepArrays &A, const StepScalars &S)
 {
-    size_t const rows_bytes = (size_t) A.ntypes2 * sizeof(PairRow) + (size_t) A.nbond_rows * sizeof(BondRow);
+    size_t const rows_bytes = step_smem_bytes(A);
     switch (prog) {
     case PROG_SC23_SC83: k_step_fused<BOX, PROG_SC23_SC83><<<grid, STEP_BLOCK, rows_bytes, st>>>(A, S); break;
     case PROG_SC23: k_step_fused<BOX, PROG_SC23><<<grid, STEP_BLOCK, rows_bytes, st>>>(A, S); break;
@@ -1190,7 +1246,7 @@ template <int BOX>
 static void launch_force_box(int prog, dim3 grid, cudaStream_t st, const StepArrays &A, const StepScalars &S,
                              Select sel)
 {
-    size_t const rows_bytes = (size_t) A.ntypes2 * sizeof(PairRow) + (size_t) A.nbond_rows * sizeof(BondRow);
+    size_t const rows_bytes = step_smem_bytes(A);
     switch (prog) {
     case PROG_SC23_SC83: k_force<BOX, PROG_SC23_SC83><<<grid, STEP_BLOCK, rows_bytes, st>>>(A, S, sel); break;
     case PROG_SC23: k_force<BOX, PROG_SC23><<<grid, STEP_BLOCK, rows_bytes, st>>>(A, S, sel); break;
@@ -1244,7 +1300,12 @@ static int enqueue_rebuild_chain(bd_engine *h)
     k_scan_down<<<tile_blocks, NL_BLOCK, 0, st>>>(A);
     k_group<<<bead_blocks, NL_BLOCK, 0, st>>>(A);
     k_place<<<bead_blocks, NL_BLOCK, 0, st>>>(A);
-    k_rows<<<row_blocks, ROWS_BLOCK, 0, st>>>(A);
+    if (h->staged) {
+        unsigned const tiles = h->chunks * h->replicas;
+        k_rows_staged<<<std::min(tiles, 148u * 12u), ROWS_BLOCK, sizeof(RowsStagedShared), st>>>(A);
+    } else {
+        k_rows<<<row_blocks, ROWS_BLOCK, 0, st>>>(A);
+    }
     k_balance<<<std::min(h->chunks * h->replicas, 148u * 16u), BAL_TILE, 0, st>>>(A);
     h->launches += 11;
     if (h->bond_rows_stale) {
@@ -1270,6 +1331,12 @@ static int sync_and_check(bd_engine *h)
                       "bd: %u neighbour rows exceeded list_capacity=%u; raise it with bd_set_option", overflow, h->cap);
         return fail(msg);
     }
+    if (h->staged) {
+        uint32_t spilled = 0;
+        CK(cudaMemcpy(&spilled, &h->ctl.p->stage_overflow, sizeof spilled, cudaMemcpyDeviceToHost));
+        if (spilled && h->list_verified)
+            return fail("bd: a tile's neighbourhood outgrew the staging tables during a run; set option staged=0");
+    }
     return 0;
 }
 
@@ -1282,6 +1349,20 @@ static int prepare_list(bd_engine *h)
         CK(cudaStreamSynchronize(h->stream));
         DControl c;
         CK(cudaMemcpy(&c, h->ctl.p, sizeof c, cudaMemcpyDeviceToHost));
+        if (h->staged && c.stage_overflow) {
+            // some tile's neighbourhood does not fit the staging tables (a very sparse or badly sorted system):
+            // this engine keeps rows of slots and gathers from global memory
+            h->staged = false;
+            CK(cudaMemset(&h->ctl.p->stage_overflow, 0, sizeof(uint32_t)));
+            if (request_rebuild(h)) return 1;
+            continue;
+        }
+        if (h->staged && h->stage_auto) {
+            // room for the largest tile plus what it may gain before the next host visit; tiles beyond the
+            // ceiling keep working through the run table (WALK_SPILLED)
+            uint32_t const want_stage = std::min<uint32_t>(STAGE_CAP_CEILING, ((c.max_stage + c.max_stage / 8 + 63u) & ~63u));
+            h->stage_cap = std::max(h->stage_cap, want_stage);
+        }
         uint32_t const limit = std::max<uint32_t>(h->n, 16u);
         uint32_t want = h->cap;
         if (c.overflow) {
@@ -1605,6 +1686,18 @@ extern "C" int bd_set_option(bd_engine *h, const char *name, double value)
         h->params_dirty = true;
         return 0;
     }
+    if (key == "staged") {
+        h->staged = value != 0;
+        CK(cudaStreamSynchronize(h->stream));
+        CK(cudaMemset(&h->ctl.p->stage_overflow, 0, sizeof(uint32_t)));
+        return request_rebuild(h);
+    }
+    if (key == "stage_capacity") {  // 0 = follow the largest tile
+        if (!(value >= 0 && value <= STAGE_CAP_CEILING)) return fail("bd_set_option: stage_capacity out of range");
+        h->stage_auto = value == 0;
+        h->stage_cap = value == 0 ? 512u : (uint32_t) value;
+        return 0;
+    }
     if (key == "time_kernel") {
         h->time_kernel = value != 0;
         return 0;
@@ -1635,6 +1728,14 @@ extern "C" int bd_get_option(bd_engine *h, const char *name, double *value)
     else if (key == "replica_id_base") *value = h->replica_base;
     else if (key == "replica_id_stride") *value = h->replica_stride;
     else if (key == "specialize") *value = h->specialize;
+    else if (key == "staged") *value = h->staged;
+    else if (key == "stage_capacity") *value = h->stage_cap;
+    else if (key == "max_stage") {
+        CK(cudaStreamSynchronize(h->stream));
+        uint32_t v = 0;
+        CK(cudaMemcpy(&v, &h->ctl.p->max_stage, sizeof v, cudaMemcpyDeviceToHost));
+        *value = v;
+    }
     else if (key == "pair_program") {
         if (upload_params(h)) return 1;
         *value = h->prog;

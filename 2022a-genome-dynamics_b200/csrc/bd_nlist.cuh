@@ -50,6 +50,8 @@ struct NlistArrays {
     uint8_t bond_slot[BD_MAX_BOND_FF];  // bond forcefield -> block of the compiled bond table (bd_step.cuh: BondRow)
     uint32_t ntypes;
     uint32_t bond_deg;       // largest number of bonds on one bead
+    TileRuns *tile_runs;     // [replicas * chunks] staged neighbourhood of every tile (bd_device.cuh), or null
+    uint32_t staged;         // rows hold 16-bit staged positions (uint2 groups) instead of slots (uint4 groups)
     uint32_t npad, pstride;
     DControl *ctl;
     const DParams *params;
@@ -80,6 +82,7 @@ __global__ void k_rebuild_begin(DControl *ctl, const DParams *params)
         ctl->rebuilds += 1;
         ctl->listed_entries = 0;
         ctl->max_row = 0;
+        ctl->max_stage = 0;
         ctl->max_disp2_bits = 0;
         for (int d = 0; d < 3; d++) {
             ctl->bbox_lo[d] = ~0ull;
@@ -325,8 +328,8 @@ __global__ void __launch_bounds__(NL_BLOCK) k_place(NlistArrays A)
         uint32_t const slot = b + rnk;
         A.bpos[slot] = rec;
         // nobody reads the shadow buffer during a rebuild: it can be rewritten in the new order here
-        A.shadow[slot] = P.box_kind == BD_BOX_PERIODIC ? make_shadow<BD_BOX_PERIODIC>(P, G, rec.x, rec.y, rec.z)
-                                                       : make_shadow<BD_BOX_OPEN>(P, G, rec.x, rec.y, rec.z);
+        A.shadow[slot] = P.box_kind == BD_BOX_PERIODIC ? make_shadow<BD_BOX_PERIODIC>(P, G, rec.x, rec.y, rec.z, slot)
+                                                       : make_shadow<BD_BOX_OPEN>(P, G, rec.x, rec.y, rec.z, slot);
         A.slot_of[(old / A.n) * A.n + mine] = slot;
     }
 }
@@ -532,6 +535,333 @@ __global__ void __launch_bounds__(ROWS_BLOCK) k_rows(NlistArrays A)
     }
 }
 
+
+// ---- staged rows ------------------------------------------------------------------------------------
+
+constexpr uint32_t STAGE_GAP = 8;           // slots between two cells that one run bridges
+constexpr uint32_t ROWS_STAGE_CAP = 2048;   // shadows k_rows_staged itself can hold (32 KB); larger tiles read global
+
+struct RowsStagedShared {
+    alignas(16) float4 stage[ROWS_STAGE_CAP + 1];
+    alignas(16) DParams P;
+    alignas(16) DGrid G;
+    alignas(16) TileRuns runs;
+    uint32_t hkey[STAGE_HASH];               // cell key, 0xffffffff = empty
+    uint32_t hval[STAGE_HASH];               // staged offset of the cell | its bead count << 16
+    uint16_t uniq[STAGE_CELLS];              // hash slots of the distinct cells, in arrival order
+    uint16_t sorted[STAGE_CELLS];            // ... in ascending key order
+    uint32_t cbeg[STAGE_CELLS], cend[STAGE_CELLS];  // slot range of the sorted cells
+    uint16_t cells[27][ROWS_BLOCK];          // [k][thread] hash slots of the thread's non-empty surrounding cells
+    uint16_t hits[ROWS_QUEUE][ROWS_BLOCK];   // [entry][thread] listed staged positions not yet written out
+    uint8_t bitpos[3][32];
+    uint32_t nuniq, bad;
+    alignas(8) uint64_t bar;
+};
+
+/* ELL rows of 16-bit staged positions + the run table of every tile (bd_device.cuh: tile staging).
+ * One block per tile of ROWS_BLOCK slot-consecutive beads of one replica:
+ *   A. every thread looks up the (at most 27) cells around its bead and the block collects the distinct
+ *      non-empty ones in a shared hash table;
+ *   B. the distinct cells are sorted by key -- which is slot order -- their slot ranges concatenated into the
+ *      staged array, adjacent ranges merged into runs, and the run table written out for the step kernel;
+ *   C. the shadows of the runs are copied into shared memory (bulk asynchronous copies);
+ *   D. every thread walks the candidates of its cells in the staged copy and lists those within the list
+ *      radius, as positions in the staged array.
+ * The listed SET is what k_rows lists: the same candidates, the same single-precision test. */
+__global__ void __launch_bounds__(ROWS_BLOCK) k_rows_staged(NlistArrays A)
+{
+    if (!A.ctl->doing_rebuild) return;
+    extern __shared__ __align__(16) unsigned char rows_smem[];
+    RowsStagedShared &sh = *reinterpret_cast<RowsStagedShared *>(rows_smem);
+    uint32_t const tid = threadIdx.x;
+    for (uint32_t i = tid; i < sizeof(DParams) / 4; i += blockDim.x) ((uint32_t *) &sh.P)[i] = ((const uint32_t *) A.params)[i];
+    for (uint32_t i = tid; i < sizeof(DGrid) / 4; i += blockDim.x) ((uint32_t *) &sh.G)[i] = ((const uint32_t *) &A.ctl->grid)[i];
+    if (tid == 0) {
+        const int32_t *bits = A.ctl->grid.bits;
+        int pos = 0;
+        int const maxb = max(bits[0], max(bits[1], bits[2]));
+        for (int i = 0; i < maxb; i++)
+            for (int d = 0; d < 3; d++)
+                if (i < bits[d]) sh.bitpos[d][i] = (uint8_t) pos++;
+        mbar_init(&sh.bar, 1);
+    }
+    __syncthreads();
+    const DParams &P = sh.P;
+    const DGrid &G = sh.G;
+    double const wide = G.radius + G.shadow_eps;
+    float const filter2 = __double2float_ru(wide * wide * (1.0 + 4e-6));
+    float const scale[3] = {G.shadow_scale[0], G.shadow_scale[1], G.shadow_scale[2]};
+    bool const periodic = P.box_kind == BD_BOX_PERIODIC;
+    uint32_t const chunks = A.npad / ROWS_BLOCK;
+    uint32_t parity = 0;
+
+    unsigned long long tot = 0;
+    uint32_t longest = 0, overflowed = 0;
+    for (uint32_t tile = blockIdx.x; tile < chunks * A.replicas; tile += gridDim.x) {
+        uint32_t const chunk = tile % chunks, replica = tile / chunks;
+        uint32_t const local = chunk * ROWS_BLOCK + tid;
+        bool const live = local < A.n;
+        uint32_t const s = replica * A.n + (live ? local : 0u);
+        __syncthreads();  // the previous tile is done with the tables
+        for (uint32_t i = tid; i < STAGE_HASH; i += blockDim.x) sh.hkey[i] = 0xffffffffu;
+        if (tid == 0) {
+            sh.nuniq = 0;
+            sh.bad = 0;
+        }
+        __syncthreads();
+
+        // ---- A: the thread's cells, collected into the block's set ----------------------------------
+        bead4 me;
+        float4 ms = make_float4(0.f, 0.f, 0.f, 0.f);
+        uint32_t ncells = 0, self_key = 0;
+        if (live) {
+            me = A.bpos[s];
+            ms = A.shadow[s];
+            A.pos_out[s] = me;
+            int c[3];
+            cell_coords(P, G, me.x, me.y, me.z, c);
+            uint32_t dil[3][3];
+            int cnt[3];
+#pragma unroll
+            for (int d = 0; d < 3; d++) {
+                int const n = G.n[d];
+                int v[3];
+                int m = 0;
+                if (periodic) {
+                    if (n == 1) {
+                        v[m++] = c[d];
+                    } else if (n == 2) {
+                        v[m++] = c[d];
+                        v[m++] = c[d] ^ 1;
+                    } else {
+                        v[m++] = c[d] == 0 ? n - 1 : c[d] - 1;
+                        v[m++] = c[d];
+                        v[m++] = c[d] == n - 1 ? 0 : c[d] + 1;
+                    }
+                } else {
+                    if (c[d] > 0) v[m++] = c[d] - 1;
+                    v[m++] = c[d];
+                    if (c[d] < n - 1) v[m++] = c[d] + 1;
+                }
+                cnt[d] = m;
+#pragma unroll
+                for (int i = 0; i < 3; i++) {
+                    uint32_t key = 0;
+                    if (i < m)
+                        for (int bit = 0; bit < G.bits[d]; bit++) key |= (((uint32_t) v[i] >> bit) & 1u) << sh.bitpos[d][bit];
+                    dil[d][i] = key;
+                }
+            }
+            {
+                uint32_t key = 0;
+                for (int d = 0; d < 3; d++)
+                    for (int bit = 0; bit < G.bits[d]; bit++) key |= (((uint32_t) c[d] >> bit) & 1u) << sh.bitpos[d][bit];
+                self_key = (replica << G.totalbits) | key;
+            }
+            bool const ghost = w_ghost(me.w);  // no force is evaluated for a ghost: it needs no row
+#pragma unroll
+            for (int iz = 0; iz < 3; iz++)
+#pragma unroll
+                for (int iy = 0; iy < 3; iy++)
+#pragma unroll
+                    for (int ix = 0; ix < 3; ix++) {
+                        if (!(ix < cnt[0] && iy < cnt[1] && iz < cnt[2]) || ghost) continue;
+                        uint32_t const key = (replica << G.totalbits) | dil[0][ix] | dil[1][iy] | dil[2][iz];
+                        if (A.cell_start[key] == A.cell_start[key + 1]) continue;
+                        uint32_t h = (key * 2654435761u) >> 22;
+                        bool placed = false;
+                        for (uint32_t probe = 0; probe < STAGE_HASH; probe++) {
+                            uint32_t const old = atomicCAS(&sh.hkey[h], 0xffffffffu, key);
+                            if (old == 0xffffffffu) {
+                                uint32_t const at = atomicAdd(&sh.nuniq, 1u);
+                                if (at < STAGE_CELLS) sh.uniq[at] = (uint16_t) h;
+                                placed = true;
+                                break;
+                            }
+                            if (old == key) {
+                                placed = true;
+                                break;
+                            }
+                            h = (h + 1) & (STAGE_HASH - 1);
+                        }
+                        if (!placed) sh.bad = 1;
+                        sh.cells[ncells++][tid] = (uint16_t) h;
+                    }
+        }
+        __syncthreads();
+
+        // ---- B: sort the distinct cells by key, lay them out, merge adjacent ones into runs -----------
+        uint32_t const nu = min(sh.nuniq, STAGE_CELLS);
+        bool bad = sh.bad != 0 || sh.nuniq > STAGE_CELLS;
+        for (uint32_t i = tid; i < nu; i += blockDim.x) {
+            uint32_t const mine = sh.hkey[sh.uniq[i]];
+            uint32_t rnk = 0;
+            for (uint32_t u = 0; u < nu; u++) rnk += sh.hkey[sh.uniq[u]] < mine;
+            sh.sorted[rnk] = sh.uniq[i];
+            sh.cbeg[rnk] = A.cell_start[mine];
+            sh.cend[rnk] = A.cell_start[mine + 1];
+        }
+        __syncthreads();
+        if (tid < 32) {
+            uint32_t off = 0, nruns = 0;
+            for (uint32_t base = 0; base < nu; base += 32) {
+                uint32_t const i = base + tid;
+                bool const in = i < nu;
+                uint32_t const b = in ? sh.cbeg[i] : 0u, e = in ? sh.cend[i] : 0u;
+                // a cell opens a new run only when it begins more than STAGE_GAP slots after the previous cell:
+                // the few beads in between are staged along (cheaper than one more bulk copy)
+                uint32_t const gap = (in && i > 0) ? b - sh.cend[i - 1] : 0u;
+                bool const starts = in && (i == 0 || gap > STAGE_GAP);
+                uint32_t const count = (e - b) + (starts ? 0u : gap);
+                uint32_t incl = count;
+                for (int o = 1; o < 32; o <<= 1) {
+                    uint32_t const t = __shfl_up_sync(0xffffffffu, incl, o);
+                    if ((int) tid >= o) incl += t;
+                }
+                uint32_t const mask = __ballot_sync(0xffffffffu, starts);
+                uint32_t const my_off = off + incl - (e - b);  // the cell itself sits after the bridged gap
+                if (in) {
+                    sh.hval[sh.sorted[i]] = (my_off & 0xffffu) | ((e - b) << 16);
+                    if (starts) {
+                        uint32_t const r = nruns + __popc(mask & ((1u << tid) - 1u));
+                        if (r < STAGE_RUNS) {
+                            sh.runs.start[r] = b;
+                            sh.runs.off[r] = my_off;
+                        }
+                    }
+                }
+                off += __shfl_sync(0xffffffffu, incl, 31);
+                nruns += __popc(mask);
+            }
+            if (tid == 0) {
+                if (nruns > STAGE_RUNS || off > STAGE_MAX_BEADS) sh.bad = 1;
+                sh.runs.nruns = min(nruns, STAGE_RUNS);
+                sh.runs.total = off;
+            }
+        }
+        __syncthreads();
+        bad = bad || sh.bad != 0;
+        uint32_t const total = bad ? 0u : sh.runs.total;
+        if (bad && tid == 0) {
+            sh.runs.nruns = 0;
+            sh.runs.total = 0;
+            atomicAdd(&A.ctl->stage_overflow, 1u);
+        }
+        __syncthreads();
+        {
+            const uint32_t *src = reinterpret_cast<const uint32_t *>(&sh.runs);
+            uint32_t *dst = reinterpret_cast<uint32_t *>(A.tile_runs + tile);
+            uint32_t const words = 2 + STAGE_RUNS;  // header + starts; the offsets follow
+            for (uint32_t i = tid; i < sizeof(TileRuns) / 4; i += blockDim.x)
+                if (i < 2 + sh.runs.nruns || (i >= words && i < words + sh.runs.nruns)) dst[i] = src[i];
+        }
+
+        // ---- C: the shadows of the runs into shared memory ------------------------------------------
+        bool const in_smem = total <= ROWS_STAGE_CAP;
+        if (in_smem) {
+            stage_runs(sh.stage, A.shadow, sh.runs, &sh.bar, parity, A.ntot);
+            parity ^= 1u;
+        }
+        __syncthreads();
+
+        // ---- D: one flat walk over the candidates of the thread's cells -------------------------------
+        uint32_t count = 0;
+        bool over = false;
+        if (live && !bad) {
+            uint2 *dst = reinterpret_cast<uint2 *>(A.nbr4) + (size_t) replica * A.npad + local;  // natural position; k_balance permutes
+            uint32_t qn = 0;
+            uint16_t *const queue = &sh.hits[0][tid];
+            auto flush = [&](bool last) {
+                uint32_t const groups = qn / ROW_PAD;
+                for (uint32_t g = 0; g < groups; g++) {
+                    const uint16_t *q4 = queue + g * ROW_PAD * ROWS_BLOCK;
+                    if (count < A.cap) {
+                        *dst = make_uint2((uint32_t) q4[0] | ((uint32_t) q4[ROWS_BLOCK] << 16),
+                                          (uint32_t) q4[2 * ROWS_BLOCK] | ((uint32_t) q4[3 * ROWS_BLOCK] << 16));
+                        dst += A.pstride;
+                        count += ROW_PAD;
+                    } else {
+                        over = true;
+                    }
+                }
+                uint32_t const rem = qn - groups * ROW_PAD;
+                if (!last) {
+                    if (groups)
+                        for (uint32_t k = 0; k < rem; k++) queue[k * ROWS_BLOCK] = queue[(groups * ROW_PAD + k) * ROWS_BLOCK];
+                } else if (rem) {
+                    // the last group is padded with the padding position: the step kernel reads whole groups
+                    const uint16_t *q4 = queue + groups * ROW_PAD * ROWS_BLOCK;
+                    uint32_t const pad = total;
+                    if (count < A.cap) {
+                        uint32_t const e1 = rem > 1 ? q4[ROWS_BLOCK] : pad, e2 = rem > 2 ? q4[2 * ROWS_BLOCK] : pad;
+                        *dst = make_uint2((uint32_t) q4[0] | (e1 << 16), e2 | (pad << 16));
+                        count += rem;
+                    } else {
+                        over = true;
+                    }
+                }
+                qn = rem;
+            };
+            // position of this bead itself in the staged array
+            uint32_t self = 0xffffffffu;
+            uint32_t run = 0, j = 0, e = 0, jslot = 0;
+            while (true) {
+                if (j >= e) {
+                    if (run == ncells) break;
+                    uint32_t const hs = sh.cells[run][tid];
+                    uint32_t const v = sh.hval[hs];
+                    j = v & 0xffffu;
+                    e = j + (v >> 16);
+                    jslot = A.cell_start[sh.hkey[hs]];
+                    if (sh.hkey[hs] == self_key) self = j + (s - jslot);
+                    run++;
+                }
+                uint32_t const left = e - j;
+                uint32_t const j1 = left > 1u ? j + 1 : j, j2 = left > 2u ? j + 2 : j, j3 = left > 3u ? j + 3 : j;
+                float4 q0, q1, q2, q3;
+                if (in_smem) {
+                    q0 = sh.stage[j]; q1 = sh.stage[j1]; q2 = sh.stage[j2]; q3 = sh.stage[j3];
+                } else {
+                    const float4 *g = A.shadow + jslot;
+                    q0 = g[0]; q1 = g[j1 - j]; q2 = g[j2 - j]; q3 = g[j3 - j];
+                }
+                auto consider = [&](uint32_t jj, const float4 &q, bool on) {
+                    float const d2 = periodic ? shadow_dist2<BD_BOX_PERIODIC>(ms, q, scale)
+                                              : shadow_dist2<BD_BOX_OPEN>(ms, q, scale);
+                    if (on && d2 <= filter2 && jj != self) {
+                        queue[qn * ROWS_BLOCK] = (uint16_t) jj;
+                        qn++;
+                    }
+                };
+                consider(j, q0, true);
+                consider(j1, q1, left > 1u);
+                consider(j2, q2, left > 2u);
+                consider(j3, q3, left > 3u);
+                uint32_t const adv = left < 4u ? left : 4u;
+                j += adv;
+                jslot += adv;
+                if (__any_sync(__activemask(), qn > ROWS_QUEUE - 4)) flush(false);
+            }
+            flush(true);
+        }
+        if (live) A.nnbr[s] = count;
+        overflowed += over;
+        tot += count;
+        longest = max(longest, count);
+        if (tid == 0 && !bad) atomicMax(&A.ctl->max_stage, total);
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        tot += __shfl_xor_sync(0xffffffffu, tot, o);
+        longest = max(longest, __shfl_xor_sync(0xffffffffu, longest, o));
+        overflowed += __shfl_xor_sync(0xffffffffu, overflowed, o);
+    }
+    if ((threadIdx.x & 31) == 0 && tot) {
+        atomicAdd(&A.ctl->listed_entries, tot);
+        atomicMax(&A.ctl->max_row, longest);
+        if (overflowed) atomicAdd(&A.ctl->overflow, overflowed);
+    }
+}
+
 /* one bond of bead `oi` (CSR entry {partner original index, ff | second << 8}) as the step kernel wants it:
  * {partner slot, row of the compiled bond table | ff << 12 | second << 15} -- classes do not change between
  * list builds, so the (class_first, class_second) cell of the table is resolved here, once */
@@ -586,11 +916,21 @@ __global__ void __launch_bounds__(BAL_TILE) k_balance(NlistArrays A)
         // (only the groups the row has: what lies beyond a row's padded length is never read)
         uint32_t const groups = (longest + ROW_PAD - 1) / ROW_PAD;
         uint32_t const mine_groups = owner ? (len[from] + ROW_PAD - 1) / ROW_PAD : 0u;
-        for (uint32_t g = 0; g < groups; g++) {
-            uint4 v = make_uint4(0u, 0u, 0u, 0u);
-            if (g < mine_groups) v = A.nbr4[(size_t) g * A.pstride + pbase + from];
-            __syncthreads();
-            if (g < mine_groups) A.nbr4[(size_t) g * A.pstride + pbase + threadIdx.x] = v;
+        if (A.staged) {
+            uint2 *rows = reinterpret_cast<uint2 *>(A.nbr4);  // groups of four 16-bit staged positions
+            for (uint32_t g = 0; g < groups; g++) {
+                uint2 v = make_uint2(0u, 0u);
+                if (g < mine_groups) v = rows[(size_t) g * A.pstride + pbase + from];
+                __syncthreads();
+                if (g < mine_groups) rows[(size_t) g * A.pstride + pbase + threadIdx.x] = v;
+            }
+        } else {
+            for (uint32_t g = 0; g < groups; g++) {
+                uint4 v = make_uint4(0u, 0u, 0u, 0u);
+                if (g < mine_groups) v = A.nbr4[(size_t) g * A.pstride + pbase + from];
+                __syncthreads();
+                if (g < mine_groups) A.nbr4[(size_t) g * A.pstride + pbase + threadIdx.x] = v;
+            }
         }
         A.plen[pbase + threadIdx.x] = owner ? len[from] : 0u;
         if (A.bond_deg) {
@@ -644,9 +984,9 @@ __global__ void __launch_bounds__(NL_BLOCK) k_export_pairs(NlistArrays A, uint32
     double const radius = A.ctl->grid.radius;
     double const r2max = __dmul_rn(radius, radius);
     uint32_t const m = A.plen[p];
+    uint32_t const tile_id = replica * (A.npad / BAL_TILE) + i / BAL_TILE;
     for (uint32_t k = 0; k < m; k++) {
-        uint4 const grp = A.nbr4[(size_t) (k / ROW_PAD) * A.pstride + p];
-        uint32_t const j = k % ROW_PAD == 0 ? grp.x : k % ROW_PAD == 1 ? grp.y : k % ROW_PAD == 2 ? grp.z : grp.w;
+        uint32_t const j = row_entry_slot(A.nbr4, A.tile_runs, A.staged, A.pstride, p, tile_id, k);
         bead4 const o = A.bpos[j];
         uint32_t const oj = w_orig(o.w);
         // the stored rows are a superset by the shadow error bound: apply the reference's test

@@ -36,6 +36,9 @@ struct StepArrays {
     float4 *shadow_out;           // ... of pos_out
     const uint32_t *slot_of;
     const uint4 *nbr4;            // [cap / ROW_PAD][pstride] Verlet rows by thread position (bd_nlist.cuh)
+    const TileRuns *tile_runs;    // [replicas * chunks] staged neighbourhoods (staged rows: uint2 groups of 16-bit positions)
+    uint32_t staged, stage_cap;   // row format; shadows a block can stage (dynamic shared memory)
+    uint32_t stage_off;           // byte offset of the staged shadows in the dynamic shared memory
     const uint32_t *plen;         // [pstride] row length at a position
     const uint2 *bondrow;         // [bond_deg][pstride] {partner slot, ff | second << 8}
     uint32_t bond_deg, npad, pstride;
@@ -195,7 +198,12 @@ __device__ __forceinline__ double compiled_pair_scalar(double ca, double cb, dou
     return s;
 }
 
-constexpr int HIT_CAP = 24;  // near-hits buffered per bead between the two phases of the pair walk
+#ifndef STEP_HIT_CAP
+#define STEP_HIT_CAP 24
+#endif
+constexpr int HIT_CAP = STEP_HIT_CAP;  // near-hits buffered per bead between the two phases of the pair walk
+
+extern __shared__ __align__(16) unsigned char dyn_smem[];  // PairRow[ntypes^2] of the compiled program
 
 struct StepShared {
     alignas(16) DParams P;
@@ -206,87 +214,104 @@ struct StepShared {
     double mu_dt[BD_MAX_TYPES], sigma[BD_MAX_TYPES], sigma_prev[BD_MAX_TYPES];
     uint32_t hits[HIT_CAP][STEP_BLOCK];
     double wall_red[STEP_BLOCK / 32][BD_MAX_WALL_FF][WALL_STATS];
+    // tile staging (bd_device.cuh; staged engines only): whether the tile's shadows are in shared memory.
+    // The run table and the staged shadows live in the dynamic shared memory, so that engines that do not
+    // stage do not pay for them (the L1 gets what shared memory does not take).
+    alignas(8) uint64_t bar;
+    uint32_t stage_ok;
 };
 
-extern __shared__ __align__(16) unsigned char dyn_smem[];  // PairRow[ntypes^2] of the compiled program
+/* dynamic shared memory of the step kernels: [compiled pair rows][compiled bond rows] then, staged engines only,
+ * [TileRuns][staged shadows (stage_cap + 1)] */
+__device__ __forceinline__ TileRuns &tile_table(const StepArrays &A)
+{
+    return *reinterpret_cast<TileRuns *>(dyn_smem + A.stage_off);
+}
+constexpr uint32_t STAGE_TABLE_BYTES = (uint32_t) ((sizeof(TileRuns) + 15) & ~(size_t) 15);
+
+
+/* where phase 1 of the pair walk finds the shadows of the listed neighbours */
+enum WalkMode {
+    WALK_GLOBAL = 0,   // rows of slots, one 16-byte global gather per entry (engines that do not stage)
+    WALK_STAGED = 1,   // rows of 16-bit staged positions, gathers from the tile's shared-memory copy
+    WALK_SPILLED = 2   // staged rows of a tile whose neighbourhood does not fit the block's shared memory:
+                       // positions are translated back to slots through the run table (rare, slow, correct)
+};
+
+__device__ __forceinline__ float4 lds_f4(uint32_t addr)
+{
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+    return v;
+}
 
 /* Non-bonded forces on the bead at slot s from its Verlet row, in two phases:
- *   1. walk the row (groups of ROW_PAD coalesced indices), test the 16-byte shadow of each listed
- *      neighbour against the widened cutoff in single precision and queue the survivors;
+ *   1. walk the row (groups of ROW_PAD coalesced entries), test the 16-byte shadow of each listed
+ *      neighbour against the widened cutoff in single precision and queue the survivors' slots;
  *   2. load the queued neighbours' fp64 records and evaluate them exactly -- the reference's
  *      arithmetic, in row order, so the result does not depend on the shadows at all.
  * About 26 neighbours are listed per bead and 8 interact: phase 1 is cheap per entry and fully
  * convergent, phase 2 runs on a third of the entries. */
-template <int BOX, int PROG>
-__device__ __forceinline__ void pair_forces(const StepArrays &A, StepShared &sh, Select sel, uint32_t s,
-                                            uint32_t pos, const bead4 &me, d3 &F, uint32_t &interactions)
+template <int BOX, int PROG, int MODE>
+__device__ __forceinline__ void pair_walk(const StepArrays &A, StepShared &sh, Select sel, uint32_t s,
+                                          uint32_t pos, const bead4 &me, d3 &F, uint32_t &interactions)
 {
     const DParams &P = sh.P;
     uint32_t const oi = w_orig(me.w), ti = w_type(me.w);
     int const T = P.ntypes;
     (void) oi;
-    if (PROG == PROG_GENERIC) {
-        bool any_pair = false;
-        for (int f = 0; f < BD_MAX_PAIR_FF; f++) any_pair |= ff_on(sel, BD_FF_PAIR, f, P.pair[f].enabled);
-        if (!any_pair) return;
-    }
     const PairRow *mine = reinterpret_cast<const PairRow *>(dyn_smem) + ti * T;
     double const dcut2 = PROG != PROG_GENERIC ? P.pair[A.fast_ff].dcut2 : 0.0;
     float const filter2 = sh.filter2;
     float const scale[3] = {sh.G.shadow_scale[0], sh.G.shadow_scale[1], sh.G.shadow_scale[2]};
     size_t const stride = A.pstride;
-    uint32_t const m = (A.plen[pos] + ROW_PAD - 1) & ~(ROW_PAD - 1);  // rows are padded with the sentinel
+    uint32_t const m = (A.plen[pos] + ROW_PAD - 1) & ~(ROW_PAD - 1);  // rows are padded
     float4 const ms = A.shadow[s];
-    const uint4 *col = A.nbr4 + pos;
+    const uint4 *col = A.nbr4 + pos;                                        // WALK_GLOBAL: four slots per group
+    const uint2 *col2 = reinterpret_cast<const uint2 *>(A.nbr4) + pos;      // staged: four 16-bit positions
+    uint32_t const stage = smem_addr(dyn_smem) + A.stage_off + STAGE_TABLE_BYTES;  // the tile's staged shadows
+    uint32_t const pad = MODE == WALK_GLOBAL ? 0u : tile_table(A).total;            // staged rows are padded with this position
     // the thread's queue column and its row of the compiled pair table, as shared-space addresses
     constexpr uint32_t QSTEP = STEP_BLOCK * 4u;  // bytes between consecutive entries of one thread's queue
     uint32_t const queue = smem_addr(&sh.hits[0][threadIdx.x]);
     uint32_t const qfull = queue + (HIT_CAP - ROW_PAD) * QSTEP;
     uint32_t const cav = smem_addr(dyn_smem) + ti * (uint32_t) T * 8u;  // uniform tables: ca[T*T] then cb[T*T]
 
-#ifdef EXP_SMEM_P1
-    __shared__ float4 exp_fake[1024];
-    for (uint32_t i = threadIdx.x; i < 1024; i += blockDim.x) exp_fake[i] = A.shadow[min((s & ~127u) + i, A.ntot)];
-#ifdef EXP_SMEM_P2
-    __shared__ bead4 exp_fake2[512];
-    for (uint32_t i = threadIdx.x; i < 512; i += blockDim.x) exp_fake2[i] = A.pos[min((s & ~127u) + i, A.ntot)];
-#endif
-    __syncthreads();
-#endif
+    auto fetch = [&](uint32_t out[ROW_PAD]) {
+        if (MODE == WALK_GLOBAL) {
+            uint4 const g = *col;
+            out[0] = g.x; out[1] = g.y; out[2] = g.z; out[3] = g.w;
+        } else {
+            uint2 const g = *col2;
+            out[0] = g.x & 0xffffu; out[1] = g.x >> 16; out[2] = g.y & 0xffffu; out[3] = g.y >> 16;
+        }
+    };
     uint32_t k = 0;
     uint32_t j[ROW_PAD], jn[ROW_PAD];
-    if (m) {
-        uint4 const g = *col;
-        j[0] = g.x; j[1] = g.y; j[2] = g.z; j[3] = g.w;
-    }
+    if (m) fetch(j);
     while (k < m) {
         // ---- phase 1: single-precision filter ------------------------------------------------
-        // the indices of the next group are requested together with the shadows of this one, so
+        // the entries of the next group are requested together with the shadows of this one, so
         // only the gather itself is on the dependent path
         uint32_t qp = queue;
         while (k < m && qp <= qfull) {
             float4 q[ROW_PAD];
 #pragma unroll
-#ifdef EXP_SMEM_P1
-            for (int u = 0; u < (int) ROW_PAD; u++) q[u] = exp_fake[j[u] & 1023u];
-#else
-            for (int u = 0; u < (int) ROW_PAD; u++) q[u] = __ldg(A.shadow + j[u]);
-#endif
-            col += stride;
-            k += ROW_PAD;
-            if (k < m) {
-                uint4 const g = *col;
-                jn[0] = g.x; jn[1] = g.y; jn[2] = g.z; jn[3] = g.w;
+            for (int u = 0; u < (int) ROW_PAD; u++) {
+                if (MODE == WALK_GLOBAL) q[u] = __ldg(A.shadow + j[u]);
+                else if (MODE == WALK_STAGED) q[u] = lds_f4(stage + j[u] * 16u);
+                else q[u] = __ldg(A.shadow + (j[u] == pad ? A.ntot : staged_to_slot(tile_table(A), j[u])));
             }
+            col += stride;
+            col2 += stride;
+            k += ROW_PAD;
+            if (k < m) fetch(jn);
 #pragma unroll
             for (int u = 0; u < (int) ROW_PAD; u++) {
                 bool near = shadow_dist2<BOX>(ms, q[u], scale) <= filter2;
-#ifdef EXP_SMEM_P1
-                near = (near && q[u].w == 12345.0f) || (((j[u] * 2654435761u) >> 24) < 83u && j[u] < A.ntot);
-#endif
-                if (BOX == BD_BOX_PERIODIC) near = near && j[u] < A.ntot;  // fixed point has no NaN
+                if (BOX == BD_BOX_PERIODIC) near = near && (MODE == WALK_GLOBAL ? j[u] < A.ntot : j[u] != pad);  // fixed point has no NaN
                 if (near) {
-                    sts_u32(qp, j[u]);
+                    sts_u32(qp, MODE == WALK_GLOBAL ? j[u] : __float_as_uint(q[u].w));  // the neighbour's slot
                     qp += QSTEP;
                 }
             }
@@ -298,13 +323,8 @@ __device__ __forceinline__ void pair_forces(const StepArrays &A, StepShared &sh,
         // ---- phase 2: exact evaluation -------------------------------------------------------
         for (uint32_t qa = queue; qa < qp; qa += 2 * QSTEP) {
             uint32_t const j0 = lds_u32(qa), j1 = lds_u32(qa + QSTEP);
-#ifdef EXP_SMEM_P2
-            bead4 const o0 = exp_fake2[j0 & 511u];
-            bead4 const o1 = exp_fake2[j1 & 511u];
-#else
             bead4 const o0 = load_bead(A.pos + j0);
             bead4 const o1 = load_bead(A.pos + j1);
-#endif
 #pragma unroll
             for (int u = 0; u < 2; u++) {
                 const bead4 &o = u == 0 ? o0 : o1;
@@ -344,6 +364,44 @@ __device__ __forceinline__ void pair_forces(const StepArrays &A, StepShared &sh,
             }
         }
     }
+}
+
+template <int BOX, int PROG>
+__device__ __forceinline__ void pair_forces(const StepArrays &A, StepShared &sh, Select sel, uint32_t s,
+                                            uint32_t pos, const bead4 &me, d3 &F, uint32_t &interactions)
+{
+    if (PROG == PROG_GENERIC) {
+        bool any_pair = false;
+        for (int f = 0; f < BD_MAX_PAIR_FF; f++) any_pair |= ff_on(sel, BD_FF_PAIR, f, sh.P.pair[f].enabled);
+        if (!any_pair) return;
+    }
+    // block-uniform choice
+    if (!A.staged) pair_walk<BOX, PROG, WALK_GLOBAL>(A, sh, sel, s, pos, me, F, interactions);
+    else if (sh.stage_ok) pair_walk<BOX, PROG, WALK_STAGED>(A, sh, sel, s, pos, me, F, interactions);
+    else pair_walk<BOX, PROG, WALK_SPILLED>(A, sh, sel, s, pos, me, F, interactions);
+}
+
+/* Bring the tile's neighbourhood into shared memory (staged engines; every thread of the block calls this
+ * before block_forces).  `parity` is the block's count of stagings so far, modulo 2. */
+__device__ __forceinline__ void stage_tile(const StepArrays &A, StepShared &sh, uint32_t replica, uint32_t chunk,
+                                           uint32_t &parity)
+{
+    if (!A.staged) return;
+    __syncthreads();  // the block's previous tile is done with the table and the staged copy
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(A.tile_runs + (size_t) replica * A.chunks + chunk);
+    TileRuns &runs = tile_table(A);
+    uint32_t *dst = reinterpret_cast<uint32_t *>(&runs);
+    uint32_t const nruns = src[0];
+    for (uint32_t i = threadIdx.x; i < 2u + STAGE_RUNS + nruns; i += blockDim.x)
+        if (i < 2u + nruns || i >= 2u + STAGE_RUNS) dst[i] = src[i];
+    __syncthreads();
+    bool const ok = runs.total <= A.stage_cap;
+    if (threadIdx.x == 0) sh.stage_ok = ok;
+    if (ok) {
+        stage_runs(reinterpret_cast<float4 *>(dyn_smem + A.stage_off + STAGE_TABLE_BYTES), A.shadow, runs, &sh.bar, parity, A.ntot);
+        parity ^= 1u;
+    }
+    __syncthreads();
 }
 
 /* bonded pairs, bending triples and point sources acting on one bead */
@@ -529,6 +587,7 @@ template <int PROG>
 __device__ __forceinline__ void load_shared(StepShared &sh, const StepArrays &A, Select sel)
 {
     static_assert(sizeof(DParams) % 16 == 0 && sizeof(DGrid) % 16 == 0, "copied in 16-byte pieces");
+    if (threadIdx.x == 0) mbar_init(&sh.bar, 1);
     copy16(&sh.P, A.params, sizeof(DParams));
     copy16(&sh.G, &A.ctl->grid, sizeof(DGrid));
     if (PROG != PROG_GENERIC) copy16(dyn_smem, A.pair_rows, A.ntypes2 * (uint32_t) sizeof(PairRow));
@@ -648,7 +707,7 @@ __device__ __forceinline__ double integrate_bead(const StepArrays &A, const DPar
     double x = me.x + mu_dt * F.x, y = me.y + mu_dt * F.y, z2 = me.z + mu_dt * F.z;
     x += 0.5 * (wx + px); y += 0.5 * (wy + py); z2 += 0.5 * (wz + pz);
     store_bead(A.pos_out + s, x, y, z2, me.w);
-    A.shadow_out[s] = make_shadow<BOX>(P, G, x, y, z2);
+    A.shadow_out[s] = make_shadow<BOX>(P, G, x, y, z2, s);
 
     bead4 const b0 = load_bead(A.bpos + s);
     d3 const d = displacement_t<BOX>(P, x, y, z2, b0.x, b0.y, b0.z);
@@ -662,7 +721,7 @@ __device__ __forceinline__ double carry_ghost(const StepArrays &A, const DParams
                                               const bead4 &me)
 {
     store_bead(A.pos_out + s, me.x, me.y, me.z, me.w);
-    A.shadow_out[s] = make_shadow<BOX>(P, G, me.x, me.y, me.z);
+    A.shadow_out[s] = make_shadow<BOX>(P, G, me.x, me.y, me.z, s);
     bead4 const b0 = load_bead(A.bpos + s);
     d3 const d = displacement_t<BOX>(P, me.x, me.y, me.z, b0.x, b0.y, b0.z);
     return sqnorm_exact(d.x, d.y, d.z);
@@ -704,8 +763,10 @@ __global__ void __launch_bounds__(STEP_BLOCK, STEP_MIN_BLOCKS) k_step_fused(Step
     __syncthreads();
     double const known = __longlong_as_double((long long) A.ctl->max_disp2_bits);
     double moved2 = 0.0;
+    uint32_t parity = 0;
     uint32_t const last = min((blockIdx.x + 1) * STEP_TILES, A.chunks);
     for (uint32_t chunk = blockIdx.x * STEP_TILES; chunk < last; chunk++) {
+        stage_tile(A, sh, replica, chunk, parity);
         bool const live = chunk * STEP_BLOCK + threadIdx.x < A.n;
         // threads take the tile's beads in order of row length, so that the rows of a warp end together
         uint32_t const s = replica * A.n
@@ -732,6 +793,8 @@ __global__ void __launch_bounds__(STEP_BLOCK) k_force(StepArrays A, StepScalars 
     __shared__ StepShared sh;
     load_shared<PROG>(sh, A, sel);
     uint32_t const replica = blockIdx.y, chunk = blockIdx.x;
+    uint32_t parity = 0;
+    stage_tile(A, sh, replica, chunk, parity);
     bool const live = chunk * STEP_BLOCK + threadIdx.x < A.n;
     uint32_t const s = replica * A.n
         + (live ? chunk * STEP_BLOCK + A.order[replica * A.n + chunk * STEP_BLOCK + threadIdx.x] : 0u);
@@ -823,8 +886,7 @@ __global__ void __launch_bounds__(STEP_BLOCK) k_energy(StepArrays A, Select sel,
         uint32_t const base = replica * A.n;
         uint32_t const m = A.plen[pos];
         for (uint32_t k = 0; k < m; k++) {
-            uint4 const grp = A.nbr4[(size_t) (k / ROW_PAD) * A.pstride + pos];
-            uint32_t const j = k % ROW_PAD == 0 ? grp.x : k % ROW_PAD == 1 ? grp.y : k % ROW_PAD == 2 ? grp.z : grp.w;
+            uint32_t const j = row_entry_slot(A.nbr4, A.tile_runs, A.staged, A.pstride, pos, replica * A.chunks + chunk, k);
             bead4 const o = load_bead(A.pos + j);
             uint32_t const oj = w_orig(o.w), tj = w_type(o.w);
             if (oi >= oj) continue;
@@ -1013,10 +1075,10 @@ __global__ void k_scatter_tracked(bead4 *pos, float4 *shadow, const bead4 *bpos,
         bead4 const b0 = bpos[s];
         d3 d;
         if (params->box_kind == BD_BOX_PERIODIC) {
-            shadow[s] = make_shadow<BD_BOX_PERIODIC>(*params, ctl->grid, x, y, z);
+            shadow[s] = make_shadow<BD_BOX_PERIODIC>(*params, ctl->grid, x, y, z, s);
             d = displacement_t<BD_BOX_PERIODIC>(*params, x, y, z, b0.x, b0.y, b0.z);
         } else {
-            shadow[s] = make_shadow<BD_BOX_OPEN>(*params, ctl->grid, x, y, z);
+            shadow[s] = make_shadow<BD_BOX_OPEN>(*params, ctl->grid, x, y, z, s);
             d = displacement_t<BD_BOX_OPEN>(*params, x, y, z, b0.x, b0.y, b0.z);
         }
         moved2 = sqnorm_exact(d.x, d.y, d.z);
@@ -1073,8 +1135,8 @@ __global__ void k_scatter_indexed(bead4 *pos, float4 *shadow, const uint32_t *sl
     pos[s].x = x;
     pos[s].y = y;
     pos[s].z = z;
-    shadow[s] = params->box_kind == BD_BOX_PERIODIC ? make_shadow<BD_BOX_PERIODIC>(*params, ctl->grid, x, y, z)
-                                                    : make_shadow<BD_BOX_OPEN>(*params, ctl->grid, x, y, z);
+    shadow[s] = params->box_kind == BD_BOX_PERIODIC ? make_shadow<BD_BOX_PERIODIC>(*params, ctl->grid, x, y, z, s)
+                                                    : make_shadow<BD_BOX_OPEN>(*params, ctl->grid, x, y, z, s);
 }
 
 /* (re)write the packed word of every bead: original index, class, target masks */
@@ -1121,8 +1183,8 @@ __global__ void k_init_identity(uint32_t *slot_of, bead4 *pos0, bead4 *pos1, bea
         b.w = pack_w(0xffffffffu, 0, 0, 0);
         pos0[g] = b;
         pos1[g] = b;
-        shadow0[g] = make_float4(fnan, fnan, fnan, 0.0f);
-        shadow1[g] = make_float4(fnan, fnan, fnan, 0.0f);
+        shadow0[g] = make_float4(fnan, fnan, fnan, __uint_as_float(g));
+        shadow1[g] = make_float4(fnan, fnan, fnan, __uint_as_float(g));
         return;
     }
     slot_of[g] = g;
@@ -1133,8 +1195,8 @@ __global__ void k_init_identity(uint32_t *slot_of, bead4 *pos0, bead4 *pos1, bea
     pos0[g] = b;
     pos1[g] = b;
     bpos[g] = b;
-    shadow0[g] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    shadow1[g] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    shadow0[g] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(g));
+    shadow1[g] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(g));
 }
 
 }  // namespace bd

@@ -51,6 +51,8 @@ def parse():
     ap.add_argument("--frozen-walls", action="store_true",
                     help="genome100kb: keep the wall semiaxes fixed (round-1 workload) instead of the driver's per-step feedback")
     ap.add_argument("--verlet-factor", type=float, default=None, help="list radius / dcut (engine option; reference 1.5)")
+    ap.add_argument("--staged", type=int, default=None, help="engine option staged (tile staging of the pair walk) after the relaxation")
+    ap.add_argument("--stage-capacity", type=int, default=None, help="engine option stage_capacity")
     ap.add_argument("--workload", default="genome100kb", choices=sorted(WORKLOADS) + ["slab1kb"],
                     help="genome100kb: the headline replica ensemble (weak scaling); ab_box / ab_sphere / genome10mb / "
                          "chromatin1kb: the other BASELINE.json configurations on one engine per GPU; slab1kb: ONE 1kb "
@@ -392,9 +394,19 @@ def run_b200(args):
         sysm.step(k, dt, kT, seed=1234 + rank, first_step=step_no[0])
         step_no[0] += k
 
+    if args.staged is not None:
+        sysm.set_option("staged", 0)
     advance(args.relax)
+    if args.staged is not None:
+        sysm.sync()
+        sysm.set_option("staged", args.staged)
+    if args.stage_capacity is not None:
+        sysm.set_option("stage_capacity", args.stage_capacity)
     advance(max(args.warmup, 3))
     sysm.sync()
+    if args.staged:
+        print("max_stage", sysm.get_option("max_stage"), "stage_capacity", sysm.get_option("stage_capacity"),
+              "staged", sysm.get_option("staged"), file=sys.stderr)
     parity = None
     if rank == 0 and not args.no_parity:
         parity = parity_check(eng, sysm, scen, R, ids)

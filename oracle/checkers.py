@@ -56,10 +56,13 @@ class DriverC4:
     """One system of scenarios.genome_100kb on the unmodified micromd with compile-time potentials and the
     driver's per-step wall feedback as the simulate_brownian_dynamics callback.  TIMING ONLY."""
 
-    def __init__(self, scen, positions, flavour="O2"):
+    def __init__(self, scen, positions, flavour="O2", lib_path=None):
+        """lib_path: the same source (oracle/ref_drivers.cc) compiled against another <md.hpp> -- e.g. the
+        B200 header 2022a-genome-dynamics_b200/md/md.hpp + libbd_b200.so, which is how the single-system
+        latency of a relinked driver is measured (profiles/measure_configs.py)"""
         import scenarios as sc
 
-        lib = _C.CDLL(DRIVER_LIBS[flavour])
+        lib = _C.CDLL(lib_path or DRIVER_LIBS[flavour])
         lib.drv_c4_create.restype = _C.c_void_p
         lib.drv_c4_create.argtypes = [_C.c_int64, _C.c_void_p, _C.c_void_p, _C.c_int64, _C.c_void_p, _C.c_int64,
                                       _C.c_void_p, _C.c_void_p, _C.c_int64]
