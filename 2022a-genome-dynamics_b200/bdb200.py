@@ -172,6 +172,8 @@ ENGINE_ONLY = {
     "set_wall_relaxation": [C.c_void_p, _P(C.c_int32), C.c_int32, _dbl_p, C.c_double],
     "noise_statistics": [C.c_uint64, C.c_int64, C.c_int64, C.c_int64, C.c_int32, C.c_int32, _dbl_p, C.c_int32],
     "set_all_positions": [C.c_void_p, C.c_void_p],
+    "nsearch_pairs_ordered": [C.c_int32, _dbl_p, C.c_int64, C.c_double, _dbl_p, C.c_int64, _u32_p, C.c_int64, _P(C.c_int64),
+                              C.c_int32],
     "get_all_positions": [C.c_void_p, C.c_void_p],
     "get_all_positions_async": [C.c_void_p, C.c_void_p],
     "set_owned": [C.c_void_p, _u8_p],
@@ -250,14 +252,16 @@ class Backend:
                   _dp(xyz), len(xyz), out.ctypes.data_as(_u32_p), device)
         return out
 
-    def nsearch_pairs(self, box_kind, period, particle_count, dcut, xyz, cap=None, device=0):
+    def nsearch_pairs(self, box_kind, period, particle_count, dcut, xyz, cap=None, device=0, ordered=False):
+        """ordered (engine only): the reference's emission order (orc_ / ref_ always emit in it)"""
+        fn = "nsearch_pairs_ordered" if ordered else "nsearch_pairs"
         xyz = np.ascontiguousarray(xyz, dtype=np.float64)
         period = np.ascontiguousarray(period if period is not None else [1, 1, 1], dtype=np.float64)
         cap = int(cap if cap is not None else max(1024, 64 * len(xyz)))
         while True:
             out = np.zeros((cap, 2), dtype=np.uint32)
             count = C.c_int64(0)
-            self.call("nsearch_pairs", box_kind, _dp(period), int(particle_count), float(dcut),
+            self.call(fn, box_kind, _dp(period), int(particle_count), float(dcut),
                       _dp(xyz), len(xyz), out.ctypes.data_as(_u32_p), cap, C.byref(count), device)
             if count.value <= cap:
                 return out[: count.value]

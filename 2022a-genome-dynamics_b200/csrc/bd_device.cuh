@@ -129,6 +129,7 @@ struct DControl {
     uint32_t stage_overflow; // tiles whose neighbourhood did not fit the staging tables (sticky; bd_nlist.cuh)
     uint32_t max_stage;      // largest staged neighbourhood (beads) of a tile at the last build
     unsigned long long rebuilds;
+    unsigned long long graph_rebuilds;  // ... of which inside a step graph's conditional node (bd_engine.cu)
     unsigned long long max_disp2_bits;  // bits of max_i |x_i - x_i(build)|^2, kept by the step kernel
     unsigned long long listed_entries;  // sum of row lengths at the last build (2 x listed pairs)
     unsigned long long bbox_lo[3], bbox_hi[3];  // order-preserving encodings of the bounding box

@@ -167,6 +167,17 @@ struct bd_engine {
     bool list_verified = false;  // rows were checked for overflow since the last host-side change
     int64_t capacity_rebuilds = 0;  // builds repeated only because the ELL rows were re-sized
 
+    // one BD step as a CUDA graph per ping-pong side (step_graph below)
+    struct StepGraph {
+        cudaGraph_t graph = nullptr;
+        cudaGraphExec_t exec = nullptr;
+        cudaGraphNode_t step_node = nullptr;
+        cudaKernelNodeParams step_params = {};
+        std::vector<unsigned char> signature;  // everything the nodes were built from
+    } graphs[2];
+    bool use_graph = true;
+    int64_t graph_steps = 0;
+
     // optional CUDA-event timing of the step kernel alone (bench.py roofline)
     bool time_kernel = false;
     uint32_t replica_base = 0, replica_stride = 1;  // noise key of local replica r (bd_set_option)
@@ -175,6 +186,7 @@ struct bd_engine {
 
 static int sync_and_check(bd_engine *h);
 static void opt_in_shared_memory();
+static void destroy_step_graph(bd_engine::StepGraph &g);
 static size_t table_bytes(uint32_t ntypes2, uint32_t nbond_rows);
 
 // ---- small helpers -------------------------------------------------------------------------------
@@ -595,6 +607,8 @@ extern "C" int bd_destroy(bd_engine *h)
     h->tile_runs.release();
     h->bondrow.release();
     h->d_bond_rows.release();
+    destroy_step_graph(h->graphs[0]);
+    destroy_step_graph(h->graphs[1]);
     if (h->contact_search) bd_destroy(h->contact_search);
     for (int k = 0; k < 2; k++) {
         h->contact_keys[k].release();
@@ -804,7 +818,8 @@ extern "C" int bd_scatter_positions_indexed(bd_engine *h, const uint32_t *d_inde
     if (count == 0) return 0;
     if (upload_params(h)) return 1;
     k_scatter_indexed<<<blocks_for((uint32_t) count, 256), 256, 0, h->stream>>>(
-        h->pos[h->cur].p, h->shadow[h->cur].p, h->slot_of.p, d_index, d_xyz, (uint32_t) count, h->d_params.p, h->ctl.p);
+        h->pos[h->cur].p, h->shadow[h->cur].p, h->bpos.p, h->slot_of.p, d_index, d_xyz, (uint32_t) count, h->d_params.p,
+        h->ctl.p);
     h->launches++;
     CK(cudaGetLastError());
     return 0;
@@ -1098,6 +1113,7 @@ extern "C" int bd_set_ff_enabled(bd_engine *h, int32_t ff_class, int32_t ff, int
 static NlistArrays nlist_arrays(bd_engine *h)
 {
     NlistArrays A;
+    std::memset(&A, 0, sizeof A);  // padding included: the step graphs compare these structs byte for byte
     A.pos = h->pos[h->cur].p;
     A.pos_out = h->pos[h->cur].p;
     A.bpos = h->bpos.p;
@@ -1138,6 +1154,7 @@ static NlistArrays nlist_arrays(bd_engine *h)
 static StepArrays step_arrays(bd_engine *h)
 {
     StepArrays A;
+    std::memset(&A, 0, sizeof A);  // padding included: the step graphs compare these structs byte for byte
     A.pos = h->pos[h->cur].p;
     A.pos_out = h->pos[h->cur ^ 1].p;
     A.shadow = h->shadow[h->cur].p;
@@ -1291,7 +1308,7 @@ static int enqueue_rebuild_chain(bd_engine *h)
     unsigned const bead_blocks = std::min(blocks_for(h->ntot, NL_BLOCK), 148u * 8u);
     unsigned const row_blocks = std::min(blocks_for(h->ntot, ROWS_BLOCK), 148u * 56u);
     unsigned const tile_blocks = blocks_for(h->cell_cap, SCAN_TILE);
-    k_rebuild_begin<<<1, 32, 0, st>>>(h->ctl.p, h->d_params.p);
+    k_rebuild_begin<<<1, 32, 0, st>>>(h->ctl.p, h->d_params.p, (cudaGraphConditionalHandle) 0, 0u);
     k_bbox_zero<<<std::min(bead_blocks + tile_blocks, 148u * 8u), NL_BLOCK, 0, st>>>(A);
     k_make_grid<<<1, 32, 0, st>>>(A);
     k_cell_count<<<bead_blocks, NL_BLOCK, 0, st>>>(A);
@@ -1387,6 +1404,166 @@ static int prepare_list(bd_engine *h)
     return fail("bd: neighbour rows keep overflowing (positions degenerate?)");
 }
 
+// ---- one BD step as a CUDA graph with a conditional rebuild -----------------------------------------
+//
+// Launched kernel by kernel, a step is k_rebuild_begin + ten chain kernels that return at once nine times out
+// of ten + the step kernel (+ the wall relaxation): thirteen launches, ~40 us of launch gaps that dominate a
+// single 62 600-bead system (15 us of work) and cost the 64-replica ensemble 4 %.  As a graph the chain sits
+// in a conditional IF node whose handle k_rebuild_begin sets on the device, so a step that keeps its list
+// executes two (three) kernels, and the host issues one cudaGraphLaunch.  The graph of a ping-pong side is
+// rebuilt whenever anything it was built from differs (compared byte for byte: pointers, sizes, kernels,
+// launch shapes), which makes it safe against every setter of this file; only the step kernel's scalars
+// (step number, ...) are patched per launch.
+
+template <int BOX>
+static const void *step_kernel_of(int prog)
+{
+    switch (prog) {
+    case PROG_SC23_SC83: return (const void *) k_step_fused<BOX, PROG_SC23_SC83>;
+    case PROG_SC23: return (const void *) k_step_fused<BOX, PROG_SC23>;
+    default: return (const void *) k_step_fused<BOX, PROG_GENERIC>;
+    }
+}
+
+static void destroy_step_graph(bd_engine::StepGraph &g)
+{
+    if (g.exec) cudaGraphExecDestroy(g.exec);
+    if (g.graph) cudaGraphDestroy(g.graph);
+    g.exec = nullptr;
+    g.graph = nullptr;
+    g.step_node = nullptr;
+    g.signature.clear();
+}
+
+template <typename T>
+static void sign(std::vector<unsigned char> &sig, const T &v)
+{
+    const unsigned char *p = reinterpret_cast<const unsigned char *>(&v);
+    sig.insert(sig.end(), p, p + sizeof(T));
+}
+
+static int add_kernel(cudaGraph_t graph, cudaGraphNode_t *node, cudaGraphNode_t after, const void *func, dim3 grid,
+                      dim3 block, size_t smem, void **args)
+{
+    cudaKernelNodeParams kp = {};
+    kp.func = const_cast<void *>(func);
+    kp.gridDim = grid;
+    kp.blockDim = block;
+    kp.sharedMemBytes = (unsigned) smem;
+    kp.kernelParams = args;
+    CK(cudaGraphAddKernelNode(node, graph, after ? &after : nullptr, after ? 1 : 0, &kp));
+    return 0;
+}
+
+/* make graphs[h->cur] current for (A, S-independent launch data); dt is the wall relaxation's timestep */
+static int ensure_step_graph(bd_engine *h, const StepArrays &A, const StepScalars &S, double dt)
+{
+    bd_engine::StepGraph &g = h->graphs[h->cur];
+    NlistArrays NA = nlist_arrays(h);
+    const void *step_fn = h->hp.box_kind == BD_BOX_PERIODIC ? step_kernel_of<BD_BOX_PERIODIC>(h->prog)
+                                                            : step_kernel_of<BD_BOX_OPEN>(h->prog);
+    size_t const step_smem = step_smem_bytes(A);
+    dim3 const step_grid((h->chunks + STEP_TILES - 1) / STEP_TILES, h->replicas);
+    std::vector<unsigned char> sig;
+    sign(sig, NA);
+    sign(sig, A);
+    sign(sig, step_fn);
+    sign(sig, step_smem);
+    sign(sig, step_grid);
+    sign(sig, h->relax);
+    sign(sig, dt);
+    sign(sig, h->cell_cap);
+    if (g.exec && sig == g.signature) return 0;
+    destroy_step_graph(g);
+
+    CK(cudaGraphCreate(&g.graph, 0));
+    cudaGraphConditionalHandle gate;
+    CK(cudaGraphConditionalHandleCreate(&gate, g.graph, 0, cudaGraphCondAssignDefault));
+    DControl *ctl = h->ctl.p;
+    const DParams *params = h->d_params.p;
+    uint32_t use_gate = 1;
+    cudaGraphNode_t begin = nullptr, cond = nullptr, relax = nullptr, prev = nullptr;
+    {
+        void *args[] = {&ctl, &params, &gate, &use_gate};
+        if (add_kernel(g.graph, &begin, nullptr, (const void *) k_rebuild_begin, 1, 32, 0, args)) return 1;
+    }
+    cudaGraphNodeParams cp = {};
+    cp.type = cudaGraphNodeTypeConditional;
+    cp.conditional.handle = gate;
+    cp.conditional.type = cudaGraphCondTypeIf;
+    cp.conditional.size = 1;
+    CK(cudaGraphAddNode(&cond, g.graph, &begin, 1, &cp));
+    cudaGraph_t body = cp.conditional.phGraph_out[0];
+    {
+        unsigned const bead_blocks = std::min(blocks_for(h->ntot, NL_BLOCK), 148u * 8u);
+        unsigned const row_blocks = std::min(blocks_for(h->ntot, ROWS_BLOCK), 148u * 56u);
+        unsigned const tile_blocks = blocks_for(h->cell_cap, SCAN_TILE);
+        unsigned const tiles = h->chunks * h->replicas;
+        void *args[] = {&NA};
+        struct { const void *fn; unsigned grid, block; size_t smem; } chain[] = {
+            {(const void *) k_bbox_zero, std::min(bead_blocks + tile_blocks, 148u * 8u), NL_BLOCK, 0},
+            {(const void *) k_make_grid, 1, 32, 0},
+            {(const void *) k_cell_count, bead_blocks, NL_BLOCK, 0},
+            {(const void *) k_scan_reduce, tile_blocks, NL_BLOCK, 0},
+            {(const void *) k_scan_top, 1, 1024, 0},
+            {(const void *) k_scan_down, tile_blocks, NL_BLOCK, 0},
+            {(const void *) k_group, bead_blocks, NL_BLOCK, 0},
+            {(const void *) k_place, bead_blocks, NL_BLOCK, 0},
+            {h->staged ? (const void *) k_rows_staged : (const void *) k_rows, h->staged ? std::min(tiles, 148u * 12u) : row_blocks,
+             ROWS_BLOCK, h->staged ? sizeof(RowsStagedShared) : 0},
+            {(const void *) k_balance, std::min(tiles, 148u * 16u), BAL_TILE, 0},
+        };
+        for (auto &k : chain) {
+            cudaGraphNode_t node = nullptr;
+            if (add_kernel(body, &node, prev, k.fn, k.grid, k.block, k.smem, args)) return 1;
+            prev = node;
+        }
+    }
+    {
+        StepArrays a = A;
+        StepScalars s0 = S;
+        void *args[] = {&a, &s0};
+        if (add_kernel(g.graph, &g.step_node, cond, step_fn, step_grid, STEP_BLOCK, step_smem, args)) return 1;
+        g.step_params = {};
+        g.step_params.func = const_cast<void *>(step_fn);
+        g.step_params.gridDim = step_grid;
+        g.step_params.blockDim = dim3(STEP_BLOCK);
+        g.step_params.sharedMemBytes = (unsigned) step_smem;
+    }
+    if (h->relax.mask) {
+        const double *partial = h->wall_partial.p;
+        double *out = h->wall_out.p;
+        DWallGeom *geom = h->wall_geom.p;
+        WallRelax law = h->relax;
+        uint32_t chunks = h->chunks;
+        double step_dt = dt;
+        void *args[] = {&partial, &out, &geom, &law, &chunks, &step_dt};
+        if (add_kernel(g.graph, &relax, g.step_node, (const void *) k_wall_relax, h->replicas, RELAX_WIDTH * RELAX_LANES, 0, args))
+            return 1;
+    }
+    CK(cudaGraphInstantiate(&g.exec, g.graph, 0));
+    g.signature.swap(sig);
+    return 0;
+}
+
+/* one step through the graph of the current ping-pong side */
+static int launch_step_graph(bd_engine *h, const StepArrays &A, const StepScalars &S, double dt)
+{
+    if (upload_params(h)) return 1;
+    if (ensure_step_graph(h, A, S, dt)) return 1;
+    bd_engine::StepGraph &g = h->graphs[h->cur];
+    StepArrays a = A;
+    StepScalars s = S;
+    void *args[] = {&a, &s};
+    cudaKernelNodeParams kp = g.step_params;
+    kp.kernelParams = args;
+    CK(cudaGraphExecKernelNodeSetParams(g.exec, g.step_node, &kp));
+    CK(cudaGraphLaunch(g.exec, h->stream));
+    h->launches += h->relax.mask ? 3 : 2;  // + 10 per rebuild inside the conditional node (counted on the device)
+    h->graph_steps++;
+    return 0;
+}
+
 extern "C" int bd_step(bd_engine *h, const bd_step_config *cfg)
 {
     NEED(h);
@@ -1454,7 +1631,8 @@ extern "C" int bd_step(bd_engine *h, const bd_step_config *cfg)
             CK(cudaMemcpyAsync(h->replay.p, cfg->replay_normals + staged_from * per_step,
                                staged_count * per_step * sizeof(double), cudaMemcpyHostToDevice, st));
         }
-        if (enqueue_rebuild_chain(h)) return 1;
+        bool const graphed = h->use_graph && !adaptive && !replay && !h->time_kernel && !h->bond_rows_stale;
+        if (!graphed && enqueue_rebuild_chain(h)) return 1;
         StepArrays const A = step_arrays(h);
         S.step = cfg->first_step + k;
         S.dt = cfg->timestep;
@@ -1462,6 +1640,15 @@ extern "C" int bd_step(bd_engine *h, const bd_step_config *cfg)
         S.kT_prev = h->last_kT;
         S.want_stats = k == cfg->steps - 1 || h->relax.mask != 0;
         if (replay) S.replay = h->replay.p + ((size_t) k - staged_from) * per_step;
+        if (graphed) {
+            if (launch_step_graph(h, A, S, cfg->timestep)) return 1;
+            h->wall_stats_fresh = h->relax.mask != 0;
+            h->cur ^= 1;
+            h->last_dt = cfg->timestep;
+            h->last_kT = cfg->temperature;
+            h->steps_done++;
+            continue;
+        }
         if (!adaptive) {
             cudaEvent_t e0 = nullptr, e1 = nullptr;
             if (h->time_kernel) {
@@ -1702,6 +1889,10 @@ extern "C" int bd_set_option(bd_engine *h, const char *name, double value)
         h->time_kernel = value != 0;
         return 0;
     }
+    if (key == "step_graph") {
+        h->use_graph = value != 0;
+        return 0;
+    }
     if (key == "replica_id_base" || key == "replica_id_stride") {
         if (!(value >= 0 && value < 4294967296.0)) return fail("bd_set_option: replica id out of range");
         (key == "replica_id_base" ? h->replica_base : h->replica_stride) = (uint32_t) value;
@@ -1729,6 +1920,7 @@ extern "C" int bd_get_option(bd_engine *h, const char *name, double *value)
     else if (key == "replica_id_stride") *value = h->replica_stride;
     else if (key == "specialize") *value = h->specialize;
     else if (key == "staged") *value = h->staged;
+    else if (key == "step_graph") *value = h->use_graph;
     else if (key == "stage_capacity") *value = h->stage_cap;
     else if (key == "max_stage") {
         CK(cudaStreamSynchronize(h->stream));
@@ -1762,6 +1954,13 @@ extern "C" int bd_get_launch_count(bd_engine *h, int64_t *out)
 {
     NEED(h);
     *out = h->launches;
+    if (h->graph_steps) {
+        // the ten chain kernels inside the step graphs' conditional nodes ran once per rebuild (device count)
+        CK(cudaStreamSynchronize(h->stream));
+        unsigned long long in_graph = 0;
+        CK(cudaMemcpy(&in_graph, &h->ctl.p->graph_rebuilds, sizeof in_graph, cudaMemcpyDeviceToHost));
+        *out += 10 * (int64_t) in_graph;
+    }
     return 0;
 }
 

@@ -66,7 +66,10 @@ struct NlistArrays {
 /* decide whether this chain rebuilds the list (neighbor_list.hpp:101-159) and latch the answer:
  * a host request (new positions), a list radius that no longer covers dcut, or a bead that has
  * moved further than (radius - dcut)/2 from its build position */
-__global__ void k_rebuild_begin(DControl *ctl, const DParams *params)
+/* `gate`: inside a step graph (bd_engine.cu) the nine kernels of the chain sit in a conditional node that this
+ * kernel opens only when a rebuild is due -- a step that keeps its list launches nothing but this kernel and
+ * the step kernel.  Outside a graph (use_gate = 0) the chain kernels are launched anyway and return at once. */
+__global__ void k_rebuild_begin(DControl *ctl, const DParams *params, cudaGraphConditionalHandle gate, uint32_t use_gate)
 {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     uint32_t need = ctl->need_rebuild;
@@ -78,8 +81,10 @@ __global__ void k_rebuild_begin(DControl *ctl, const DParams *params)
     }
     ctl->doing_rebuild = need;
     ctl->need_rebuild = 0;
+    if (use_gate) cudaGraphSetConditional(gate, need);
     if (need) {
         ctl->rebuilds += 1;
+        ctl->graph_rebuilds += use_gate;
         ctl->listed_entries = 0;
         ctl->max_row = 0;
         ctl->max_stage = 0;

@@ -121,3 +121,49 @@ extern "C" int bd_nsearch_pairs(int32_t box_kind, const double period[3], int64_
     bd_destroy(h);
     return rc;
 }
+
+/* The same pair set in the ORDER md::neighbor_searcher<Box>::search emits it (MD/misc/neighbor_searcher.hpp:54-100):
+ * buckets in index order; for each, its sorted directed neighbours (open box: neighbour >= centre,
+ * search_grid.hpp:279-283; periodic: adjacent <= centre, :124-127); members of the neighbour bucket in the
+ * outer loop, members of the centre bucket in the inner loop, both in insertion (= index) order.  So a pair
+ * sorts by (centre bucket, neighbour bucket, index of the bead in the neighbour bucket, index of the bead in
+ * the centre bucket); within one bucket the larger index is the outer member.  3-sim-1kb's glue simulator
+ * feeds a sequential RNG in this order (glues/glue_simulator.cpp:66-80), so a relinked driver takes the same
+ * stochastic decisions only if the order is the reference's.  Pairs come out as (min, max). */
+extern "C" int bd_nsearch_pairs_ordered(int32_t box_kind, const double period[3], int64_t particle_count, double dcut,
+                                        const double *xyz, int64_t n, uint32_t *pairs_out, int64_t cap,
+                                        int64_t *count_out, int32_t device)
+{
+    if (bd_nsearch_pairs(box_kind, period, particle_count, dcut, xyz, n, pairs_out, cap, count_out, device)) return 1;
+    int64_t const m = *count_out;
+    if (m > cap || m == 0) return 0;  // the caller retries with a larger buffer
+    std::vector<uint32_t> bucket((size_t) n);
+    if (bd_nsearch_buckets(box_kind, period, particle_count, dcut, xyz, n, bucket.data(), device)) return 1;
+    struct Key { uint32_t centre, other, outer, inner; };
+    std::vector<Key> keys((size_t) m);
+    for (int64_t k = 0; k < m; k++) {
+        uint32_t const p = pairs_out[2 * k], q = pairs_out[2 * k + 1];
+        uint32_t const lo = p < q ? p : q, hi = p < q ? q : p;
+        uint32_t const bl = bucket[lo], bh = bucket[hi];
+        Key key;
+        if (bl == bh) {
+            key = {bl, bl, hi, lo};
+        } else {
+            bool const lo_is_centre = box_kind == BD_BOX_OPEN ? bl < bh : bl > bh;
+            key = lo_is_centre ? Key{bl, bh, hi, lo} : Key{bh, bl, lo, hi};
+        }
+        keys[(size_t) k] = key;
+    }
+    std::sort(keys.begin(), keys.end(), [](const Key &a, const Key &b) {
+        if (a.centre != b.centre) return a.centre < b.centre;
+        if (a.other != b.other) return a.other < b.other;
+        if (a.outer != b.outer) return a.outer < b.outer;
+        return a.inner < b.inner;
+    });
+    for (int64_t k = 0; k < m; k++) {
+        Key const &key = keys[(size_t) k];
+        pairs_out[2 * k] = key.outer < key.inner ? key.outer : key.inner;
+        pairs_out[2 * k + 1] = key.outer < key.inner ? key.inner : key.outer;
+    }
+    return 0;
+}

@@ -1124,19 +1124,37 @@ __global__ void k_gather_indexed(const bead4 *pos, const uint32_t *slot_of, cons
     xyz[3 * (size_t) i + 2] = b.z;
 }
 
-/* xyz[count][3] -> positions (and shadows) of a list of original indices: the ghosts a slab receives */
-__global__ void k_scatter_indexed(bead4 *pos, float4 *shadow, const uint32_t *slot_of, const uint32_t *idx,
-                                  const double *xyz, uint32_t count, const DParams *params, const DControl *ctl)
+/* xyz[count][3] -> positions (and shadows) of a list of original indices: the ghosts a slab receives.
+ * Like every other writer of positions it folds the displacement from the bead's position at the last list
+ * build into the control block, so that k_rebuild_begin sees a ghost that left its skin BEFORE the next
+ * force evaluation (neighbor_list.hpp:132-158 looks at all points, whoever moved them). */
+__global__ void k_scatter_indexed(bead4 *pos, float4 *shadow, const bead4 *bpos, const uint32_t *slot_of,
+                                  const uint32_t *idx, const double *xyz, uint32_t count, const DParams *params,
+                                  DControl *ctl)
 {
     uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= count) return;
-    uint32_t const s = slot_of[idx[i]];
-    double const x = xyz[3 * (size_t) i], y = xyz[3 * (size_t) i + 1], z = xyz[3 * (size_t) i + 2];
-    pos[s].x = x;
-    pos[s].y = y;
-    pos[s].z = z;
-    shadow[s] = params->box_kind == BD_BOX_PERIODIC ? make_shadow<BD_BOX_PERIODIC>(*params, ctl->grid, x, y, z, s)
-                                                    : make_shadow<BD_BOX_OPEN>(*params, ctl->grid, x, y, z, s);
+    double moved2 = 0.0;
+    if (i < count) {
+        uint32_t const s = slot_of[idx[i]];
+        double const x = xyz[3 * (size_t) i], y = xyz[3 * (size_t) i + 1], z = xyz[3 * (size_t) i + 2];
+        pos[s].x = x;
+        pos[s].y = y;
+        pos[s].z = z;
+        bead4 const b0 = bpos[s];
+        d3 d;
+        if (params->box_kind == BD_BOX_PERIODIC) {
+            shadow[s] = make_shadow<BD_BOX_PERIODIC>(*params, ctl->grid, x, y, z, s);
+            d = displacement_t<BD_BOX_PERIODIC>(*params, x, y, z, b0.x, b0.y, b0.z);
+        } else {
+            shadow[s] = make_shadow<BD_BOX_OPEN>(*params, ctl->grid, x, y, z, s);
+            d = displacement_t<BD_BOX_OPEN>(*params, x, y, z, b0.x, b0.y, b0.z);
+        }
+        moved2 = sqnorm_exact(d.x, d.y, d.z);
+        if (!(moved2 == moved2)) moved2 = __longlong_as_double(0x7ff0000000000000ll);  // NaN: force a rebuild
+    }
+    for (int o = 16; o > 0; o >>= 1) moved2 = fmax(moved2, __shfl_xor_sync(0xffffffffu, moved2, o));
+    if ((threadIdx.x & 31) == 0 && moved2 > 0.0)
+        atomicMax(&ctl->max_disp2_bits, (unsigned long long) __double_as_longlong(moved2));
 }
 
 /* (re)write the packed word of every bead: original index, class, target masks */

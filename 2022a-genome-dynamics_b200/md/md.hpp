@@ -1784,8 +1784,16 @@ namespace md
 
     // ---- md::neighbor_searcher<Box> (MD/misc/neighbor_searcher.hpp:23-131) ------------------------
     //
-    // Every unordered pair (i < j) within dcut, found on the device.  The pairs are emitted in
-    // ascending (i, j) order (the reference emits them in bucket order; callers accumulate sets).
+    // Every unordered pair (i < j) within dcut, found on the device and emitted in the reference's order
+    // (bucket by bucket: bd_nsearch_pairs_ordered), so that a caller which feeds a sequential generator in
+    // search order -- 3-sim-1kb's glue simulator -- takes the decisions it takes with micromd.
+    namespace b200
+    {
+        extern "C" int bd_nsearch_pairs_ordered(std::int32_t box_kind, const double period[3], std::int64_t particle_count,
+                                                double dcut, const double* xyz, std::int64_t n, std::uint32_t* pairs_out,
+                                                std::int64_t cap, std::int64_t* count_out, std::int32_t device);
+    }
+
     template<typename Box>
     class neighbor_searcher
     {
@@ -1804,19 +1812,14 @@ namespace md
             std::vector<std::uint32_t> pairs;
             for (;;) {
                 pairs.resize(std::size_t(cap) * 2);
-                b200::check(MD_B200_CALL(nsearch_pairs)(b200::box_kind(box_), period, std::int64_t(b200::box_count(box_)), dcut_,
-                                                        &points_.data()->x, std::int64_t(points_.size()), pairs.data(), cap,
-                                                        &count, 0), "nsearch_pairs");
+                b200::check(b200::bd_nsearch_pairs_ordered(b200::box_kind(box_), period, std::int64_t(b200::box_count(box_)), dcut_,
+                                                           &points_.data()->x, std::int64_t(points_.size()), pairs.data(), cap,
+                                                           &count, 0), "nsearch_pairs_ordered");
                 if (count <= cap) break;
                 cap = count;
             }
-            std::vector<std::pair<md::index, md::index>> sorted(static_cast<std::size_t>(count));
-            for (std::int64_t k = 0; k < count; k++) {
-                md::index const i = pairs[2 * k], j = pairs[2 * k + 1];
-                sorted[std::size_t(k)] = {std::min(i, j), std::max(i, j)};
-            }
-            std::sort(sorted.begin(), sorted.end());
-            for (auto const& p : sorted) *out++ = p;
+            for (std::int64_t k = 0; k < count; k++)
+                *out++ = std::pair<md::index, md::index>{pairs[2 * k], pairs[2 * k + 1]};
         }
 
         // Indices of the points closer than dcut to `point` (strict, as MD/misc/neighbor_searcher.hpp:104-131).

@@ -42,6 +42,15 @@ int bd_sync(bd_engine *h);
 int bd_set_option(bd_engine *h, const char *name, double value);
 int bd_get_option(bd_engine *h, const char *name, double *value);
 
+/* md::neighbor_searcher<Box>::search with the reference's EMISSION ORDER (MD/misc/neighbor_searcher.hpp:54-100:
+ * bucket by bucket, directed neighbours ascending, neighbour-bucket member outer, centre-bucket member inner),
+ * pairs as (min, max): the pair set of bd_nsearch_pairs found on the device, ordered on the host by the
+ * device-computed bucket ids.  Callers that feed a sequential generator in search order (3-sim-1kb's
+ * glue_simulator.cpp:66-80) then take the reference's decisions.  Same arguments as bd_nsearch_pairs. */
+int bd_nsearch_pairs_ordered(int32_t box_kind, const double period[3], int64_t particle_count, double dcut,
+                             const double *xyz, int64_t n, uint32_t *pairs_out, int64_t cap, int64_t *count_out,
+                             int32_t device);
+
 /* ---- per-replica walls (the real 100kb interphase model in an ensemble) ---------------------------
  * The interphase driver moves the wall semiaxes of its system after every step from that system's own
  * wall reaction (5-sim-genome/src/simulation_interphase/simulation_driver_interphase.cc:70-80:

@@ -81,3 +81,33 @@ def test_engine_shards_reproduce_the_unsharded_ensemble(engine):
     stats = whole.statistics()
     assert stats.shape == (n_global, len(scen.chains)) and np.isfinite(stats).all() and (stats > 0).all()
     whole.close()
+
+
+@pytest.mark.gpu
+def test_host_pipeline_equals_the_single_engine_ensemble(engine):
+    """ensemble.HostPipeline (replica chunks on their own streams, upload -> step -> download per chunk) advances
+    every replica as one engine holding all of them does: same noise keys (global replica ids), the same
+    positions after steps driven through the host buffer (to rounding: the chunks have their own cell grids,
+    so forces are summed in a different order)."""
+    import torch
+
+    import ensemble as en
+
+    R, steps = 6, 8
+    scen = sc.genome_10mb(total=320, replicas=R, bend_energy=0.7)
+    host = torch.empty((R, scen.n, 3), dtype=torch.float64).pin_memory()
+    host.numpy()[:] = scen.positions
+    pipe = en.HostPipeline(engine, scen, R, chunks=4, seed=5)
+    for _ in range(steps):
+        pipe.step_through_host(host, host, scen.timestep, scen.temperature)
+    got = host.numpy().copy()
+    pipe.close()
+
+    one = bd.System(engine, scen.n, R)
+    scen.apply(one)
+    for k in range(steps):  # the same per-step host round trip, one engine
+        one.step(1, scen.timestep, scen.temperature, seed=5, first_step=k + 1)
+    want = np.stack([one.get_positions(r) for r in range(R)])
+    one.close()
+    assert np.abs(got - want).max() <= 1e-12
+    assert np.abs(got - scen.positions).max() > 1e-4

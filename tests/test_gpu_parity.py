@@ -572,3 +572,44 @@ def test_pair_search_and_distances_on_resident_positions(engine, oracle):
     with pytest.raises(bd.BackendError):
         e.pair_distances(np.array([[0, s.n]], np.uint32))
     e.close()
+
+
+# ---- tile staging (engine option "staged") ----------------------------------------------------------
+
+@pytest.mark.parametrize("name", ["genome_100kb", "chromatin_1kb", "ab_sphere"])
+def test_staged_pair_walk_gives_the_same_forces_and_trajectory(engine, oracle, name):
+    """bd_set_option("staged", 1): Verlet rows of 16-bit positions inside the tile's staged neighbourhood,
+    shadows copied to shared memory by bulk asynchronous copies (bd_device.cuh: tile staging).  Same listed
+    set, same exact evaluation: forces, energy, exported list and a replayed trajectory equal the oracle's,
+    for an open-box, a periodic and a wall-confined model.  (Measured slower than the global gathers on
+    B200 -- profiles/README.md -- so it is off by default; this keeps the path honest.)"""
+    scen = SMALL[name]()
+    se, _ = build(engine, scen)
+    se.set_option("staged", 1)
+    so, _ = build(oracle, scen)
+    assert se.get_option("staged") == 1
+    assert rel_force_error(se.compute_forces(), so.compute_forces()) <= FORCE_TOL
+    assert se.compute_energy() == pytest.approx(so.compute_energy(), rel=ENERGY_TOL)
+    assert np.array_equal(sort_pairs(se.get_neighbor_list()), sort_pairs(so.get_neighbor_list()))
+    steps = 30
+    z = oracle.normals(17, steps * scen.n * 3)
+    se.step(steps, scen.timestep, scen.temperature, replay_normals=z)
+    so.step(steps, scen.timestep, scen.temperature, replay_normals=z)
+    assert se.get_option("staged") == 1 and se.get_option("max_stage") > 0
+    assert np.abs(se.get_positions() - so.get_positions()).max() <= TRAJ_TOL
+    # a capacity below the largest tile: those tiles translate through the run table instead
+    se.set_option("stage_capacity", 64)
+    assert rel_force_error(se.compute_forces(), so.compute_forces()) <= FORCE_TOL
+
+
+@pytest.mark.parametrize("kind,period", [(bd.BOX_OPEN, None), (bd.BOX_PERIODIC, (0.9, 1.0, 1.1)),
+                                         (bd.BOX_PERIODIC, (0.5, 2.0, 0.31))])
+@pytest.mark.parametrize("n", [2, 100, 1000, 5000])
+def test_ordered_pair_search_is_the_reference_emission_order(engine, oracle, kind, period, n):
+    """bd_nsearch_pairs_ordered: not only the reference's pair SET but its ORDER (bucket by bucket, directed
+    neighbours ascending, neighbour-bucket member outer) -- the oracle's search emits in the reference's order
+    bit for bit (tests/test_oracle_vs_reference.py::test_buckets_and_pairs_bit_exact), so array equality."""
+    x = sc.random_points(n, seed=n + 3)
+    got = engine.nsearch_pairs(kind, period, n, 0.3, x, ordered=True)
+    want = oracle.nsearch_pairs(kind, period, n, 0.3, x)
+    assert np.array_equal(got, want)

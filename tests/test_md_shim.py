@@ -83,6 +83,10 @@ def oracle_forwarders(tmp_path):
                          for n in names)
         lines.append(f"{ret}orc_{name}({orc_args});")
         lines.append(f"{ret}bd_{name}({bd_args}) {{ return orc_{name}({call}); }}")
+    # engine-only entry point the header uses: the search in the reference's emission order -- which is the
+    # order the oracle's own search emits in
+    lines.append("int bd_nsearch_pairs_ordered(int32_t k, const double p[3], int64_t c, double d, const double *x, int64_t n, "
+                 "uint32_t *o, int64_t cap, int64_t *cnt, int32_t dev) { return orc_nsearch_pairs(k, p, c, d, x, n, o, cap, cnt, dev); }")
     path = str(tmp_path / "bd_on_oracle.c")
     open(path, "w").write("\n".join(lines) + "\n")
     obj = str(tmp_path / "bd_on_oracle.o")
