@@ -174,6 +174,9 @@ ENGINE_ONLY = {
     "set_all_positions": [C.c_void_p, C.c_void_p],
     "nsearch_pairs_ordered": [C.c_int32, _dbl_p, C.c_int64, C.c_double, _dbl_p, C.c_int64, _u32_p, C.c_int64, _P(C.c_int64),
                               C.c_int32],
+    "glue_update": [C.c_void_p, C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_int64, C.c_uint64, C.c_int64,
+                    C.c_int32, _P(C.c_int64), _P(C.c_int64), _P(C.c_int64)],
+    "get_bond_pairs": [C.c_void_p, C.c_int32, _u32_p, C.c_int64, _P(C.c_int64)],
     "get_all_positions": [C.c_void_p, C.c_void_p],
     "get_all_positions_async": [C.c_void_p, C.c_void_p],
     "set_owned": [C.c_void_p, _u8_p],
@@ -559,6 +562,20 @@ class System:
     def set_all_positions(self, host_ptr: int):
         """host buffer [replicas][n][3] doubles (address), e.g. a pinned torch tensor's data_ptr()"""
         self.b.call("set_all_positions", self.h, C.c_void_p(host_ptr))
+
+    def glue_update(self, bond_ff, max_distance, p_bind, p_unbind, max_glues, seed, update_index, use_box=True):
+        """kinetic glue update on the device (bd_cuda.h: bd_glue_update); returns (unbound, bound, glued)"""
+        a, b, c = C.c_int64(0), C.c_int64(0), C.c_int64(0)
+        self.b.call("glue_update", self.h, bond_ff, 0, float(max_distance), float(p_bind), float(p_unbind), int(max_glues),
+                    int(seed), int(update_index), 1 if use_box else 0, C.byref(a), C.byref(b), C.byref(c))
+        return a.value, b.value, c.value
+
+    def get_bond_pairs(self, bond_ff) -> np.ndarray:
+        n = C.c_int64(0)
+        self.b.call("get_bond_pairs", self.h, bond_ff, None, 0, C.byref(n))
+        out = np.zeros((max(n.value, 1), 2), dtype=np.uint32)
+        self.b.call("get_bond_pairs", self.h, bond_ff, out.ctypes.data_as(_u32_p), n.value, C.byref(n))
+        return out[: n.value]
 
     def get_all_positions(self, host_ptr: int):
         self.b.call("get_all_positions", self.h, C.c_void_p(host_ptr))

@@ -2395,3 +2395,193 @@ extern "C" int bd_pair_distances(bd_engine *h, int32_t replica, const uint32_t *
     if (e != cudaSuccess) return fail(std::string("bd_pair_distances: ") + cudaGetErrorString(e));
     return 0;
 }
+
+// ---- kinetic glue update on the device (second half) ----------------------------------
+//
+// Replaces glue_simulator::update of the 1kb chromatin driver (3-sim-1kb/src/simulation/glues/
+// glue_simulator.cpp:35-80), which at every update downloads all positions, searches them on the host and
+// walks the pairs through one sequential generator:
+//   unbond: a glued pair comes apart if its box distance exceeds max_distance or with probability p_unbind;
+//   bond:   every pair within max_distance that is not glued passes with probability p_bind; the passing pairs
+//           fill the free capacity (max_glues - glued), a uniformly random subset of them if they are too many
+//           (reservoir sampling, glues/reservoir_sampler.hpp:57-93).
+// Here the glue list is a bonded pair list of the engine (bd_set_bond_pairs); the update runs on the resident
+// positions: distances and Bernoulli draws per glued pair, the candidate search of bd_search_pairs, a binary
+// search against the sorted survivors, Bernoulli draws per free candidate, and -- when the accepted ones
+// exceed the capacity -- a radix sort by a random 64-bit tag whose first `capacity` entries are a uniform
+// subset.  Only the new list (<= max_glues pairs) goes to the host, which rebuilds the bond adjacency.
+// The draws are counter-based (Philox keyed by seed, update index and the pair), not the reference's
+// sequential stream in search order: the update is the same stochastic process, not the same sample path --
+// tests/test_gpu_glue.py holds its rates and the glue-count distribution against the reference algorithm.
+
+__device__ inline void pair_uniforms(unsigned long long seed, unsigned long long update, uint32_t i, uint32_t j, uint32_t stream,
+                                     double &u, unsigned long long &tag)
+{
+    uint32_t c[4] = {i, j, (uint32_t) update, ((uint32_t) (update >> 32) << 8) | stream};
+    philox4x32_10(c, (uint32_t) seed, (uint32_t) (seed >> 32));
+    u = ((double) c[0] * 4294967296.0 + (double) c[1] + 0.5) * 5.421010862427522e-20;  // 2^-64: uniform in (0, 1)
+    tag = ((unsigned long long) c[2] << 32) | c[3];
+}
+
+__global__ void k_glue_unbond(const bead4 *pos, const uint32_t *slot_of, uint32_t base, const uint32_t *pairs, uint32_t m,
+                              const DParams *params, int use_box, double max_distance, double p_unbind,
+                              unsigned long long seed, unsigned long long update, unsigned long long *keys, uint8_t *keep)
+{
+    uint32_t const k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= m) return;
+    uint32_t const a = pairs[2 * k], b = pairs[2 * k + 1];
+    uint32_t const i = a < b ? a : b, j = a < b ? b : a;
+    bead4 const p = pos[slot_of[base + i]], q = pos[slot_of[base + j]];
+    d3 r = {__dsub_rn(p.x, q.x), __dsub_rn(p.y, q.y), __dsub_rn(p.z, q.z)};
+    if (use_box) r = displacement(*params, p.x, p.y, p.z, q.x, q.y, q.z);
+    double const dist = sqrt(sqnorm_exact(r.x, r.y, r.z));
+    double u;
+    unsigned long long tag;
+    pair_uniforms(seed, update, i, j, 0u, u, tag);
+    keys[k] = ((unsigned long long) i << 32) | j;
+    keep[k] = !(dist > max_distance || u < p_unbind);  // glue_simulator.cpp:57
+}
+
+__global__ void k_glue_candidates(const uint32_t *cand, unsigned long long found, const unsigned long long *glued,
+                                  unsigned long long nglued, double p_bind, unsigned long long seed, unsigned long long update,
+                                  unsigned long long *keys, unsigned long long *tags, uint8_t *accept)
+{
+    unsigned long long const k = (unsigned long long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= found) return;
+    uint32_t const a = cand[2 * k], b = cand[2 * k + 1];
+    uint32_t const i = a < b ? a : b, j = a < b ? b : a;
+    unsigned long long const key = ((unsigned long long) i << 32) | j;
+    unsigned long long lo = 0, hi = nglued;  // is the pair glued already? (glue_simulator.cpp:74)
+    while (lo < hi) {
+        unsigned long long const mid = (lo + hi) >> 1;
+        if (glued[mid] < key) lo = mid + 1; else hi = mid;
+    }
+    bool const already = lo < nglued && glued[lo] == key;
+    double u;
+    unsigned long long tag;
+    pair_uniforms(seed, update, i, j, 1u, u, tag);
+    keys[k] = key;
+    tags[k] = tag;
+    accept[k] = !already && u < p_bind;
+}
+
+extern "C" int bd_glue_update(bd_engine *h, int32_t bond_ff, int32_t replica, double max_distance, double p_bind,
+                              double p_unbind, int64_t max_glues, uint64_t seed, int64_t update_index, int32_t use_box,
+                              int64_t *unbound_out, int64_t *bound_out, int64_t *count_out)
+{
+    NEED(h);
+    if (bond_ff < 0 || bond_ff >= BD_MAX_BOND_FF || !h->bond[bond_ff].used) return fail("bd_glue_update: bad forcefield id");
+    if (replica < 0 || (uint32_t) replica >= h->replicas) return fail("bd_glue_update: bad replica");
+    if (h->replicas != 1) return fail("bd_glue_update: the pair lists of an ensemble are shared; one replica per engine");
+    if (!(max_distance > 0) || !(p_bind >= 0 && p_bind <= 1) || !(p_unbind >= 0 && p_unbind <= 1) || max_glues < 0)
+        return fail("bd_glue_update: bad parameters");
+    if (upload_params(h)) return 1;
+    cudaStream_t const st = h->stream;
+    std::vector<uint32_t> &list = h->bond_pairs[bond_ff];
+    size_t const m = list.size() / 2;
+
+    // ---- unbond ----------------------------------------------------------------------------------
+    DevBuf<uint32_t> d_pairs;
+    DevBuf<unsigned long long> keys, kept, sorted, d_count;
+    DevBuf<uint8_t> flags;
+    CK(d_count.alloc(1));
+    unsigned long long nkept = 0;
+    size_t need = 0;
+    if (m) {
+        CK(d_pairs.alloc(2 * m));
+        CK(keys.alloc(m));
+        CK(kept.alloc(m));
+        CK(sorted.alloc(m));
+        CK(flags.alloc(m));
+        CK(cudaMemcpyAsync(d_pairs.p, list.data(), 2 * m * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+        k_glue_unbond<<<blocks_for(m, 256), 256, 0, st>>>(h->pos[h->cur].p, h->slot_of.p, (uint32_t) replica * h->n, d_pairs.p,
+                                                         (uint32_t) m, h->d_params.p, use_box != 0, max_distance, p_unbind, seed,
+                                                         (unsigned long long) update_index, keys.p, flags.p);
+        CK(cub::DeviceSelect::Flagged(nullptr, need, keys.p, flags.p, kept.p, d_count.p, (int) m, st));
+        if (h->contact_temp.count < need) CK(h->contact_temp.alloc(need + need / 4));
+        size_t bytes = h->contact_temp.count;
+        CK(cub::DeviceSelect::Flagged(h->contact_temp.p, bytes, keys.p, flags.p, kept.p, d_count.p, (int) m, st));
+        CK(cudaMemcpyAsync(&nkept, d_count.p, sizeof nkept, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        if (nkept) {
+            CK(cub::DeviceRadixSort::SortKeys(nullptr, need, kept.p, sorted.p, (int) nkept, 0, 64, st));
+            if (h->contact_temp.count < need) CK(h->contact_temp.alloc(need + need / 4));
+            bytes = h->contact_temp.count;
+            CK(cub::DeviceRadixSort::SortKeys(h->contact_temp.p, bytes, kept.p, sorted.p, (int) nkept, 0, 64, st));
+        }
+        h->launches += 3;
+    }
+    if (unbound_out) *unbound_out = (int64_t) (m - nkept);
+
+    // ---- bond ------------------------------------------------------------------------------------
+    unsigned long long found = 0, naccepted = 0;
+    size_t const capacity = (size_t) max_glues > nkept ? (size_t) max_glues - (size_t) nkept : 0;
+    DevBuf<unsigned long long> ckeys, ctags, akeys, atags, skeys, stags;
+    DevBuf<uint8_t> accept;
+    if (capacity && p_bind > 0) {
+        if (search_current(h, replica, max_distance, use_box != 0, &found)) return 1;
+    }
+    if (found) {
+        CK(ckeys.alloc(found));
+        CK(ctags.alloc(found));
+        CK(akeys.alloc(found));
+        CK(atags.alloc(found));
+        CK(accept.alloc(found));
+        k_glue_candidates<<<(unsigned) ((found + 255) / 256), 256, 0, st>>>(h->contact_pairs.p, found, sorted.p, nkept, p_bind, seed,
+                                                                          (unsigned long long) update_index, ckeys.p, ctags.p,
+                                                                          accept.p);
+        size_t bytes = 0;
+        CK(cub::DeviceSelect::Flagged(nullptr, need, ckeys.p, accept.p, akeys.p, d_count.p, (int) found, st));
+        if (h->contact_temp.count < need) CK(h->contact_temp.alloc(need + need / 4));
+        bytes = h->contact_temp.count;
+        CK(cub::DeviceSelect::Flagged(h->contact_temp.p, bytes, ckeys.p, accept.p, akeys.p, d_count.p, (int) found, st));
+        bytes = h->contact_temp.count;
+        CK(cub::DeviceSelect::Flagged(h->contact_temp.p, bytes, ctags.p, accept.p, atags.p, d_count.p, (int) found, st));
+        CK(cudaMemcpyAsync(&naccepted, d_count.p, sizeof naccepted, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        h->launches += 3;
+    }
+    size_t const nbound = std::min<size_t>((size_t) naccepted, capacity);
+    const unsigned long long *chosen = akeys.p;
+    if (naccepted > capacity) {
+        // too many: the `capacity` entries with the smallest random tags are a uniformly random subset
+        CK(skeys.alloc(naccepted));
+        CK(stags.alloc(naccepted));
+        CK(cub::DeviceRadixSort::SortPairs(nullptr, need, atags.p, stags.p, akeys.p, skeys.p, (int) naccepted, 0, 64, st));
+        if (h->contact_temp.count < need) CK(h->contact_temp.alloc(need + need / 4));
+        size_t bytes = h->contact_temp.count;
+        CK(cub::DeviceRadixSort::SortPairs(h->contact_temp.p, bytes, atags.p, stags.p, akeys.p, skeys.p, (int) naccepted, 0, 64, st));
+        chosen = skeys.p;
+        h->launches += 1;
+    }
+    if (bound_out) *bound_out = (int64_t) nbound;
+
+    // ---- the new list: survivors (sorted) then the newly bound pairs -----------------------------------
+    std::vector<unsigned long long> out(nkept + nbound);
+    if (nkept) CK(cudaMemcpyAsync(out.data(), sorted.p, nkept * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    if (nbound) CK(cudaMemcpyAsync(out.data() + nkept, chosen, nbound * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    for (auto *b : {&keys, &kept, &sorted, &d_count, &ckeys, &ctags, &akeys, &atags, &skeys, &stags}) b->release();
+    d_pairs.release();
+    flags.release();
+    accept.release();
+    list.resize(2 * out.size());
+    for (size_t k = 0; k < out.size(); k++) {
+        list[2 * k] = (uint32_t) (out[k] >> 32);
+        list[2 * k + 1] = (uint32_t) out[k];
+    }
+    if (count_out) *count_out = (int64_t) out.size();
+    return upload_topology(h);
+}
+
+extern "C" int bd_get_bond_pairs(bd_engine *h, int32_t bond_ff, uint32_t *pairs_out, int64_t cap, int64_t *count_out)
+{
+    NEED(h);
+    if (bond_ff < 0 || bond_ff >= BD_MAX_BOND_FF || !h->bond[bond_ff].used) return fail("bd_get_bond_pairs: bad forcefield id");
+    const std::vector<uint32_t> &list = h->bond_pairs[bond_ff];
+    int64_t const m = (int64_t) (list.size() / 2);
+    if (count_out) *count_out = m;
+    int64_t const take = std::min<int64_t>(m, std::max<int64_t>(cap, 0));
+    if (take > 0 && pairs_out) std::memcpy(pairs_out, list.data(), (size_t) take * 2 * sizeof(uint32_t));
+    return 0;
+}

@@ -1000,7 +1000,7 @@ struct WallRelax {
     double mobility;
 };
 
-constexpr int RELAX_LANES = 8;
+constexpr int RELAX_LANES = 32;  // threads per statistic: the chunk sums are a chain of dependent loads
 constexpr int RELAX_WIDTH = BD_MAX_WALL_FF * WALL_STATS;
 
 __global__ void __launch_bounds__(RELAX_WIDTH * RELAX_LANES)

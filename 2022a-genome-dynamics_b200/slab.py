@@ -198,6 +198,16 @@ class SlabSystem:
         for t in self.recv_index.values():
             self.accurate[t.long()] = True
         self.store.set_owned(self.owned)
+        # the per-step exchange as ONE gather, ONE collective and ONE scatter (DistExchange.halo): everything
+        # this rank sends, concatenated by peer, and everything it receives, with the row counts per peer
+        world = self.layout.world
+        empty = torch.zeros(0, dtype=torch.int32, device=self.device)
+        self.send_cat = torch.cat([self.send_index.get(p, empty) for p in range(world)]).contiguous()
+        self.recv_cat = torch.cat([self.recv_index.get(p, empty) for p in range(world)]).contiguous()
+        self.send_rows = [len(self.send_index.get(p, empty)) for p in range(world)]
+        self.recv_rows = [len(self.recv_index.get(p, empty)) for p in range(world)]
+        self.send_buf = torch.empty((len(self.send_cat), 3), dtype=torch.float64, device=self.device)
+        self.recv_buf = torch.empty((len(self.recv_cat), 3), dtype=torch.float64, device=self.device)
 
     # -- halo --------------------------------------------------------------------------------------
     def halo_pack(self) -> Dict[int, torch.Tensor]:
@@ -296,6 +306,23 @@ class DistExchange:
         self._p2p(send, recv)
         return recv
 
+    def halo(self, slab: "SlabSystem"):
+        """The per-step ghost refresh.  On NCCL: one indexed gather of everything this rank sends (engine kernel),
+        one all-to-all with per-peer row counts, one indexed scatter into the ghosts (engine kernel) -- three
+        enqueues on the work stream whatever the number of peers, no host wait.  Other backends (gloo in the CPU
+        tests has no all-to-all) keep the point-to-point form."""
+        if self.dist.get_backend() != "nccl" or not hasattr(slab.store, "system"):
+            slab.halo_unpack(self.positions(slab.halo_pack(), slab.recv_index))
+            return
+        system = slab.store.system
+        if len(slab.send_cat):
+            system.gather_positions_indexed(slab.send_cat.data_ptr(), len(slab.send_cat), slab.send_buf.data_ptr())
+        self.dist.all_to_all_single(slab.recv_buf, slab.send_buf, output_split_sizes=slab.recv_rows,
+                                    input_split_sizes=slab.send_rows)
+        if len(slab.recv_cat):
+            system.scatter_positions_indexed(slab.recv_cat.data_ptr(), len(slab.recv_cat), slab.recv_buf.data_ptr())
+        slab.halo_bytes_sent += slab.send_buf.numel() * 8
+
 
 def run_distributed(slab: SlabSystem, exchange: DistExchange, steps: int, timestep: float, temperature: float, seed: int):
     """One rank of the decomposed run; every rank calls this with the same arguments."""
@@ -306,9 +333,9 @@ def run_distributed(slab: SlabSystem, exchange: DistExchange, steps: int, timest
             exchange.dist.all_reduce(owned)
             if int(owned.item()) != slab.n:
                 raise RuntimeError(f"slab: {int(owned.item())} of {slab.n} beads are owned after a migration")
-            slab.halo_unpack(exchange.positions(slab.halo_pack(), slab.recv_index))
+            exchange.halo(slab)
         slab.advance(timestep, temperature, seed)
-        slab.halo_unpack(exchange.positions(slab.halo_pack(), slab.recv_index))
+        exchange.halo(slab)
 
 
 def gather_owned(slab: SlabSystem, exchange: Optional[DistExchange] = None) -> np.ndarray:

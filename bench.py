@@ -51,6 +51,8 @@ def parse():
     ap.add_argument("--frozen-walls", action="store_true",
                     help="genome100kb: keep the wall semiaxes fixed (round-1 workload) instead of the driver's per-step feedback")
     ap.add_argument("--verlet-factor", type=float, default=None, help="list radius / dcut (engine option; reference 1.5)")
+    ap.add_argument("--step-graph", type=int, default=None, help="engine option step_graph (0: launch kernel by kernel, "
+                    "e.g. under ncu)")
     ap.add_argument("--staged", type=int, default=None, help="engine option staged (tile staging of the pair walk) after the relaxation")
     ap.add_argument("--stage-capacity", type=int, default=None, help="engine option stage_capacity")
     ap.add_argument("--workload", default="genome100kb", choices=sorted(WORKLOADS) + ["slab1kb"],
@@ -60,6 +62,8 @@ def parse():
     ap.add_argument("--chains", type=int, default=600, help="chromatin1kb / slab1kb: chains")
     ap.add_argument("--chain-len", type=int, default=10000, help="chromatin1kb / slab1kb: beads per chain")
     ap.add_argument("--migrate-every", type=int, default=40, help="slab1kb: steps between ownership migrations")
+    ap.add_argument("--no-slab", action="store_true", help="N > 1: skip the attached slab1kb pass")
+    ap.add_argument("--slab-steps", type=int, default=40, help="N > 1: steps of the attached slab1kb pass")
     return ap.parse_args()
 
 
@@ -313,6 +317,33 @@ def run_reference(args):
 
 # ---- B200 arm ------------------------------------------------------------------------------------
 
+def bind_near_gpu(torch, local):
+    """Pin this rank to the CPUs of the NUMA node its GPU hangs off (sysfs local_cpulist of the PCI device), so
+    that the rank's pinned host buffers are first-touched there and its copies do not cross the socket
+    interconnect.  Best effort: returns what was found."""
+    out = {"bound": False}
+    try:
+        p = torch.cuda.get_device_properties(local)
+        bus = f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        base = f"/sys/bus/pci/devices/{bus}"
+        out["pci"] = bus
+        out["numa_node"] = int(open(f"{base}/numa_node").read())
+        cpus = open(f"{base}/local_cpulist").read().strip()
+        out["local_cpulist"] = cpus
+        ids = set()
+        for part in cpus.split(","):
+            a, _, b = part.partition("-")
+            ids.update(range(int(a), int(b or a) + 1))
+        allowed = os.sched_getaffinity(0)
+        use = ids & allowed
+        if use and use != allowed:
+            os.sched_setaffinity(0, use)
+            out["bound"] = True
+    except Exception as e:  # sysfs not exposed (containers): keep the inherited affinity
+        out["note"] = f"{type(e).__name__}: {e}"
+    return out
+
+
 def parity_check(eng, sysm, scen, R, ids):
     """Replica 0 and replica R-1 of the state about to be timed against the reference's own code (the
     unmodified micromd where oracle/_ref was built, else the CPU restatement): per-bead forces, and the
@@ -360,6 +391,7 @@ def run_b200(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the engine has no CPU fallback")
     torch.cuda.set_device(local)
+    numa = bind_near_gpu(torch, local)  # before any pinned allocation: first touch then lands on the GPU's node
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
@@ -381,6 +413,8 @@ def run_b200(args):
         sysm.set_wall_relaxation(ids["wall"], feedback["spring"], feedback["mobility"])
     if args.verlet_factor:
         sysm.set_option("verlet_factor", args.verlet_factor)
+    if args.step_graph is not None:
+        sysm.set_option("step_graph", args.step_graph)
     stream = torch.cuda.Stream()
     sysm.set_stream(stream.cuda_stream)
     host = torch.empty((R, n, 3), dtype=torch.float64).pin_memory()
@@ -478,6 +512,16 @@ def run_b200(args):
     else:
         e2e_ms_max = t[1].item()
 
+    slab_line = None
+    if world > 1 and args.workload == "genome100kb" and not args.no_slab:
+        # the one workload with a data-path collective, so that the scaling record carries it too: a short pass of
+        # the slab-decomposed 1kb chromatin system on the same ranks (strong scaling; its own N = 1 figure is in
+        # profiles/)
+        import copy
+        sargs = copy.copy(args)
+        sargs.steps, sargs.warmup, sargs.relax = args.slab_steps, 3, 200
+        slab_line = run_slab(sargs, embedded=True)
+
     if rank == 0:
         peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
         if os.path.exists(peaks_path):
@@ -502,7 +546,8 @@ def run_b200(args):
                                          else "none"),
                        "l2": "working set %.2f GB per GPU > 126 MB L2 (no flush needed)" % (ntot * 32 * 3 / 1e9 + ntot * 4 * 8 / 1e9),
                        "relax_steps": args.relax, "list_rebuilds_in_timed_region": rebuilds,
-                       "parallelism": f"replica shards, {world} GPU(s), no data-path collective"},
+                       "parallelism": f"replica shards, {world} GPU(s), no data-path collective",
+                       "host_binding_rank0": numa},
             "pair_interactions_per_s": inter / (ms * 1e-3),
             "pair_interactions_per_step": inter / args.steps,
             "gpu_launches": int(launches),
@@ -515,6 +560,11 @@ def run_b200(args):
         }
         if parity:
             line["parity_check"] = parity
+        if slab_line:
+            line["slab1kb"] = {k: slab_line[k] for k in ("value", "unit", "ms_per_step", "scaling", "steps", "halo_bytes_per_step",
+                                                          "pair_interactions_per_s", "gpu_launches")}
+            line["slab1kb"]["workload"] = slab_line["config"]["workload"]
+            line["slab1kb"]["parallelism"] = slab_line["config"]["parallelism"]
         if semi_now:
             line["config"]["wall_semiaxes_replica0_after_timed_region"] = semi_now
         if e2e:
@@ -547,10 +597,12 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
-def run_slab(args):
+def run_slab(args, embedded=False):
     """One large periodic 1kb chromatin system, slab-decomposed over the ranks (slab.py).  A step is one
     BD step of the whole system: fused force+integrate on every rank's owned beads, then the halo
-    exchange (NCCL send/recv).  Migrations (every --migrate-every steps) are inside the timed region."""
+    exchange (NCCL send/recv).  Migrations (every --migrate-every steps) are inside the timed region.
+    embedded: called from the replica-ensemble run at N > 1 (the process group exists); returns the line
+    (rank 0) instead of printing it, so that the scaling record carries the decomposed workload too."""
     import torch
     import torch.distributed as dist
 
@@ -565,7 +617,7 @@ def run_slab(args):
         raise SystemExit("bench.py: no CUDA device; the engine has no CPU fallback")
     torch.cuda.set_device(local)
     dev = f"cuda:{local}"
-    if world > 1:
+    if world > 1 and not embedded:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     eng = bd.load_engine()
     scen = sc.chromatin_1kb(args.chains, args.chain_len)
@@ -646,10 +698,12 @@ def run_slab(args):
             "pair_interactions_per_s": inter / (ms * 1e-3), "gpu_launches": int(launches),
             "halo_bytes_per_step": halo_bytes / K, "clocks": clocks,
         }
-        print(json.dumps(line), flush=True)
+        if not embedded:
+            print(json.dumps(line), flush=True)
     sysm.close()
-    if world > 1:
+    if world > 1 and not embedded:
         dist.destroy_process_group()
+    return line if rank == 0 else None
 
 
 def main():

@@ -111,6 +111,23 @@ int bd_search_pairs(bd_engine *h, int32_t replica, double distance, int32_t use_
                     int64_t *count_out);
 int bd_pair_distances(bd_engine *h, int32_t replica, const uint32_t *pairs, int64_t m, int32_t min_image, double *out);
 
+/* ---- kinetic glue update on the device --------------------------------------------
+ * Replaces glue_simulator::update of the 1kb chromatin driver (3-sim-1kb/src/simulation/glues/
+ * glue_simulator.cpp:35-80) for a glue list held as the pair list of bond forcefield `bond_ff`
+ * (bd_add_bond_ff / bd_set_bond_pairs + bd_set_bond_min_image): glued pairs farther apart than max_distance
+ * (box distance when use_box) or hit by a Bernoulli(p_unbind) draw come apart; every pair within max_distance
+ * that is not glued passes a Bernoulli(p_bind) draw, and the passing pairs fill the free capacity
+ * max_glues - glued, a uniformly random subset if they are too many (the reference's reservoir sampling).
+ * p_bind / p_unbind are the driver's -expm1(-rate * timestep).  Everything runs on the resident positions;
+ * only the new list crosses to the host.  Draws are Philox keyed by (seed, update_index, pair): the same
+ * stochastic process as the reference, not its sample path (the reference consumes one sequential generator in
+ * search order).  Outputs (each may be NULL): pairs unbound, pairs bound, length of the new list. */
+int bd_glue_update(bd_engine *h, int32_t bond_ff, int32_t replica, double max_distance, double p_bind, double p_unbind,
+                   int64_t max_glues, uint64_t seed, int64_t update_index, int32_t use_box, int64_t *unbound_out,
+                   int64_t *bound_out, int64_t *count_out);
+/* the current pair list of a bond forcefield: up to `cap` pairs to pairs_out [cap][2], the total to *count_out */
+int bd_get_bond_pairs(bd_engine *h, int32_t bond_ff, uint32_t *pairs_out, int64_t cap, int64_t *count_out);
+
 /* ---- single-precision snapshots -------------------------------------------------
  * The drivers' stores write float positions: 5-sim-genome quantises to 16 fraction bits on the host,
  * quantize(val, bits) = nearbyint(float(val) * 2^bits) / 2^bits in float arithmetic
