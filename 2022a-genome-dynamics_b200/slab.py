@@ -326,14 +326,34 @@ class DistExchange:
 
 def run_distributed(slab: SlabSystem, exchange: DistExchange, steps: int, timestep: float, temperature: float, seed: int):
     """One rank of the decomposed run; every rank calls this with the same arguments."""
+    import os
+    import time
+    prof = os.environ.get("SLAB_PROFILE") and slab.device.type == "cuda"
+
+    def lap(t0, tag):
+        if not prof:
+            return t0
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        if slab.rank == 0:
+            print(f"slab migration {tag}: {1e3 * (t1 - t0):.2f} ms", flush=True)
+        return t1
+
     for _ in range(steps):
         if slab.steps_done % slab.migrate_every == 0:
-            slab.migrate_commit(exchange.indices(slab.migrate_plan()))
+            t = lap(time.perf_counter(), "start") if prof else 0.0
+            plan = slab.migrate_plan()
+            t = lap(t, "plan")
+            recv = exchange.indices(plan)
+            t = lap(t, "index exchange")
+            slab.migrate_commit(recv)
+            t = lap(t, "commit")
             owned = slab.owned.sum().to(torch.int64).reshape(1)
             exchange.dist.all_reduce(owned)
             if int(owned.item()) != slab.n:
                 raise RuntimeError(f"slab: {int(owned.item())} of {slab.n} beads are owned after a migration")
             exchange.halo(slab)
+            t = lap(t, "check + halo")
         slab.advance(timestep, temperature, seed)
         exchange.halo(slab)
 
