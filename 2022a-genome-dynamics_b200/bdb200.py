@@ -172,6 +172,8 @@ ENGINE_ONLY = {
     "set_wall_relaxation": [C.c_void_p, _P(C.c_int32), C.c_int32, _dbl_p, C.c_double],
     "noise_statistics": [C.c_uint64, C.c_int64, C.c_int64, C.c_int64, C.c_int32, C.c_int32, _dbl_p, C.c_int32],
     "set_all_positions": [C.c_void_p, C.c_void_p],
+    "nsearch_query": [C.c_int32, _dbl_p, C.c_double, _dbl_p, C.c_int64, _dbl_p, C.c_int64, _P(C.c_int64), _u32_p, C.c_int64,
+                      C.c_int32],
     "nsearch_pairs_ordered": [C.c_int32, _dbl_p, C.c_int64, C.c_double, _dbl_p, C.c_int64, _u32_p, C.c_int64, _P(C.c_int64),
                               C.c_int32],
     "glue_update": [C.c_void_p, C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_int64, C.c_uint64, C.c_int64,
@@ -182,6 +184,7 @@ ENGINE_ONLY = {
     "set_owned": [C.c_void_p, _u8_p],
     "set_owned_device": [C.c_void_p, C.c_void_p],
     "gather_positions_indexed": [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p],
+    "displacement_pointer": [C.c_void_p, _P(C.c_void_p)],
     "scatter_positions_indexed": [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p],
     "contact_update": [C.c_void_p, C.c_int32, C.c_double],
     "contact_accumulate": [C.c_void_p, C.c_int32, C.POINTER(C.c_uint32), C.c_int64, C.POINTER(C.c_int64)],
@@ -275,6 +278,19 @@ class Backend:
         out = np.empty(xyz.shape, dtype=np.float32)
         self.call("quantize_positions", _dp(xyz), len(xyz), int(fraction_bits), out.ctypes.data_as(_P(C.c_float)))
         return out
+
+    def nsearch_query(self, box_kind, period, dcut, xyz, queries, device=0):
+        """md::neighbor_searcher::query for a batch of points: (start[m + 1], index[total]) (bd_cuda.h)"""
+        xyz = np.ascontiguousarray(xyz, dtype=np.float64).reshape(-1, 3)
+        q = np.ascontiguousarray(queries, dtype=np.float64).reshape(-1, 3)
+        period = np.ascontiguousarray(period if period is not None else [1, 1, 1], dtype=np.float64)
+        start = np.zeros(len(q) + 1, dtype=np.int64)
+        self.call("nsearch_query", box_kind, _dp(period), float(dcut), _dp(xyz), len(xyz), _dp(q), len(q),
+                  start.ctypes.data_as(_P(C.c_int64)), None, 0, device)
+        index = np.zeros(max(int(start[-1]), 1), dtype=np.uint32)
+        self.call("nsearch_query", box_kind, _dp(period), float(dcut), _dp(xyz), len(xyz), _dp(q), len(q),
+                  start.ctypes.data_as(_P(C.c_int64)), index.ctypes.data_as(_u32_p), int(start[-1]), device)
+        return start, index[: int(start[-1])]
 
     def noise_statistics(self, seed, first_step, steps, beads, replica=0, device=0) -> dict:
         """moments, tail counts and correlations of the step kernel's production noise (bd_cuda.h)"""
@@ -583,6 +599,12 @@ class System:
     def get_all_positions_async(self, host_ptr: int):
         """enqueue the download into a pinned buffer; complete after sync()"""
         self.b.call("get_all_positions_async", self.h, C.c_void_p(host_ptr))
+
+    def displacement_pointer(self) -> int:
+        """device address of the running max displacement^2 (bits of a double); see bd_cuda.h"""
+        p = C.c_void_p()
+        self.b.call("displacement_pointer", self.h, C.byref(p))
+        return p.value
 
     def set_owned(self, owned):
         """slab decomposition: 0/1 per bead, None = every bead is advanced by this engine"""

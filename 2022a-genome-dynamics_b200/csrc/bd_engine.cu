@@ -799,6 +799,18 @@ extern "C" int bd_set_owned_device(bd_engine *h, const uint8_t *d_owned)
     return request_rebuild(h);  // ghosts carry no Verlet row
 }
 
+/* Device address of the running maximum of |x - x(list build)|^2 over the beads this engine has seen move
+ * (an IEEE double's bits; non-negative, so integer max = floating max).  Slabs of one system all-reduce it
+ * (max) after every step, so that every rank takes the rebuild decision the undecomposed system takes -- any
+ * bead anywhere beyond the skin -- and they rebuild at the same step instead of stalling each other's exchange. */
+extern "C" int bd_displacement_pointer(bd_engine *h, void **d_out)
+{
+    NEED(h);
+    if (!d_out) return fail("bd_displacement_pointer: null output");
+    *d_out = &h->ctl.p->max_disp2_bits;
+    return 0;
+}
+
 extern "C" int bd_gather_positions_indexed(bd_engine *h, const uint32_t *d_index, int64_t count, double *d_xyz)
 {
     NEED(h);
@@ -1230,9 +1242,12 @@ static void allow_big_smem(K kernel)
 
 static void opt_in_shared_memory()
 {
-    static bool done = false;  // per process; attributes are per device function
-    if (done) return;
-    done = true;
+    // function attributes belong to the current device: once per device of this process
+    static unsigned long long done = 0;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 64 && ((done >> dev) & 1ull)) return;
+    if (dev < 64) done |= 1ull << dev;
     allow_big_smem(k_step_fused<BD_BOX_OPEN, PROG_GENERIC>);
     allow_big_smem(k_step_fused<BD_BOX_OPEN, PROG_SC23_SC83>);
     allow_big_smem(k_step_fused<BD_BOX_OPEN, PROG_SC23>);

@@ -167,3 +167,103 @@ extern "C" int bd_nsearch_pairs_ordered(int32_t box_kind, const double period[3]
     }
     return 0;
 }
+
+// ---- md::neighbor_searcher<Box>::query, batched -------------------------------------------------------
+//
+// The reference answers one point at a time from its bucket grid (MD/misc/neighbor_searcher.hpp:65-70,104-131:
+// every stored point with shortest_displacement(point, query).squared_norm() < dcut^2, strict).  Its one caller,
+// the hetero-RDF tool (4-sim-ab/box/src/rdf_analysis_hetero/distance_histogram.cc:52), asks for every particle in
+// turn; here the whole batch is one call: a warp per query scans the points 32 at a time (coalesced) and a
+// ballot keeps the hits of a query in ascending index order.  Two passes (count, fill) around one scan.
+
+struct QueryBox { int32_t periodic; double period[3], inv_period[3]; };
+
+template <bool FILL>
+__global__ void k_query(QueryBox box, double dcut2, const double *xyz, uint32_t n, const double *queries, uint32_t m,
+                        uint32_t *count, const unsigned long long *start, uint32_t *out, unsigned long long cap)
+{
+    uint32_t const q = (blockIdx.x * blockDim.x + threadIdx.x) / 32, lane = threadIdx.x & 31;
+    if (q >= m) return;
+    double const qx = queries[3 * (size_t) q], qy = queries[3 * (size_t) q + 1], qz = queries[3 * (size_t) q + 2];
+    unsigned long long at = FILL ? start[q] : 0;
+    uint32_t found = 0;
+    for (uint32_t base = 0; base < n; base += 32) {
+        uint32_t const i = base + lane;
+        bool hit = false;
+        if (i < n) {
+            double dx = __dsub_rn(xyz[3 * (size_t) i], qx), dy = __dsub_rn(xyz[3 * (size_t) i + 1], qy),
+                   dz = __dsub_rn(xyz[3 * (size_t) i + 2], qz);
+            if (box.periodic) {
+                dx = round_mod_exact(dx, box.period[0], box.inv_period[0]);
+                dy = round_mod_exact(dy, box.period[1], box.inv_period[1]);
+                dz = round_mod_exact(dz, box.period[2], box.inv_period[2]);
+            }
+            hit = sqnorm_exact(dx, dy, dz) < dcut2;
+        }
+        uint32_t const mask = __ballot_sync(0xffffffffu, hit);
+        if (FILL && hit) {
+            unsigned long long const slot = at + found + __popc(mask & ((1u << lane) - 1u));
+            if (slot < cap) out[slot] = i;
+        }
+        found += __popc(mask);
+    }
+    if (!FILL && lane == 0) count[q] = found;
+}
+
+extern "C" int bd_nsearch_query(int32_t box_kind, const double period[3], double dcut, const double *xyz, int64_t n,
+                                const double *queries, int64_t m, int64_t *start_out, uint32_t *index_out, int64_t cap,
+                                int32_t device)
+{
+    if (n < 0 || m < 0 || !(dcut > 0) || !start_out) return bd_internal_fail("bd_nsearch_query: bad arguments");
+    if (box_kind != BD_BOX_OPEN && box_kind != BD_BOX_PERIODIC) return bd_internal_fail("bd_nsearch_query: unknown box kind");
+    if (n >= (1ll << 32) || m >= (1ll << 27)) return bd_internal_fail("bd_nsearch_query: too many points");
+    for (int64_t q = 0; q <= m; q++) start_out[q] = 0;
+    if (m == 0 || n == 0) return 0;
+    if (cudaSetDevice(device) != cudaSuccess) return bd_internal_fail("bd_nsearch_query: no such CUDA device");
+    QueryBox box;
+    std::memset(&box, 0, sizeof box);
+    box.periodic = box_kind == BD_BOX_PERIODIC;
+    for (int d = 0; d < 3; d++) {
+        box.period[d] = box.periodic ? period[d] : 1.0;
+        box.inv_period[d] = 1 / box.period[d];
+    }
+    double *d_xyz = nullptr, *d_q = nullptr;
+    uint32_t *d_count = nullptr, *d_out = nullptr;
+    unsigned long long *d_start = nullptr;
+    std::vector<uint32_t> counts((size_t) m);
+    std::vector<unsigned long long> starts((size_t) m + 1, 0ull);
+    unsigned const blocks = (unsigned) ((m * 32 + 255) / 256);
+    cudaError_t e = cudaMalloc((void **) &d_xyz, 3 * (size_t) n * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc((void **) &d_q, 3 * (size_t) m * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc((void **) &d_count, (size_t) m * sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaMalloc((void **) &d_start, ((size_t) m + 1) * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMemcpy(d_xyz, xyz, 3 * (size_t) n * sizeof(double), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_q, queries, 3 * (size_t) m * sizeof(double), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        k_query<false><<<blocks, 256>>>(box, dcut * dcut, d_xyz, (uint32_t) n, d_q, (uint32_t) m, d_count, nullptr, nullptr, 0);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(counts.data(), d_count, (size_t) m * sizeof(uint32_t), cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) {
+        for (int64_t q = 0; q < m; q++) starts[(size_t) q + 1] = starts[(size_t) q] + counts[(size_t) q];
+        for (int64_t q = 0; q <= m; q++) start_out[q] = (int64_t) starts[(size_t) q];
+        unsigned long long const total = starts[(size_t) m];
+        unsigned long long const take = std::min<unsigned long long>(total, (unsigned long long) std::max<int64_t>(cap, 0));
+        if (take && index_out) {
+            e = cudaMalloc((void **) &d_out, (size_t) take * sizeof(uint32_t));
+            if (e == cudaSuccess) e = cudaMemcpy(d_start, starts.data(), ((size_t) m + 1) * sizeof(unsigned long long), cudaMemcpyHostToDevice);
+            if (e == cudaSuccess) {
+                k_query<true><<<blocks, 256>>>(box, dcut * dcut, d_xyz, (uint32_t) n, d_q, (uint32_t) m, d_count, d_start, d_out, take);
+                e = cudaGetLastError();
+            }
+            if (e == cudaSuccess) e = cudaMemcpy(index_out, d_out, (size_t) take * sizeof(uint32_t), cudaMemcpyDeviceToHost);
+        }
+    }
+    cudaFree(d_xyz);
+    cudaFree(d_q);
+    cudaFree(d_count);
+    cudaFree(d_start);
+    cudaFree(d_out);
+    if (e != cudaSuccess) return bd_internal_fail((std::string("bd_nsearch_query: ") + cudaGetErrorString(e)).c_str());
+    return 0;
+}

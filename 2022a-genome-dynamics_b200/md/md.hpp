@@ -1789,6 +1789,9 @@ namespace md
     // search order -- 3-sim-1kb's glue simulator -- takes the decisions it takes with micromd.
     namespace b200
     {
+        extern "C" int bd_nsearch_query(std::int32_t box_kind, const double period[3], double dcut, const double* xyz,
+                                        std::int64_t n, const double* queries, std::int64_t m, std::int64_t* start_out,
+                                        std::uint32_t* index_out, std::int64_t cap, std::int32_t device);
         extern "C" int bd_nsearch_pairs_ordered(std::int32_t box_kind, const double period[3], std::int64_t particle_count,
                                                 double dcut, const double* xyz, std::int64_t n, std::uint32_t* pairs_out,
                                                 std::int64_t cap, std::int64_t* count_out, std::int32_t device);
@@ -1833,6 +1836,27 @@ namespace md
             double const dcut2 = dcut_ * dcut_;
             for (md::index i = 0; i < points_.size(); i++)
                 if (box_.shortest_displacement(points_[i], point).squared_norm() < dcut2) *out++ = i;
+        }
+
+        // extension over micromd: query() for many points in one device call; result[q] = indices (ascending) of
+        // the stored points closer than dcut to queries[q]
+        std::vector<std::vector<md::index>> b200_query_all(md::array_view<md::point const> queries) const
+        {
+            std::vector<std::vector<md::index>> result(queries.size());
+            if (queries.size() == 0 || points_.empty()) return result;
+            double period[3];
+            b200::box_period(box_, period);
+            std::vector<std::int64_t> start(queries.size() + 1);
+            b200::check(b200::bd_nsearch_query(b200::box_kind(box_), period, dcut_, &points_.data()->x, std::int64_t(points_.size()),
+                                               &queries.begin()->x, std::int64_t(queries.size()), start.data(), nullptr, 0, 0),
+                        "nsearch_query");
+            std::vector<std::uint32_t> index(std::size_t(std::max<std::int64_t>(start.back(), 1)));
+            b200::check(b200::bd_nsearch_query(b200::box_kind(box_), period, dcut_, &points_.data()->x, std::int64_t(points_.size()),
+                                               &queries.begin()->x, std::int64_t(queries.size()), start.data(), index.data(),
+                                               start.back(), 0), "nsearch_query");
+            for (std::size_t q = 0; q < result.size(); q++)
+                result[q].assign(index.begin() + start[q], index.begin() + start[q + 1]);
+            return result;
         }
 
     private:

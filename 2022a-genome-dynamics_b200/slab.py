@@ -322,6 +322,22 @@ class DistExchange:
         if len(slab.recv_cat):
             system.scatter_positions_indexed(slab.recv_cat.data_ptr(), len(slab.recv_cat), slab.recv_buf.data_ptr())
         slab.halo_bytes_sent += slab.send_buf.numel() * 8
+        # one list-rebuild decision for the whole system, as in the undecomposed run: the largest displacement since
+        # the last build over ALL ranks.  Without it every rank rebuilds on its own schedule and each rebuild (O(N))
+        # stalls everybody's next exchange.
+        if not hasattr(slab, "_moved"):
+            slab._moved = _device_int64(system.displacement_pointer(), self.device)
+        self.dist.all_reduce(slab._moved, op=self.dist.ReduceOp.MAX)
+
+
+class _DevicePointer:
+    def __init__(self, ptr: int):
+        self.__cuda_array_interface__ = {"shape": (1,), "typestr": "<i8", "data": (int(ptr), False), "version": 2}
+
+
+def _device_int64(ptr: int, device) -> torch.Tensor:
+    """a one-element int64 tensor aliasing engine memory at `ptr`"""
+    return torch.as_tensor(_DevicePointer(ptr), device=device)
 
 
 def run_distributed(slab: SlabSystem, exchange: DistExchange, steps: int, timestep: float, temperature: float, seed: int):

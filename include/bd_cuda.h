@@ -51,6 +51,14 @@ int bd_nsearch_pairs_ordered(int32_t box_kind, const double period[3], int64_t p
                              const double *xyz, int64_t n, uint32_t *pairs_out, int64_t cap, int64_t *count_out,
                              int32_t device);
 
+/* md::neighbor_searcher<Box>::query (MD/misc/neighbor_searcher.hpp:65-70,104-131), batched: for query q the indices i
+ * of the points with shortest_displacement(x_i, query_q).squared_norm() < dcut^2 (strict, fp64), ascending, at
+ * index_out[start_out[q] .. start_out[q + 1]); start_out has m + 1 entries and is complete even when the total
+ * exceeds cap (call with cap = 0 to size index_out).  The reference's one caller asks for every particle of a
+ * frame in turn (4-sim-ab/box/src/rdf_analysis_hetero/distance_histogram.cc:52); here that is one call. */
+int bd_nsearch_query(int32_t box_kind, const double period[3], double dcut, const double *xyz, int64_t n,
+                     const double *queries, int64_t m, int64_t *start_out, uint32_t *index_out, int64_t cap, int32_t device);
+
 /* ---- per-replica walls (the real 100kb interphase model in an ensemble) ---------------------------
  * The interphase driver moves the wall semiaxes of its system after every step from that system's own
  * wall reaction (5-sim-genome/src/simulation_interphase/simulation_driver_interphase.cc:70-80:
@@ -82,6 +90,9 @@ int bd_set_owned(bd_engine *h, const uint8_t *owned);
 /* the same with a DEVICE mask, enqueued on the engine's stream (no host copy of the mask) */
 int bd_set_owned_device(bd_engine *h, const uint8_t *d_owned);
 int bd_gather_positions_indexed(bd_engine *h, const uint32_t *d_index, int64_t count, double *d_xyz);
+/* DEVICE address of the engine's running max of |x - x(list build)|^2 (the bits of a non-negative double, 8 bytes):
+ * slabs all-reduce it (integer max) after every step so that all ranks rebuild their lists at the same step */
+int bd_displacement_pointer(bd_engine *h, void **d_out);
 int bd_scatter_positions_indexed(bd_engine *h, const uint32_t *d_index, int64_t count, const double *d_xyz);
 
 /* ---- contact map accumulated on the device -------------------------------------

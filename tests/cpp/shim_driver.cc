@@ -18,6 +18,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <algorithm>
 #include <functional>
 #include <iterator>
@@ -586,6 +587,14 @@ namespace
             double sum = 0;
             for (md::index i : around) sum += double(i) * 31 + 1;
             std::printf("%s.query %zu %.17g\n", tag, around.size(), sum);
+#if defined(MD_B200_ENGINE) && !defined(SHIM_DRIVER_HOST_QUERIES)
+            // the batched device form answers every particle at once and must agree with the one-point query
+            auto const all = searcher.b200_query_all(system.view_positions());
+            if (all.size() != system.particle_count() || all[7] != around) {
+                std::printf("%s.query_all MISMATCH\n", tag);
+                std::abort();
+            }
+#endif
         }
     }
 }

@@ -613,3 +613,23 @@ def test_ordered_pair_search_is_the_reference_emission_order(engine, oracle, kin
     got = engine.nsearch_pairs(kind, period, n, 0.3, x, ordered=True)
     want = oracle.nsearch_pairs(kind, period, n, 0.3, x)
     assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("kind,period", [(bd.BOX_OPEN, None), (bd.BOX_PERIODIC, (0.9, 1.0, 1.1))])
+@pytest.mark.parametrize("n", [1, 33, 1000])
+def test_batched_query_is_the_brute_force_set(engine, kind, period, n):
+    """bd_nsearch_query = md::neighbor_searcher::query for every query point: strictly closer than dcut, with the
+    box's shortest displacement, ascending indices -- the brute-force expectation of the reference's own unit test
+    (micromd tests/misc/test_neighbor_searcher.cc), in the reference's fp64 arithmetic."""
+    x = sc.random_points(n, seed=n + 1)
+    queries = np.concatenate([x[: min(n, 40)], sc.random_points(25, seed=99)])
+    start, index = engine.nsearch_query(kind, period, 0.3, x, queries)
+    assert start[0] == 0 and start[-1] == len(index) and (np.diff(start) >= 0).all()
+    for q, point in enumerate(queries):
+        d = x - point
+        if period is not None:
+            L = np.asarray(period)
+            d = d - np.rint(d * (1 / L)) * L
+        r2 = d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1] + d[:, 2] * d[:, 2]
+        want = np.nonzero(r2 < 0.3 * 0.3)[0]
+        assert np.array_equal(index[start[q]:start[q + 1]], want), q
