@@ -95,6 +95,7 @@ struct bd_engine {
     DevBuf<uint4> nbr4;       // Verlet rows by thread position, ROW_PAD indices per group
     DevBuf<TileRuns> tile_runs;  // staged neighbourhood of every tile (bd_device.cuh: tile staging)
     bool staged = false;      // rows hold 16-bit staged positions (option "staged"); false = rows of slots, global gathers
+    bool balance_rows = false;  // tile threads ordered by row length (round 1) or in slot order (default)
     bool stage_auto = true;   // the block's staging capacity follows the largest tile (bd_set_option stage_capacity fixes it)
     uint32_t stage_cap = 512; // shadows a block of the step kernel stages
     DevBuf<uint2> bondrow;    // bonded partners by thread position, resolved to slots at every rebuild
@@ -1150,6 +1151,7 @@ static NlistArrays nlist_arrays(bd_engine *h)
     A.bond_deg = h->bond_deg;
     A.tile_runs = h->tile_runs.p;
     A.staged = h->staged;
+    A.balance = h->balance_rows;
     A.npad = h->npad;
     A.pstride = h->pstride;
     A.ctl = h->ctl.p;
@@ -1894,6 +1896,10 @@ extern "C" int bd_set_option(bd_engine *h, const char *name, double value)
         CK(cudaMemset(&h->ctl.p->stage_overflow, 0, sizeof(uint32_t)));
         return request_rebuild(h);
     }
+    if (key == "balance_rows") {
+        h->balance_rows = value != 0;
+        return request_rebuild(h);
+    }
     if (key == "stage_capacity") {  // 0 = follow the largest tile
         if (!(value >= 0 && value <= STAGE_CAP_CEILING)) return fail("bd_set_option: stage_capacity out of range");
         h->stage_auto = value == 0;
@@ -1936,6 +1942,7 @@ extern "C" int bd_get_option(bd_engine *h, const char *name, double *value)
     else if (key == "specialize") *value = h->specialize;
     else if (key == "staged") *value = h->staged;
     else if (key == "step_graph") *value = h->use_graph;
+    else if (key == "balance_rows") *value = h->balance_rows;
     else if (key == "stage_capacity") *value = h->stage_cap;
     else if (key == "max_stage") {
         CK(cudaStreamSynchronize(h->stream));

@@ -52,6 +52,7 @@ struct NlistArrays {
     uint32_t bond_deg;       // largest number of bonds on one bead
     TileRuns *tile_runs;     // [replicas * chunks] staged neighbourhood of every tile (bd_device.cuh), or null
     uint32_t staged;         // rows hold 16-bit staged positions (uint2 groups) instead of slots (uint4 groups)
+    uint32_t balance;        // k_balance ranks the beads of a tile by row length (option "balance_rows")
     uint32_t npad, pstride;
     DControl *ctl;
     const DParams *params;
@@ -904,10 +905,16 @@ __global__ void __launch_bounds__(BAL_TILE) k_balance(NlistArrays A)
         if (threadIdx.x == 0) longest = 0;
         len[threadIdx.x] = mine;
         __syncthreads();
-        uint32_t rnk = 0;
-        for (uint32_t t = 0; t < BAL_TILE; t++) {
-            uint32_t const other = len[t];
-            rnk += (other < mine) || (other == mine && t < threadIdx.x);
+        // A.balance = 0 (default since round 2): threads keep slot order, rows stay where k_rows wrote them.  With
+        // the pair walk bound by L1 gathers instead of issue slots, lanes that end together buy nothing
+        // (measured: 0.718 vs 0.721 ms per launch), and the row move below was 0.35 ms of every rebuild.
+        uint32_t rnk = threadIdx.x;
+        if (A.balance) {
+            rnk = 0;
+            for (uint32_t t = 0; t < BAL_TILE; t++) {
+                uint32_t const other = len[t];
+                rnk += (other < mine) || (other == mine && t < threadIdx.x);
+            }
         }
         src[rnk] = (uint8_t) threadIdx.x;
         if (live) {
@@ -921,7 +928,9 @@ __global__ void __launch_bounds__(BAL_TILE) k_balance(NlistArrays A)
         // (only the groups the row has: what lies beyond a row's padded length is never read)
         uint32_t const groups = (longest + ROW_PAD - 1) / ROW_PAD;
         uint32_t const mine_groups = owner ? (len[from] + ROW_PAD - 1) / ROW_PAD : 0u;
-        if (A.staged) {
+        if (!A.balance) {
+            // identity: nothing to move
+        } else if (A.staged) {
             uint2 *rows = reinterpret_cast<uint2 *>(A.nbr4);  // groups of four 16-bit staged positions
             for (uint32_t g = 0; g < groups; g++) {
                 uint2 v = make_uint2(0u, 0u);

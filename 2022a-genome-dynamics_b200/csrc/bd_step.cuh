@@ -99,6 +99,35 @@ __device__ __forceinline__ bead4 load_bead(const bead4 *p)
     return b;
 }
 
+#ifndef STEP_STREAM_LOADS
+__device__ __forceinline__ bead4 stream_bead(const bead4 *p) { return load_bead(p); }
+#endif
+
+/* read-once streams (Verlet rows, bond rows, build positions): keep them out of the L1, which the gathers need */
+#ifdef STEP_STREAM_LOADS
+__device__ __forceinline__ uint4 stream_u4(const uint4 *p)
+{
+    uint4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ uint2 stream_u2(const uint2 *p)
+{
+    uint2 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ bead4 stream_bead(const bead4 *p)
+{
+    bead4 b;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.b64 {%0, %1, %2, %3}, [%4];" : "=d"(b.x), "=d"(b.y), "=d"(b.z), "=l"(b.w) : "l"(p));
+    return b;
+}
+#else
+__device__ __forceinline__ uint4 stream_u4(const uint4 *p) { return *p; }
+__device__ __forceinline__ uint2 stream_u2(const uint2 *p) { return *p; }
+#endif
+
 __device__ __forceinline__ void store_bead(bead4 *p, double x, double y, double z, uint64_t w)
 {
     asm volatile("st.global.v4.b64 [%0], {%1, %2, %3, %4};" :: "l"(p), "d"(x), "d"(y), "d"(z), "l"(w) : "memory");
@@ -279,10 +308,10 @@ __device__ __forceinline__ void pair_walk(const StepArrays &A, StepShared &sh, S
 
     auto fetch = [&](uint32_t out[ROW_PAD]) {
         if (MODE == WALK_GLOBAL) {
-            uint4 const g = *col;
+            uint4 const g = stream_u4(col);
             out[0] = g.x; out[1] = g.y; out[2] = g.z; out[3] = g.w;
         } else {
-            uint2 const g = *col2;
+            uint2 const g = stream_u2(col2);
             out[0] = g.x & 0xffffu; out[1] = g.x >> 16; out[2] = g.y & 0xffffu; out[3] = g.y >> 16;
         }
     };
@@ -421,7 +450,7 @@ __device__ __forceinline__ void bonded_forces(const StepArrays &A, const StepSha
         // software pipeline: the next bond's row entry and partner record are requested while this
         // bond is evaluated (the loop was bound by these two dependent loads)
         const uint2 *col = A.bondrow + pos;
-        uint2 adj_next = A.bond_deg ? *col : make_uint2(0xffffffffu, 0u);
+        uint2 adj_next = A.bond_deg ? stream_u2(col) : make_uint2(0xffffffffu, 0u);
         bead4 o_next = me;
         if (adj_next.x != 0xffffffffu) o_next = load_bead(A.pos + adj_next.x);
         for (uint32_t k = 0; k < A.bond_deg; k++) {
@@ -429,7 +458,7 @@ __device__ __forceinline__ void bonded_forces(const StepArrays &A, const StepSha
             if (adj.x == 0xffffffffu) break;
             bead4 const o = o_next;
             col += A.pstride;
-            adj_next = k + 1 < A.bond_deg ? *col : make_uint2(0xffffffffu, 0u);
+            adj_next = k + 1 < A.bond_deg ? stream_u2(col) : make_uint2(0xffffffffu, 0u);
             if (adj_next.x != 0xffffffffu) o_next = load_bead(A.pos + adj_next.x);
             uint32_t const f = (adj.y >> 12) & 7u;
             if (!((on_mask >> f) & 1u)) continue;
@@ -709,7 +738,7 @@ __device__ __forceinline__ double integrate_bead(const StepArrays &A, const DPar
     store_bead(A.pos_out + s, x, y, z2, me.w);
     A.shadow_out[s] = make_shadow<BOX>(P, G, x, y, z2, s);
 
-    bead4 const b0 = load_bead(A.bpos + s);
+    bead4 const b0 = stream_bead(A.bpos + s);
     d3 const d = displacement_t<BOX>(P, x, y, z2, b0.x, b0.y, b0.z);
     return sqnorm_exact(d.x, d.y, d.z);
 }
@@ -722,7 +751,7 @@ __device__ __forceinline__ double carry_ghost(const StepArrays &A, const DParams
 {
     store_bead(A.pos_out + s, me.x, me.y, me.z, me.w);
     A.shadow_out[s] = make_shadow<BOX>(P, G, me.x, me.y, me.z, s);
-    bead4 const b0 = load_bead(A.bpos + s);
+    bead4 const b0 = stream_bead(A.bpos + s);
     d3 const d = displacement_t<BOX>(P, me.x, me.y, me.z, b0.x, b0.y, b0.z);
     return sqnorm_exact(d.x, d.y, d.z);
 }

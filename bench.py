@@ -309,7 +309,8 @@ def run_reference(args):
                              f"after {relax} relaxation steps by the reference itself"},
         "cpu_baseline": {"value": value, "unit": "bead-steps/s", "cores": threads, "kind": kind, "build": flavour,
                          "sample": f"{threads} independent replicas x {inner * K} BD steps, micromd single-threaded per replica"
-                                   + (", per-step wall feedback through the C entry points" if feedback else "")},
+                                   + ((", per-step wall feedback " + ("as the simulate_brownian_dynamics callback" if flavour.startswith("driver")
+                                                                   else "through the C entry points")) if feedback else "")},
         "e2e": {"value": value, "unit": "bead-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }

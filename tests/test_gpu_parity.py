@@ -633,3 +633,21 @@ def test_batched_query_is_the_brute_force_set(engine, kind, period, n):
         r2 = d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1] + d[:, 2] * d[:, 2]
         want = np.nonzero(r2 < 0.3 * 0.3)[0]
         assert np.array_equal(index[start[q]:start[q + 1]], want), q
+
+
+def test_row_length_ranking_is_an_option_with_the_same_results(engine, oracle):
+    """bd_set_option("balance_rows", 1): the round-1 thread order (beads of a tile ranked by row length, rows
+    moved to their thread positions).  Default is slot order; both give the oracle's forces and trajectory."""
+    scen = SMALL["genome_100kb"]()
+    so, _ = build(oracle, scen)
+    fo = so.compute_forces()
+    z = oracle.normals(21, 20 * scen.n * 3)
+    so.step(20, scen.timestep, scen.temperature, replay_normals=z)
+    for flag in (0, 1):
+        se, _ = build(engine, scen)
+        se.set_option("balance_rows", flag)
+        assert se.get_option("balance_rows") == flag
+        assert rel_force_error(se.compute_forces(), fo) <= FORCE_TOL
+        se.step(20, scen.timestep, scen.temperature, replay_normals=z)
+        assert np.abs(se.get_positions() - so.get_positions()).max() <= TRAJ_TOL
+        se.close()
