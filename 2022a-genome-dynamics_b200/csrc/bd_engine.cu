@@ -99,6 +99,10 @@ struct bd_engine {
     bool stage_auto = true;   // the block's staging capacity follows the largest tile (bd_set_option stage_capacity fixes it)
     uint32_t stage_cap = 512; // shadows a block of the step kernel stages
     DevBuf<uint2> bondrow;    // bonded partners by thread position, resolved to slots at every rebuild
+    DevBuf<uint2> bend_pq;    // bending triples by thread position: slots of the other two beads,
+    DevBuf<double> bend_e;    // ... the triple's energy,
+    DevBuf<uint8_t> bend_meta;  // ... role and forcefield (bd_nlist.cuh: fill_bend_rows)
+    uint32_t bend_deg = 0;
     DevBuf<BondRow> d_bond_rows;
     uint32_t npad = 0, pstride = 0, bond_deg = 0;
     bool bond_rows_stale = false;  // bonded pair lists changed since the bond rows were written
@@ -459,6 +463,13 @@ static int upload_topology(bd_engine *h)
     fill.assign(start.begin(), start.end() - 1);
     for (size_t t = 0; t < ten.size(); t++)
         for (uint32_t role = 0; role < 3; role++) badj[fill[tri[3 * t + role]]++] = (uint32_t) (t << 2) | role;
+    uint32_t bdeg = 0;
+    for (uint32_t i = 0; i < n; i++) bdeg = std::max(bdeg, start[i + 1] - start[i]);
+    h->bend_deg = bdeg;
+    CK(h->bend_pq.ensure((size_t) bdeg * h->pstride));
+    CK(h->bend_e.ensure((size_t) bdeg * h->pstride));
+    CK(h->bend_meta.ensure((size_t) bdeg * h->pstride));
+    if (bdeg) CK(cudaMemset(h->bend_meta.p, 0, (size_t) bdeg * h->pstride));
     CK(h->bend_start.alloc(n + 1));
     CK(h->bend_adj.alloc(badj.size()));
     CK(h->triples.alloc(tri.size()));
@@ -607,6 +618,9 @@ extern "C" int bd_destroy(bd_engine *h)
     h->nbr4.release();
     h->tile_runs.release();
     h->bondrow.release();
+    h->bend_pq.release();
+    h->bend_e.release();
+    h->bend_meta.release();
     h->d_bond_rows.release();
     destroy_step_graph(h->graphs[0]);
     destroy_step_graph(h->graphs[1]);
@@ -1146,6 +1160,15 @@ static NlistArrays nlist_arrays(bd_engine *h)
     A.bond_start = h->bond_start.p;
     A.bond_adj = h->bond_adj.p;
     A.type = h->d_type.p;
+    A.bend_start = h->bend_start.p;
+    A.bend_adj = h->bend_adj.p;
+    A.triples = h->triples.p;
+    A.bend_energy = h->bend_energy.p;
+    A.bend_ff = h->bend_ff.p;
+    A.bend_pq = h->bend_pq.p;
+    A.bend_e = h->bend_e.p;
+    A.bend_meta = h->bend_meta.p;
+    A.bend_deg = h->bend_deg;
     for (int f = 0; f < BD_MAX_BOND_FF; f++) A.bond_slot[f] = h->bond_slot[f];
     A.ntypes = (uint32_t) h->hp.ntypes;
     A.bond_deg = h->bond_deg;
@@ -1193,6 +1216,10 @@ static StepArrays step_arrays(bd_engine *h)
     A.order = h->order.p;
     A.bond_start = h->bond_start.p;
     A.bond_adj = h->bond_adj.p;
+    A.bend_pq = h->bend_pq.p;
+    A.bend_e = h->bend_e.p;
+    A.bend_meta = h->bend_meta.p;
+    A.bend_deg = h->bend_deg;
     A.bend_start = h->bend_start.p;
     A.bend_adj = h->bend_adj.p;
     A.triples = h->triples.p;
@@ -1343,7 +1370,7 @@ static int enqueue_rebuild_chain(bd_engine *h)
     k_balance<<<std::min(h->chunks * h->replicas, 148u * 16u), BAL_TILE, 0, st>>>(A);
     h->launches += 11;
     if (h->bond_rows_stale) {
-        if (h->bond_deg) {
+        if (h->bond_deg || h->bend_deg) {
             k_bond_rows<<<std::min(h->chunks * h->replicas, 148u * 16u), BAL_TILE, 0, st>>>(A);
             h->launches += 1;
         }

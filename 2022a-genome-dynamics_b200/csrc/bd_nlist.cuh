@@ -47,6 +47,14 @@ struct NlistArrays {
     const uint32_t *bond_start;  // CSR of all bond forcefields by original index (bd_engine.cu: upload_topology)
     const uint2 *bond_adj;
     const uint8_t *type;     // [n] bead class by original index
+    // bending triples by original index (CSR) and, resolved to slots per thread position, the rows the step kernel reads
+    const uint32_t *bend_start, *bend_adj, *triples;
+    const double *bend_energy;
+    const uint8_t *bend_ff;
+    uint2 *bend_pq;
+    double *bend_e;
+    uint8_t *bend_meta;
+    uint32_t bend_deg;
     uint8_t bond_slot[BD_MAX_BOND_FF];  // bond forcefield -> block of the compiled bond table (bd_step.cuh: BondRow)
     uint32_t ntypes;
     uint32_t bond_deg;       // largest number of bonds on one bead
@@ -880,6 +888,26 @@ __device__ inline uint2 resolve_bond(const NlistArrays &A, uint32_t replica, uin
     return make_uint2(A.slot_of[replica * A.n + adj.x], (row & 0xfffu) | (f << 12) | (second << 15));
 }
 
+/* the bending triples of bead `oi`, for the thread at position P: slots of the other two beads (in triple order),
+ * energy, role of this bead; what the step kernel reads instead of walking the CSR */
+__device__ inline void fill_bend_rows(const NlistArrays &A, uint32_t replica, uint32_t oi, bool live, size_t P)
+{
+    uint32_t k = 0;
+    if (live) {
+        for (uint32_t c = A.bend_start[oi]; c < A.bend_start[oi + 1] && k < A.bend_deg; c++, k++) {
+            uint32_t const adj = A.bend_adj[c];
+            uint32_t const t = adj >> 2, role = adj & 3u;
+            uint32_t const i0 = A.triples[3 * t], i1 = A.triples[3 * t + 1], i2 = A.triples[3 * t + 2];
+            uint32_t const p = role == 0 ? i1 : i0, q = role == 2 ? i1 : i2;
+            size_t const at = (size_t) k * A.pstride + P;
+            A.bend_pq[at] = make_uint2(A.slot_of[replica * A.n + p], A.slot_of[replica * A.n + q]);
+            A.bend_e[at] = A.bend_energy[t];
+            A.bend_meta[at] = (uint8_t) (1u | (role << 1) | ((uint32_t) A.bend_ff[t] << 3));
+        }
+    }
+    for (; k < A.bend_deg; k++) A.bend_meta[(size_t) k * A.pstride + P] = 0;
+}
+
 /* Thread -> bead assignment of the step kernels.  Inside every tile of BAL_TILE consecutive slots
  * the beads are ranked by row length, so that the 32 rows a warp walks in lockstep end together (row
  * lengths inside one tile of a polymer melt differ by 4x; unranked, half of the lanes idle).  The
@@ -957,6 +985,8 @@ __global__ void __launch_bounds__(BAL_TILE) k_balance(NlistArrays A)
             for (; k < A.bond_deg; k++)
                 A.bondrow[(size_t) k * A.pstride + pbase + threadIdx.x] = make_uint2(0xffffffffu, 0u);
         }
+        if (A.bend_deg)
+            fill_bend_rows(A, replica, owner ? w_orig(A.bpos[base + from].w) : 0u, owner, (size_t) pbase + threadIdx.x);
     }
 }
 
@@ -979,6 +1009,9 @@ __global__ void __launch_bounds__(BAL_TILE) k_bond_rows(NlistArrays A)
                 A.bondrow[(size_t) k * A.pstride + pbase + threadIdx.x] = resolve_bond(A, replica, oi, A.bond_adj[c]);
         }
         for (; k < A.bond_deg; k++) A.bondrow[(size_t) k * A.pstride + pbase + threadIdx.x] = make_uint2(0xffffffffu, 0u);
+        if (A.bend_deg)
+            fill_bend_rows(A, replica, live ? w_orig(A.bpos[base + A.order[base + threadIdx.x]].w) : 0u, live,
+                           (size_t) pbase + threadIdx.x);
     }
 }
 

@@ -45,6 +45,10 @@ struct StepArrays {
     const uint8_t *order;         // [Ntot] thread -> bead offset within its 128-slot tile (bd_nlist.cuh: k_balance)
     const uint32_t *bond_start;   // [n+1] CSR by original index
     const uint2 *bond_adj;        // {partner original index, ff | second<<8}
+    const uint2 *bend_pq;         // [bend_deg][pstride] slots of the other two beads of the thread's k-th triple (i < j < k order)
+    const double *bend_e;         // [bend_deg][pstride] its bending energy
+    const uint8_t *bend_meta;     // [bend_deg][pstride] 1 | role << 1 | ff << 3, 0 = no more triples
+    uint32_t bend_deg;
     const uint32_t *bend_start;   // [n+1]
     const uint32_t *bend_adj;     // triple id << 2 | role
     const uint32_t *triples;      // [m][3] original indices
@@ -99,12 +103,12 @@ __device__ __forceinline__ bead4 load_bead(const bead4 *p)
     return b;
 }
 
-#ifndef STEP_STREAM_LOADS
+#ifdef STEP_NO_STREAM_LOADS
 __device__ __forceinline__ bead4 stream_bead(const bead4 *p) { return load_bead(p); }
 #endif
 
 /* read-once streams (Verlet rows, bond rows, build positions): keep them out of the L1, which the gathers need */
-#ifdef STEP_STREAM_LOADS
+#ifndef STEP_NO_STREAM_LOADS
 __device__ __forceinline__ uint4 stream_u4(const uint4 *p)
 {
     uint4 v;
@@ -493,18 +497,24 @@ __device__ __forceinline__ void bonded_forces(const StepArrays &A, const StepSha
     }
 
     // bending triples (cosine_bending_potential.hpp:43-60)
+    // The triples of the bead at this thread position were resolved to slots at the last rebuild (bd_nlist.cuh:
+    // fill_bend_rows): three coalesced row reads and two record gathers per triple, where walking the CSR by
+    // original index cost ten dependent gathers (adjacency, forcefield, energy, three indices, two slot lookups,
+    // two records) -- 40 % of the gathers of the 1kb chromatin model.
     if (A.any_bend) {
-        uint32_t const b = A.bend_start[oi], e = A.bend_start[oi + 1];
-        for (uint32_t k = b; k < e; k++) {
-            uint32_t const adj = A.bend_adj[k];
-            uint32_t const t = adj >> 2, role = adj & 3u;
-            int const f = A.bend_ff[t];
+        for (uint32_t k = 0; k < A.bend_deg; k++) {
+            size_t const at = (size_t) k * A.pstride + pos;
+            uint32_t const meta = A.bend_meta[at];
+            if (!(meta & 1u)) break;
+            uint32_t const role = (meta >> 1) & 3u;
+            int const f = (int) (meta >> 3);
             if (!ff_on(sel, BD_FF_BEND, f, P.bend[f].enabled)) continue;
-            double const E = A.bend_energy[t];
-            uint32_t const i0 = A.triples[3 * t], i1 = A.triples[3 * t + 1], i2 = A.triples[3 * t + 2];
-            bead4 const pi = role == 0 ? me : load_bead(A.pos + A.slot_of[base + i0]);
-            bead4 const pj = role == 1 ? me : load_bead(A.pos + A.slot_of[base + i1]);
-            bead4 const pk = role == 2 ? me : load_bead(A.pos + A.slot_of[base + i2]);
+            double const E = A.bend_e[at];
+            uint2 const pq = stream_u2(A.bend_pq + at);
+            bead4 const rp = load_bead(A.pos + pq.x), rq = load_bead(A.pos + pq.y);
+            bead4 const pi = role == 0 ? me : rp;
+            bead4 const pj = role == 1 ? me : (role == 0 ? rp : rq);
+            bead4 const pk = role == 2 ? me : rq;
             double const ax = pi.x - pj.x, ay = pi.y - pj.y, az = pi.z - pj.z;  // rij
             double const bx = pj.x - pk.x, by = pj.y - pk.y, bz = pj.z - pk.z;  // rjk
             double const dij = ax * ax + ay * ay + az * az, djk = bx * bx + by * by + bz * bz;
