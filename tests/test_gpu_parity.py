@@ -345,27 +345,44 @@ def test_empty_system(engine):
 
 def test_statistical_equivalence_with_reference_noise(engine, oracle):
     """Long runs cannot be compared bead by bead (device Philox vs the reference's sfc64 + ziggurat), so
-    the ensemble statistics are: radius of gyration per chain and the number of contacts, averaged over
-    replicas that start from the same configuration (10Mb ana/telophase model)."""
+    the ensemble statistics are: radius of gyration per chain, the number of contacts, and the CONTACT MAP
+    -- contacts binned into 16 x 16 blocks of 20 beads, the observable the paper compares with Hi-C -- averaged
+    over replicas that start from the same configuration (10Mb ana/telophase model).  Every block of the map
+    must agree within 5 standard errors and the blocks together must scatter like chi-square."""
     import ensemble as en
 
     scen = sc.genome_10mb(total=320, bend_energy=0.7)
     steps, r_gpu, r_cpu, contact = 1500, 192, 48, 0.25
 
-    def observables(xyz):
+    nbin, maps = 16, {}
+
+    def observables(xyz, tag=None):
         rg = en.radius_of_gyration(xyz, scen.chains).mean()
-        return rg, len(oracle.nsearch_pairs(bd.BOX_OPEN, None, scen.n, contact, xyz))
+        pairs = oracle.nsearch_pairs(bd.BOX_OPEN, None, scen.n, contact, xyz)
+        if tag is not None and len(pairs):
+            lo = np.minimum(pairs[:, 0], pairs[:, 1]) * nbin // scen.n
+            hi = np.maximum(pairs[:, 0], pairs[:, 1]) * nbin // scen.n
+            maps.setdefault(tag, []).append(np.bincount(lo * nbin + hi, minlength=nbin * nbin).astype(np.float64))
+        return rg, len(pairs)
 
     gpu = en.ReplicaEnsemble(engine, scen, r_gpu, seed=21)
     gpu.step(steps)
-    a = np.array([observables(x) for x in gpu.positions()])
+    a = np.array([observables(x, "gpu") for x in gpu.positions()])
     cpu = en.ReplicaEnsemble(oracle, scen, r_cpu, seed=5)
     cpu.step(steps)
-    b = np.array([observables(x) for x in cpu.positions()])
+    b = np.array([observables(x, "cpu") for x in cpu.positions()])
     start = np.array(observables(scen.positions[0]))
     for k, name in enumerate(("radius of gyration", "contacts")):
         err = np.sqrt(a[:, k].var(ddof=1) / r_gpu + b[:, k].var(ddof=1) / r_cpu)
         assert abs(a[:, k].mean() - b[:, k].mean()) < 4.5 * err, (name, a[:, k].mean(), b[:, k].mean(), err)
+    # the binned contact map, block by block
+    ma, mb = np.array(maps["gpu"]), np.array(maps["cpu"])
+    se = np.sqrt(ma.var(axis=0, ddof=1) / r_gpu + mb.var(axis=0, ddof=1) / r_cpu)
+    used = se > 0
+    assert used.sum() >= nbin  # at least the diagonal blocks carry contacts
+    zscore = (ma.mean(axis=0) - mb.mean(axis=0))[used] / se[used]
+    assert np.abs(zscore).max() < 5.0, (np.abs(zscore).max(), int(used.sum()))
+    assert abs((zscore ** 2).sum() - used.sum()) < 6.0 * np.sqrt(2.0 * used.sum()) + 0.15 * used.sum(), (zscore ** 2).sum()
     # the run did move the chains away from their start by far more than the resolution of the test
     assert abs(b[:, 0].mean() - start[0]) > 20 * np.sqrt(b[:, 0].var(ddof=1) / r_cpu)
     gpu.close()
