@@ -436,8 +436,15 @@ __device__ inline void cell_coords(const DParams &P, const DGrid &G, double x, d
 // shadow.  Open box: float offsets from the grid origin.  Periodic box: 32-bit fixed-point
 // fractions of the period, whose wrapping difference IS the minimum image.
 
-/* .w carries the bead's own slot (as bits): a kernel that reads a shadow from a staged shared-memory copy
- * (bd_step.cuh: tile staging) learns from it where the bead's fp64 record lives */
+/* .w carries a tag (as bits).  Staged engines: the bead's own slot -- a kernel that reads a shadow from a staged
+ * shared-memory copy (bd_step.cuh: tile staging) learns from it where the bead's fp64 record lives.  All other
+ * engines: the bead's class, which is all the single-precision pair walk (bd_step.cuh: WALK_F32) needs besides
+ * the coordinates. */
+__device__ __forceinline__ uint32_t shadow_tag(uint32_t staged, uint32_t slot, uint64_t w)
+{
+    return staged ? slot : w_type(w);
+}
+
 template <int BOX>
 __device__ __forceinline__ float4 make_shadow(const DParams &P, const DGrid &G, double x, double y, double z, uint32_t slot)
 {
@@ -478,6 +485,21 @@ __device__ __forceinline__ float shadow_dist2(const float4 &a, const float4 &b, 
         dz = a.z - b.z;
     }
     return fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+}
+
+/* the displacement a - b itself, in single precision (WALK_F32) */
+template <int BOX>
+__device__ __forceinline__ void shadow_delta(const float4 &a, const float4 &b, const float scale[3], float &dx, float &dy, float &dz)
+{
+    if (BOX == BD_BOX_PERIODIC) {
+        dx = (float) (int32_t) (__float_as_uint(a.x) - __float_as_uint(b.x)) * scale[0];
+        dy = (float) (int32_t) (__float_as_uint(a.y) - __float_as_uint(b.y)) * scale[1];
+        dz = (float) (int32_t) (__float_as_uint(a.z) - __float_as_uint(b.z)) * scale[2];
+    } else {
+        dx = a.x - b.x;
+        dy = a.y - b.y;
+        dz = a.z - b.z;
+    }
 }
 
 /* order-preserving map double -> u64 (for atomicMin/Max bounding boxes) */

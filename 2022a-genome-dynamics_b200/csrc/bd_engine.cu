@@ -95,6 +95,7 @@ struct bd_engine {
     DevBuf<uint4> nbr4;       // Verlet rows by thread position, ROW_PAD indices per group
     DevBuf<TileRuns> tile_runs;  // staged neighbourhood of every tile (bd_device.cuh: tile staging)
     bool staged = false;      // rows hold 16-bit staged positions (option "staged"); false = rows of slots, global gathers
+    bool pair_f32 = false;      // option "pair_precision" = 32: pair forces straight from the single-precision shadows
     bool balance_rows = false;  // tile threads ordered by row length (round 1) or in slot order (default)
     bool stage_auto = true;   // the block's staging capacity follows the largest tile (bd_set_option stage_capacity fixes it)
     uint32_t stage_cap = 512; // shadows a block of the step kernel stages
@@ -416,7 +417,7 @@ static int upload_words(bd_engine *h)
         h->d_point_mask.p, h->n, h->ntot);
     h->launches++;
     CK(cudaGetLastError());
-    return 0;
+    return request_rebuild(h);  // the shadows carry the class (bd_device.cuh: shadow_tag): the next build rewrites them
 }
 
 /* CSR adjacency of all bond / bend forcefields by original bead index */
@@ -690,7 +691,7 @@ static int scatter_tracked(bd_engine *h, const double *d_xyz, uint32_t first, ui
     if (upload_params(h)) return 1;
     k_scatter_tracked<<<blocks_for(count, 256), 256, 0, h->stream>>>(h->pos[h->cur].p, h->shadow[h->cur].p, h->bpos.p,
                                                                     h->slot_of.p, d_xyz, first, count, h->d_params.p,
-                                                                    h->ctl.p);
+                                                                    h->ctl.p, h->staged);
     h->launches++;
     CK(cudaGetLastError());
     return 0;
@@ -846,7 +847,7 @@ extern "C" int bd_scatter_positions_indexed(bd_engine *h, const uint32_t *d_inde
     if (upload_params(h)) return 1;
     k_scatter_indexed<<<blocks_for((uint32_t) count, 256), 256, 0, h->stream>>>(
         h->pos[h->cur].p, h->shadow[h->cur].p, h->bpos.p, h->slot_of.p, d_index, d_xyz, (uint32_t) count, h->d_params.p,
-        h->ctl.p);
+        h->ctl.p, h->staged);
     h->launches++;
     CK(cudaGetLastError());
     return 0;
@@ -1201,6 +1202,7 @@ static StepArrays step_arrays(bd_engine *h)
     A.nbr4 = h->nbr4.p;
     A.tile_runs = h->tile_runs.p;
     A.staged = h->staged;
+    A.pair_f32 = h->pair_f32 && !h->staged;
     A.stage_cap = h->stage_cap;
     A.plen = h->plen.p;
     A.bondrow = h->bondrow.p;
@@ -1923,6 +1925,11 @@ extern "C" int bd_set_option(bd_engine *h, const char *name, double value)
         CK(cudaMemset(&h->ctl.p->stage_overflow, 0, sizeof(uint32_t)));
         return request_rebuild(h);
     }
+    if (key == "pair_precision") {
+        if (value != 32 && value != 64) return fail("bd_set_option: pair_precision is 32 or 64");
+        h->pair_f32 = value == 32;
+        return 0;
+    }
     if (key == "balance_rows") {
         h->balance_rows = value != 0;
         return request_rebuild(h);
@@ -1970,6 +1977,7 @@ extern "C" int bd_get_option(bd_engine *h, const char *name, double *value)
     else if (key == "staged") *value = h->staged;
     else if (key == "step_graph") *value = h->use_graph;
     else if (key == "balance_rows") *value = h->balance_rows;
+    else if (key == "pair_precision") *value = h->pair_f32 ? 32 : 64;
     else if (key == "stage_capacity") *value = h->stage_cap;
     else if (key == "max_stage") {
         CK(cudaStreamSynchronize(h->stream));

@@ -342,8 +342,8 @@ __global__ void __launch_bounds__(NL_BLOCK) k_place(NlistArrays A)
         uint32_t const slot = b + rnk;
         A.bpos[slot] = rec;
         // nobody reads the shadow buffer during a rebuild: it can be rewritten in the new order here
-        A.shadow[slot] = P.box_kind == BD_BOX_PERIODIC ? make_shadow<BD_BOX_PERIODIC>(P, G, rec.x, rec.y, rec.z, slot)
-                                                       : make_shadow<BD_BOX_OPEN>(P, G, rec.x, rec.y, rec.z, slot);
+        A.shadow[slot] = P.box_kind == BD_BOX_PERIODIC ? make_shadow<BD_BOX_PERIODIC>(P, G, rec.x, rec.y, rec.z, shadow_tag(A.staged, slot, rec.w))
+                                                       : make_shadow<BD_BOX_OPEN>(P, G, rec.x, rec.y, rec.z, shadow_tag(A.staged, slot, rec.w));
         A.slot_of[(old / A.n) * A.n + mine] = slot;
     }
 }

@@ -38,6 +38,7 @@ struct StepArrays {
     const uint4 *nbr4;            // [cap / ROW_PAD][pstride] Verlet rows by thread position (bd_nlist.cuh)
     const TileRuns *tile_runs;    // [replicas * chunks] staged neighbourhoods (staged rows: uint2 groups of 16-bit positions)
     uint32_t staged, stage_cap;   // row format; shadows a block can stage (dynamic shared memory)
+    uint32_t pair_f32;            // pair forces from the single-precision shadows (option pair_precision = 32)
     uint32_t stage_off;           // byte offset of the staged shadows in the dynamic shared memory
     const uint32_t *plen;         // [pstride] row length at a position
     const uint2 *bondrow;         // [bond_deg][pstride] {partner slot, ff | second << 8}
@@ -267,8 +268,14 @@ constexpr uint32_t STAGE_TABLE_BYTES = (uint32_t) ((sizeof(TileRuns) + 15) & ~(s
 enum WalkMode {
     WALK_GLOBAL = 0,   // rows of slots, one 16-byte global gather per entry (engines that do not stage)
     WALK_STAGED = 1,   // rows of 16-bit staged positions, gathers from the tile's shared-memory copy
-    WALK_SPILLED = 2   // staged rows of a tile whose neighbourhood does not fit the block's shared memory:
+    WALK_SPILLED = 2,  // staged rows of a tile whose neighbourhood does not fit the block's shared memory:
                        // positions are translated back to slots through the run table (rare, slow, correct)
+    WALK_F32 = 3       // the mixed-precision production lane (north_star: "SoA float4 positions"): ONE phase, the
+                       // displacement is the difference of the 16-byte single-precision shadows (coordinates as
+                       // float offsets from the grid origin / 32-bit fractions of the period, class in .w), the
+                       // potential is evaluated in double on it and the force accumulated in double; no fp64
+                       // record of a neighbour is read.  Not the reference's arithmetic: forces agree to the
+                       // rounding of a float coordinate (stated and tested: tests/test_gpu_parity.py)
 };
 
 __device__ __forceinline__ float4 lds_f4(uint32_t addr)
@@ -303,7 +310,8 @@ __device__ __forceinline__ void pair_walk(const StepArrays &A, StepShared &sh, S
     const uint4 *col = A.nbr4 + pos;                                        // WALK_GLOBAL: four slots per group
     const uint2 *col2 = reinterpret_cast<const uint2 *>(A.nbr4) + pos;      // staged: four 16-bit positions
     uint32_t const stage = smem_addr(dyn_smem) + A.stage_off + STAGE_TABLE_BYTES;  // the tile's staged shadows
-    uint32_t const pad = MODE == WALK_GLOBAL ? 0u : tile_table(A).total;            // staged rows are padded with this position
+    constexpr bool SLOT_ROWS = MODE == WALK_GLOBAL || MODE == WALK_F32;             // rows of slots (uint4 groups)
+    uint32_t const pad = SLOT_ROWS ? 0u : tile_table(A).total;                      // staged rows are padded with this position
     // the thread's queue column and its row of the compiled pair table, as shared-space addresses
     constexpr uint32_t QSTEP = STEP_BLOCK * 4u;  // bytes between consecutive entries of one thread's queue
     uint32_t const queue = smem_addr(&sh.hits[0][threadIdx.x]);
@@ -311,7 +319,7 @@ __device__ __forceinline__ void pair_walk(const StepArrays &A, StepShared &sh, S
     uint32_t const cav = smem_addr(dyn_smem) + ti * (uint32_t) T * 8u;  // uniform tables: ca[T*T] then cb[T*T]
 
     auto fetch = [&](uint32_t out[ROW_PAD]) {
-        if (MODE == WALK_GLOBAL) {
+        if (SLOT_ROWS) {
             uint4 const g = stream_u4(col);
             out[0] = g.x; out[1] = g.y; out[2] = g.z; out[3] = g.w;
         } else {
@@ -319,6 +327,45 @@ __device__ __forceinline__ void pair_walk(const StepArrays &A, StepShared &sh, S
             out[0] = g.x & 0xffffu; out[1] = g.x >> 16; out[2] = g.y & 0xffffu; out[3] = g.y >> 16;
         }
     };
+    if (MODE == WALK_F32) {
+        float const dcut2f = __double2float_ru(dcut2 * (1.0 + 1e-6));
+        uint32_t jj[ROW_PAD], jjn[ROW_PAD];
+        if (m) fetch(jj);
+        for (uint32_t kk = 0; kk < m; kk += ROW_PAD) {
+            float4 q[ROW_PAD];
+#pragma unroll
+            for (int u = 0; u < (int) ROW_PAD; u++) q[u] = __ldg(A.shadow + jj[u]);
+            col += stride;
+            if (kk + ROW_PAD < m) fetch(jjn);
+#pragma unroll
+            for (int u = 0; u < (int) ROW_PAD; u++) {
+                float dx, dy, dz;
+                shadow_delta<BOX>(ms, q[u], scale, dx, dy, dz);
+                // the cut in single precision first (26 of 34 listed neighbours are out of range): NaN for the
+                // sentinel of the open box fails it
+                bool in = fmaf(dx, dx, fmaf(dy, dy, dz * dz)) <= dcut2f;
+                if (BOX == BD_BOX_PERIODIC) in = in && jj[u] < A.ntot;
+                double const rx = (double) dx, ry = (double) dy, rz = (double) dz;
+                double const r2 = rx * rx + ry * ry + rz * rz;
+                if (in && r2 <= dcut2) {
+                    uint32_t const at = cav + (__float_as_uint(q[u].w) & 0xffu) * 8u;
+                    double sc;
+                    if (A.k2_uniform) {
+                        sc = compiled_pair_scalar<PROG>(lds_f64(at), PROG == PROG_SC23_SC83 ? lds_f64(at + A.ntypes2 * 8u) : 0.0,
+                                                        A.k2a, A.k2b, r2);
+                    } else {
+                        const PairRow &row = mine[__float_as_uint(q[u].w) & 0xffu];
+                        sc = compiled_pair_scalar<PROG>(row.ca, row.cb, row.k2a, row.k2b, r2);
+                    }
+                    F.x += sc * rx; F.y += sc * ry; F.z += sc * rz;
+                    interactions += 1u;
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < (int) ROW_PAD; u++) jj[u] = jjn[u];
+        }
+        return;
+    }
     uint32_t k = 0;
     uint32_t j[ROW_PAD], jn[ROW_PAD];
     if (m) fetch(j);
@@ -409,7 +456,8 @@ __device__ __forceinline__ void pair_forces(const StepArrays &A, StepShared &sh,
         if (!any_pair) return;
     }
     // block-uniform choice
-    if (!A.staged) pair_walk<BOX, PROG, WALK_GLOBAL>(A, sh, sel, s, pos, me, F, interactions);
+    if (PROG != PROG_GENERIC && A.pair_f32) pair_walk<BOX, PROG, WALK_F32>(A, sh, sel, s, pos, me, F, interactions);
+    else if (!A.staged) pair_walk<BOX, PROG, WALK_GLOBAL>(A, sh, sel, s, pos, me, F, interactions);
     else if (sh.stage_ok) pair_walk<BOX, PROG, WALK_STAGED>(A, sh, sel, s, pos, me, F, interactions);
     else pair_walk<BOX, PROG, WALK_SPILLED>(A, sh, sel, s, pos, me, F, interactions);
 }
@@ -746,7 +794,7 @@ __device__ __forceinline__ double integrate_bead(const StepArrays &A, const DPar
     double x = me.x + mu_dt * F.x, y = me.y + mu_dt * F.y, z2 = me.z + mu_dt * F.z;
     x += 0.5 * (wx + px); y += 0.5 * (wy + py); z2 += 0.5 * (wz + pz);
     store_bead(A.pos_out + s, x, y, z2, me.w);
-    A.shadow_out[s] = make_shadow<BOX>(P, G, x, y, z2, s);
+    A.shadow_out[s] = make_shadow<BOX>(P, G, x, y, z2, shadow_tag(A.staged, s, me.w));
 
     bead4 const b0 = stream_bead(A.bpos + s);
     d3 const d = displacement_t<BOX>(P, x, y, z2, b0.x, b0.y, b0.z);
@@ -760,7 +808,7 @@ __device__ __forceinline__ double carry_ghost(const StepArrays &A, const DParams
                                               const bead4 &me)
 {
     store_bead(A.pos_out + s, me.x, me.y, me.z, me.w);
-    A.shadow_out[s] = make_shadow<BOX>(P, G, me.x, me.y, me.z, s);
+    A.shadow_out[s] = make_shadow<BOX>(P, G, me.x, me.y, me.z, shadow_tag(A.staged, s, me.w));
     bead4 const b0 = stream_bead(A.bpos + s);
     d3 const d = displacement_t<BOX>(P, me.x, me.y, me.z, b0.x, b0.y, b0.z);
     return sqnorm_exact(d.x, d.y, d.z);
@@ -1101,7 +1149,7 @@ __global__ void k_scatter_positions(bead4 *pos, const uint32_t *slot_of, const d
  * record and its shadow, and fold the displacement into the control block; k_rebuild_begin decides. */
 __global__ void k_scatter_tracked(bead4 *pos, float4 *shadow, const bead4 *bpos, const uint32_t *slot_of,
                                   const double *xyz, uint32_t first, uint32_t count, const DParams *params,
-                                  DControl *ctl)
+                                  DControl *ctl, uint32_t staged)
 {
     uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
     double moved2 = 0.0;
@@ -1114,10 +1162,10 @@ __global__ void k_scatter_tracked(bead4 *pos, float4 *shadow, const bead4 *bpos,
         bead4 const b0 = bpos[s];
         d3 d;
         if (params->box_kind == BD_BOX_PERIODIC) {
-            shadow[s] = make_shadow<BD_BOX_PERIODIC>(*params, ctl->grid, x, y, z, s);
+            shadow[s] = make_shadow<BD_BOX_PERIODIC>(*params, ctl->grid, x, y, z, shadow_tag(staged, s, b0.w));
             d = displacement_t<BD_BOX_PERIODIC>(*params, x, y, z, b0.x, b0.y, b0.z);
         } else {
-            shadow[s] = make_shadow<BD_BOX_OPEN>(*params, ctl->grid, x, y, z, s);
+            shadow[s] = make_shadow<BD_BOX_OPEN>(*params, ctl->grid, x, y, z, shadow_tag(staged, s, b0.w));
             d = displacement_t<BD_BOX_OPEN>(*params, x, y, z, b0.x, b0.y, b0.z);
         }
         moved2 = sqnorm_exact(d.x, d.y, d.z);
@@ -1169,7 +1217,7 @@ __global__ void k_gather_indexed(const bead4 *pos, const uint32_t *slot_of, cons
  * force evaluation (neighbor_list.hpp:132-158 looks at all points, whoever moved them). */
 __global__ void k_scatter_indexed(bead4 *pos, float4 *shadow, const bead4 *bpos, const uint32_t *slot_of,
                                   const uint32_t *idx, const double *xyz, uint32_t count, const DParams *params,
-                                  DControl *ctl)
+                                  DControl *ctl, uint32_t staged)
 {
     uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
     double moved2 = 0.0;
@@ -1182,10 +1230,10 @@ __global__ void k_scatter_indexed(bead4 *pos, float4 *shadow, const bead4 *bpos,
         bead4 const b0 = bpos[s];
         d3 d;
         if (params->box_kind == BD_BOX_PERIODIC) {
-            shadow[s] = make_shadow<BD_BOX_PERIODIC>(*params, ctl->grid, x, y, z, s);
+            shadow[s] = make_shadow<BD_BOX_PERIODIC>(*params, ctl->grid, x, y, z, shadow_tag(staged, s, b0.w));
             d = displacement_t<BD_BOX_PERIODIC>(*params, x, y, z, b0.x, b0.y, b0.z);
         } else {
-            shadow[s] = make_shadow<BD_BOX_OPEN>(*params, ctl->grid, x, y, z, s);
+            shadow[s] = make_shadow<BD_BOX_OPEN>(*params, ctl->grid, x, y, z, shadow_tag(staged, s, b0.w));
             d = displacement_t<BD_BOX_OPEN>(*params, x, y, z, b0.x, b0.y, b0.z);
         }
         moved2 = sqnorm_exact(d.x, d.y, d.z);

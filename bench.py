@@ -46,6 +46,7 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-mixed", action="store_true", help="skip the second, separately labelled mixed-precision line")
     ap.add_argument("--no-parity", action="store_true", help="skip the force / pair-set check against the reference")
     ap.add_argument("--chunks", type=int, default=8, help="e2e: engines (replica chunks) of the host pipeline")
     ap.add_argument("--frozen-walls", action="store_true",
@@ -346,7 +347,7 @@ def bind_near_gpu(torch, local):
     return out
 
 
-def parity_check(eng, sysm, scen, R, ids):
+def parity_check(eng, sysm, scen, R, ids, tol=1e-6):
     """Replica 0 and replica R-1 of the state about to be timed against the reference's own code (the
     unmodified micromd where oracle/_ref was built, else the CPU restatement): per-bead forces, and the
     Verlet pair set of a fresh list build on the same positions.  The checker is used as a checker only."""
@@ -375,7 +376,7 @@ def parity_check(eng, sysm, scen, R, ids):
         out["listed_pairs"] = int(len(b))
         fresh.close()
         ref.close()
-    if not (out["force_rel_err"] <= 1e-6 and out["pairs_equal"]):
+    if not (out["force_rel_err"] <= tol and out["pairs_equal"]):
         raise SystemExit(f"bench.py: parity check failed: {out}")
     return out
 
@@ -470,6 +471,30 @@ def run_b200(args):
     advance(min(args.steps, 50))
     kernel_ms = sysm.get_option("kernel_ms_avg")
     sysm.set_option("time_kernel", 0)
+    # a second, separately labelled line: the mixed-precision lane (pair displacements from the single-precision
+    # shadows, everything else fp64), same state, same steps; its force error against the reference is measured here
+    mixed = None
+    if not args.no_mixed and sysm.get_option("pair_program") != 0:
+        sysm.set_option("pair_precision", 32)
+        advance(5)
+        sysm.sync()
+        with torch.cuda.stream(stream):
+            m0, m1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            m0.record(stream)
+            advance(args.steps)
+            m1.record(stream)
+        barrier()
+        mixed_ms = m0.elapsed_time(m1)
+        sysm.set_option("time_kernel", 1)
+        advance(min(args.steps, 50))
+        mixed_kernel = sysm.get_option("kernel_ms_avg")
+        sysm.set_option("time_kernel", 0)
+        mixed = {"dtype": "f64 state and accumulation, f32 pair displacements (bd_set_option pair_precision=32)",
+                 "value": ntot * args.steps / (mixed_ms * 1e-3), "unit": "bead-steps/s (this rank)",
+                 "ms_per_step": mixed_ms / args.steps, "kernel_ms": mixed_kernel}
+        if rank == 0 and not args.no_parity:
+            mixed["force_rel_err_vs_reference"] = parity_check(eng, sysm, scen, R, ids, tol=1e-3)["force_rel_err"]
+        sysm.set_option("pair_precision", 64)
     sysm.get_all_positions(host.data_ptr())
     sysm.close()
 
@@ -564,6 +589,8 @@ def run_b200(args):
         }
         if parity:
             line["parity_check"] = parity
+        if mixed:
+            line["mixed_precision"] = mixed
         if slab_line:
             line["slab1kb"] = {k: slab_line[k] for k in ("value", "unit", "ms_per_step", "scaling", "steps", "halo_bytes_per_step",
                                                           "pair_interactions_per_s", "gpu_launches")}

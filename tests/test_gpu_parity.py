@@ -668,3 +668,37 @@ def test_row_length_ranking_is_an_option_with_the_same_results(engine, oracle):
         se.step(20, scen.timestep, scen.temperature, replay_normals=z)
         assert np.abs(se.get_positions() - so.get_positions()).max() <= TRAJ_TOL
         se.close()
+
+
+# ---- mixed-precision pair forces (engine option "pair_precision" = 32) -----------------------------------
+
+F32_FORCE_TOL = 5e-5   # of the largest force; measured 2e-6 .. 1e-5 on these systems (float coordinate offsets)
+F32_TRAJ_TOL = 5e-6    # 30 replayed steps, positions O(1..10): 30 x mobility x timestep x the force error
+
+
+@pytest.mark.parametrize("name", ["genome_100kb", "chromatin_1kb", "ab_box", "ab_sphere"])
+def test_single_precision_pair_walk_stays_within_its_stated_tolerance(engine, oracle, name):
+    """bd_set_option("pair_precision", 32): the production lane north_star describes ("SoA float4 positions") --
+    the displacement to a listed neighbour is the difference of the 16-byte single-precision shadows, nothing
+    else of the neighbour is read; potential and accumulation stay in double.  Not the reference's arithmetic:
+    the stated tolerance is the rounding of a float coordinate offset (2^-24 of the box extent) through the
+    stiff softcore<8,3>.  Bonded, wall and point forces stay exact; energies are always exact."""
+    scen = SMALL[name]()
+    se, _ = build(engine, scen)
+    so, _ = build(oracle, scen)
+    fo = so.compute_forces()
+    exact = rel_force_error(se.compute_forces(), fo)
+    se.set_option("pair_precision", 32)
+    assert se.get_option("pair_precision") == 32
+    err = rel_force_error(se.compute_forces(), fo)
+    assert exact <= FORCE_TOL < err <= F32_FORCE_TOL, (exact, err)   # it IS a different arithmetic, and a close one
+    assert se.compute_energy() == pytest.approx(so.compute_energy(), rel=ENERGY_TOL)
+    z = oracle.normals(31, 30 * scen.n * 3)
+    se.step(30, scen.timestep, scen.temperature, replay_normals=z)
+    so.step(30, scen.timestep, scen.temperature, replay_normals=z)
+    drift = np.abs(se.get_positions() - so.get_positions()).max()
+    print(f"pair_precision=32 {name}: force error {err:.2e} of the largest force, 30-step drift {drift:.2e}")
+    assert drift <= F32_TRAJ_TOL, drift
+    se.set_option("pair_precision", 64)
+    se.set_positions(so.get_positions())
+    assert rel_force_error(se.compute_forces(), so.compute_forces()) <= FORCE_TOL  # back on the exact lane
