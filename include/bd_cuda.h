@@ -167,6 +167,29 @@ int bd_refine_spline_device(const double *d_coarse, const int64_t *coarse_ranges
                             const int64_t *fine_ranges, const int64_t *attach, int64_t n_attach, int64_t n_coarse,
                             int64_t n_fine, double *d_fine, void *cuda_stream);
 
+/* bd_refine_spline_device for callers that cannot allocate device memory.  No counterpart in the reference
+ * (its refinement is a scipy script on the host); same arguments, same result as bd_refine_spline_device.
+ * Meant for a driver that refines while the card is already full -- the engines of the 100kb phase were created
+ * first, or a framework's caching allocator holds all free memory, so cudaMalloc would fail -- and for one that
+ * refines while other engines step on the same GPU, which every cudaMalloc / cudaFree would stall.  The spline
+ * workspace (second derivatives, sweep coefficients, the chain ranges and attachments) is a static array inside
+ * libbd_b200.so, BD_REFINE_NOALLOC_SCRATCH_BYTES on every GPU that loads the library, held until the process
+ * ends; the call never calls cudaMalloc, cudaFree or any allocating library routine.  A call larger than the
+ * limits below is refused with an error that names them (split it by chains, or use bd_refine_spline_device).
+ *   - The first call on a device looks up where that device keeps the array; make it from plain host code, before
+ *     beginning any stream capture, with the device of d_coarse / d_fine current.
+ *   - All calls on a device share the one array.  It keeps the previous call's contents, which is harmless (a call
+ *     writes every entry before reading it; nothing needs zeroing), but two calls that overlap on the GPU -- from
+ *     two threads or on two streams -- race and give wrong splines.  Calls from one thread are safe: each returns
+ *     after its work has finished. */
+#define BD_REFINE_NOALLOC_MAX_COARSE 65536 /* coarse points per call (a 10Mb genome has about 640) */
+#define BD_REFINE_NOALLOC_MAX_CHAINS 4096  /* chains per call */
+#define BD_REFINE_NOALLOC_MAX_ATTACH 4096  /* {nor, nuc} attachments per call */
+#define BD_REFINE_NOALLOC_SCRATCH_BYTES 3342336 /* 2 x 3 x 65536 doubles + 2 x 2 x 4096 + 2 x 4096 int64 */
+int bd_refine_spline_device_noalloc(const double *d_coarse, const int64_t *coarse_ranges, int64_t n_chains, int32_t factor,
+                                    const int64_t *fine_ranges, const int64_t *attach, int64_t n_attach, int64_t n_coarse,
+                                    int64_t n_fine, double *d_fine, void *cuda_stream);
+
 /* All replicas at once through HOST buffers laid out [n_replicas][n_beads][3] (original bead order);
  * with pinned buffers the copies are asynchronous on the engine's stream.  bd_get_all_positions
  * returns after the data has arrived. */
