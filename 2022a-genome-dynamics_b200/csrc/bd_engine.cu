@@ -75,6 +75,16 @@ struct DevBuf {
     }
 };
 
+/* a DevBuf local to one call: released when the call returns, whichever way (engine members stay plain DevBufs,
+ * released by bd_destroy) */
+template <typename T>
+struct ScopedBuf : DevBuf<T> {
+    ScopedBuf() = default;
+    ScopedBuf(const ScopedBuf &) = delete;
+    ScopedBuf &operator=(const ScopedBuf &) = delete;
+    ~ScopedBuf() { this->release(); }
+};
+
 struct HostFF {
     bool used = false;
     int nterms = 0;
@@ -1679,6 +1689,10 @@ extern "C" int bd_step(bd_engine *h, const bd_step_config *cfg)
         }
         bool const graphed = h->use_graph && !adaptive && !replay && !h->time_kernel && !h->bond_rows_stale;
         if (!graphed && enqueue_rebuild_chain(h)) return 1;
+        // step_arrays reads what upload_params derives (pair program, uniform k2, compiled bond rows): bring the
+        // parameters up to date first on the graph path too (tests/test_gpu_graph.py caught a stale first step
+        // after bd_set_ff_enabled)
+        if (graphed && upload_params(h)) return 1;
         StepArrays const A = step_arrays(h);
         S.step = cfg->first_step + k;
         S.dt = cfg->timestep;
@@ -2532,15 +2546,24 @@ extern "C" int bd_glue_update(bd_engine *h, int32_t bond_ff, int32_t replica, do
     if (h->replicas != 1) return fail("bd_glue_update: the pair lists of an ensemble are shared; one replica per engine");
     if (!(max_distance > 0) || !(p_bind >= 0 && p_bind <= 1) || !(p_unbind >= 0 && p_unbind <= 1) || max_glues < 0)
         return fail("bd_glue_update: bad parameters");
-    if (upload_params(h)) return 1;
-    cudaStream_t const st = h->stream;
     std::vector<uint32_t> &list = h->bond_pairs[bond_ff];
     size_t const m = list.size() / 2;
+    if (max_glues == 0) {
+        // glue_simulator::update returns before unbond when there is no capacity (glue_simulator.cpp:37-39):
+        // the list, whatever it holds, is left alone
+        if (unbound_out) *unbound_out = 0;
+        if (bound_out) *bound_out = 0;
+        if (count_out) *count_out = (int64_t) m;
+        return 0;
+    }
+    if (upload_params(h)) return 1;
+    cudaStream_t const st = h->stream;
 
     // ---- unbond ----------------------------------------------------------------------------------
-    DevBuf<uint32_t> d_pairs;
-    DevBuf<unsigned long long> keys, kept, sorted, d_count;
-    DevBuf<uint8_t> flags;
+    // scratch of this call: freed on every way out, the early error returns of CK included
+    ScopedBuf<uint32_t> d_pairs;
+    ScopedBuf<unsigned long long> keys, kept, sorted, d_count;
+    ScopedBuf<uint8_t> flags;
     CK(d_count.alloc(1));
     unsigned long long nkept = 0;
     size_t need = 0;
@@ -2573,8 +2596,8 @@ extern "C" int bd_glue_update(bd_engine *h, int32_t bond_ff, int32_t replica, do
     // ---- bond ------------------------------------------------------------------------------------
     unsigned long long found = 0, naccepted = 0;
     size_t const capacity = (size_t) max_glues > nkept ? (size_t) max_glues - (size_t) nkept : 0;
-    DevBuf<unsigned long long> ckeys, ctags, akeys, atags, skeys, stags;
-    DevBuf<uint8_t> accept;
+    ScopedBuf<unsigned long long> ckeys, ctags, akeys, atags, skeys, stags;
+    ScopedBuf<uint8_t> accept;
     if (capacity && p_bind > 0) {
         if (search_current(h, replica, max_distance, use_box != 0, &found)) return 1;
     }
@@ -2618,10 +2641,6 @@ extern "C" int bd_glue_update(bd_engine *h, int32_t bond_ff, int32_t replica, do
     if (nkept) CK(cudaMemcpyAsync(out.data(), sorted.p, nkept * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
     if (nbound) CK(cudaMemcpyAsync(out.data() + nkept, chosen, nbound * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
-    for (auto *b : {&keys, &kept, &sorted, &d_count, &ckeys, &ctags, &akeys, &atags, &skeys, &stags}) b->release();
-    d_pairs.release();
-    flags.release();
-    accept.release();
     list.resize(2 * out.size());
     for (size_t k = 0; k < out.size(); k++) {
         list[2 * k] = (uint32_t) (out[k] >> 32);

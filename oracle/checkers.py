@@ -17,7 +17,6 @@ import bdb200  # noqa: E402
 
 ORACLE_LIB = os.path.join(ROOT, "oracle", "liboracle.so")
 REFERENCE_LIB = os.path.join(ROOT, "oracle", "_ref", "libmicromd_ref.so")
-REFERENCE_FAST_LIB = os.path.join(ROOT, "oracle", "_ref", "libmicromd_fast.so")
 
 _cache = {}
 
@@ -100,3 +99,48 @@ class DriverC4:
         if self.h:
             self.lib.drv_c4_destroy(self.h)
             self.h = None
+
+
+# ---- 3-sim-1kb's kinetic glue model, the unmodified class (oracle/ref_glue.cc + the reference's glue_simulator.cpp) ----
+
+GLUE_LIB = os.path.join(ROOT, "oracle", "_ref", "libglue_ref.so")
+
+
+def have_reference_glue() -> bool:
+    return os.path.exists(GLUE_LIB)
+
+
+class ReferenceGlue:
+    """glue_simulator of the 1kb chromatin driver with its own std::mt19937_64; CHECKER of bd_glue_update only."""
+
+    def __init__(self, max_glues, max_distance, binding_rate, unbinding_rate, period, seed):
+        lib = _C.CDLL(GLUE_LIB)
+        lib.ref_glue_create.restype = _C.c_void_p
+        lib.ref_glue_create.argtypes = [_C.c_uint64, _C.c_double, _C.c_double, _C.c_double, _C.c_void_p, _C.c_uint64]
+        lib.ref_glue_destroy.argtypes = [_C.c_void_p]
+        lib.ref_glue_update.restype = _C.c_int64
+        lib.ref_glue_update.argtypes = [_C.c_void_p, _C.c_double, _C.c_void_p, _C.c_int64]
+        lib.ref_glue_pairs.restype = _C.c_int64
+        lib.ref_glue_pairs.argtypes = [_C.c_void_p, _C.c_void_p, _C.c_int64]
+        self.lib = lib
+        box = _np.ascontiguousarray(period, dtype=_np.float64)
+        self.h = lib.ref_glue_create(int(max_glues), float(max_distance), float(binding_rate), float(unbinding_rate),
+                                     box.ctypes.data, int(seed))
+
+    def update(self, timestep, xyz) -> int:
+        x = _np.ascontiguousarray(xyz, dtype=_np.float64).reshape(-1, 3)
+        return self.lib.ref_glue_update(self.h, float(timestep), x.ctypes.data, len(x))
+
+    def pairs(self) -> "_np.ndarray":
+        n = self.lib.ref_glue_pairs(self.h, None, 0)
+        out = _np.zeros((max(n, 1), 2), dtype=_np.uint32)
+        self.lib.ref_glue_pairs(self.h, out.ctypes.data, n)
+        return out[:n]
+
+    def close(self):
+        if self.h:
+            self.lib.ref_glue_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
