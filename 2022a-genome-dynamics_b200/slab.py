@@ -327,6 +327,10 @@ class DistExchange:
         # stalls everybody's next exchange.
         if not hasattr(slab, "_moved"):
             slab._moved = _device_int64(system.displacement_pointer(), self.device)
+            # the all-reduce must act on the engine's own word; a silent copy would leave the ranks rebuilding on
+            # their own schedules with no error
+            if slab._moved.data_ptr() != system.displacement_pointer():
+                raise RuntimeError("slab: the displacement tensor does not alias the engine's memory")
         self.dist.all_reduce(slab._moved, op=self.dist.ReduceOp.MAX)
 
 

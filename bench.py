@@ -557,11 +557,21 @@ def run_b200(args):
             peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)"
         else:
             peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-        traffic, traffic_src = None, None
+        traffic, traffic_src, binding_unit = None, None, None
         tp = os.path.join(ROOT, "profiles", "roofline_traffic.json")
         if os.path.exists(tp) and args.workload == "genome100kb" and R == 64:
+            # a number from a committed ncu capture, NOT measured in this run: shown only while the step kernel's
+            # sources are byte-for-byte the ones that were profiled, so that it cannot go stale unnoticed
             tj = json.load(open(tp))
-            traffic, traffic_src = tj.get("k_step_fused_dram_bytes_per_launch"), tj.get("source")
+            import hashlib
+            digest = hashlib.sha256()
+            for src in tj.get("kernel_sources", []):
+                digest.update(open(os.path.join(ROOT, src), "rb").read())
+            if tj.get("kernel_sources") and digest.hexdigest() == tj.get("kernel_sources_sha256"):
+                traffic, traffic_src = tj.get("k_step_fused_dram_bytes_per_launch"), tj.get("source")
+                binding_unit = tj.get("binding_unit")
+            else:
+                traffic_src = "dropped: the step kernel's sources changed since " + str(tj.get("captured_at_commit"))
         achieved = ALGO_BYTES_PER_BEAD_STEP * ntot / (kernel_ms * 1e-3) / 1e9 if kernel_ms > 0 else 0.0
         value = world * ntot * args.steps / (ms * 1e-3)
         line = {
@@ -582,7 +592,8 @@ def run_b200(args):
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                         "frac": achieved / peak, "traffic": traffic, "traffic_from_profile_at": traffic_src,
+                         "binding_unit": binding_unit,
                          "kernel": "k_step_fused",
                          "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": ALGO_BYTES_PER_BEAD_STEP * ntot,
                          "peak_source": peak_src},

@@ -210,7 +210,9 @@ int bd_get_all_positions_async(bd_engine *h, double *xyz);
 int bd_noise_statistics(uint64_t seed, int64_t first_step, int64_t steps, int64_t beads, int32_t replica,
                         int32_t device, double *out, int32_t out_len);
 
-/* Number of kernels launched by this engine since creation (bench.py "gpu_launches"). */
+/* Number of kernels launched by this engine since creation (bench.py "gpu_launches").  Not a cheap getter: the
+ * rebuild kernels inside the step graph's conditional node are counted on the device, so the call WAITS for the
+ * engine's stream before it reads that count. */
 int bd_get_launch_count(bd_engine *h, int64_t *out);
 
 #ifdef __cplusplus
