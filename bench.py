@@ -606,6 +606,7 @@ def run_b200(args):
             line["slab1kb"] = {k: slab_line[k] for k in ("value", "unit", "ms_per_step", "scaling", "steps", "halo_bytes_per_step",
                                                           "pair_interactions_per_s", "gpu_launches")}
             line["slab1kb"]["workload"] = slab_line["config"]["workload"]
+            line["slab1kb"]["parity_check"] = slab_line.get("parity_check")
             line["slab1kb"]["parallelism"] = slab_line["config"]["parallelism"]
         if semi_now:
             line["config"]["wall_semiaxes_replica0_after_timed_region"] = semi_now
@@ -727,6 +728,41 @@ def run_slab(args, embedded=False):
         ms, inter, halo_bytes, launches = tmax[0].item(), tsum[1].item(), tsum[2].item(), tsum[3].item()
     else:
         inter, launches = t[1].item(), t[3].item()
+    slab_parity = None
+    if world > 1:
+        # In-run check of the decomposed trajectory (outside the timed region): the ranks carry on for a few steps
+        # from the state the timed region left; rank 0 replays the same steps on ONE engine that holds the whole
+        # system.  Philox is keyed by (seed, step, bead), so both see the same noise; forces differ in summation
+        # order only.  A short stretch, because rounding differences grow along a chaotic trajectory.
+        V, tol = 32, 1e-9
+        before = slab.gather_owned(sl, ex)
+        first = sl.steps_done + 1
+        slab.run_distributed(sl, ex, V, dt, kT, seed)
+        after = slab.gather_owned(sl, ex)
+        rebuilds = torch.tensor([float(sysm.get_counters().list_rebuilds)], dtype=torch.float64, device="cuda")
+        rmin, rmax = rebuilds.clone(), rebuilds.clone()
+        dist.all_reduce(rmin, op=dist.ReduceOp.MIN)
+        dist.all_reduce(rmax, op=dist.ReduceOp.MAX)
+        bad = torch.zeros(1, dtype=torch.float64, device="cuda")
+        if rank == 0:
+            whole = bd.System(eng, scen.n, 1, device=local)
+            scen.apply(whole)
+            if args.verlet_factor:
+                whole.set_option("verlet_factor", args.verlet_factor)
+            whole.step(1, dt, kT, seed=seed)  # one throw-away step: the engine then knows the previous timestep
+            whole.set_positions(before)
+            whole.step(V, dt, kT, seed=seed, first_step=first)
+            want = whole.get_positions()
+            whole.close()
+            slab_parity = {"max_dx": float(np.abs(after - want).max()), "moved": float(np.abs(want - before).max()),
+                           "steps": V, "from_step": first, "ranks": world, "tolerance": tol,
+                           "list_rebuilds_equal_on_all_ranks": bool(rmin.item() == rmax.item())}
+            if not (slab_parity["max_dx"] <= tol and slab_parity["moved"] > 100 * tol
+                    and slab_parity["list_rebuilds_equal_on_all_ranks"]):
+                bad += 1
+        dist.all_reduce(bad)
+        if bad.item():
+            raise SystemExit(f"bench.py: slab parity check failed: {slab_parity}")
     if rank == 0:
         line = {
             "metric": "bead_steps_per_s", "value": scen.n * K / (ms * 1e-3), "unit": "bead-steps/s", "n_gpus": world,
@@ -740,6 +776,8 @@ def run_slab(args, embedded=False):
             "pair_interactions_per_s": inter / (ms * 1e-3), "gpu_launches": int(launches),
             "halo_bytes_per_step": halo_bytes / K, "clocks": clocks,
         }
+        if slab_parity:
+            line["parity_check"] = slab_parity
         if not embedded:
             print(json.dumps(line), flush=True)
     sysm.close()

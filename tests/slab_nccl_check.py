@@ -51,6 +51,16 @@ def main():
         ok = err < 1e-9 and moved > 1e-3
         print(f"slab_nccl_check world={world} beads={scen.n} steps={steps} max|dx|={err:.3e} moved={moved:.3e} "
               f"halo_bytes_per_step={sl.halo_bytes_sent / steps:.0f} {'OK' if ok else 'MISMATCH'}", flush=True)
+    # one rebuild decision for the whole system (slab.DistExchange.halo all-reduces the engines' displacement word in
+    # place): every rank must have rebuilt its list the same number of times
+    rebuilds = torch.tensor([float(s.get_counters().list_rebuilds)], dtype=torch.float64, device=dev)
+    lo, hi = rebuilds.clone(), rebuilds.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    if lo.item() != hi.item():
+        ok = False
+        if rank == 0:
+            print(f"slab_nccl_check: list rebuild counts differ between ranks ({lo.item():.0f} .. {hi.item():.0f})", flush=True)
     flag = torch.tensor([0 if ok else 1], device=dev)
     dist.all_reduce(flag)
     dist.destroy_process_group()
