@@ -56,6 +56,8 @@ def parse():
                     "e.g. under ncu)")
     ap.add_argument("--staged", type=int, default=None, help="engine option staged (tile staging of the pair walk) after the relaxation")
     ap.add_argument("--stage-capacity", type=int, default=None, help="engine option stage_capacity")
+    ap.add_argument("--pair-precision", type=int, default=None, choices=[32, 64],
+                    help="engine option pair_precision for the MAIN line (profiling the mixed lane; the default line is 64)")
     ap.add_argument("--workload", default="genome100kb", choices=sorted(WORKLOADS) + ["slab1kb"],
                     help="genome100kb: the headline replica ensemble (weak scaling); ab_box / ab_sphere / genome10mb / "
                          "chromatin1kb: the other BASELINE.json configurations on one engine per GPU; slab1kb: ONE 1kb "
@@ -439,6 +441,8 @@ def run_b200(args):
         sysm.set_option("staged", args.staged)
     if args.stage_capacity is not None:
         sysm.set_option("stage_capacity", args.stage_capacity)
+    if args.pair_precision is not None:
+        sysm.set_option("pair_precision", args.pair_precision)
     advance(max(args.warmup, 3))
     sysm.sync()
     if args.staged:
@@ -446,7 +450,7 @@ def run_b200(args):
               "staged", sysm.get_option("staged"), file=sys.stderr)
     parity = None
     if rank == 0 and not args.no_parity:
-        parity = parity_check(eng, sysm, scen, R, ids)
+        parity = parity_check(eng, sysm, scen, R, ids, tol=5e-5 if args.pair_precision == 32 else 1e-6)
     c0 = sysm.get_counters()
     l0 = sysm.get_launch_count()
     sampler = ClockSampler(local)
@@ -577,7 +581,8 @@ def run_b200(args):
         line = {
             "metric": "bead_steps_per_s", "value": value, "unit": "bead-steps/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64" if args.pair_precision != 32 else "f64 state and accumulation, f32 pair displacements",
             "data": "synthetic",
             "config": {"workload": workload_name(args, scen), "beads_per_replica": n, "replicas_per_gpu": R,
                        "timestep": dt, "temperature": kT, "noise": "philox4x32-10",

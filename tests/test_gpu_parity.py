@@ -343,16 +343,13 @@ def test_empty_system(engine):
     assert s.compute_energy() == 0.0
 
 
-def test_statistical_equivalence_with_reference_noise(engine, oracle):
+def ensemble_statistics_agree(engine, oracle, scen, steps, r_gpu, r_cpu, contact, moved_observable):
     """Long runs cannot be compared bead by bead (device Philox vs the reference's sfc64 + ziggurat), so
     the ensemble statistics are: radius of gyration per chain, the number of contacts, and the CONTACT MAP
-    -- contacts binned into 16 x 16 blocks of 20 beads, the observable the paper compares with Hi-C -- averaged
-    over replicas that start from the same configuration (10Mb ana/telophase model).  Every block of the map
+    -- contacts binned into 16 x 16 blocks of n / 16 beads, the observable the paper compares with Hi-C -- averaged
+    over replicas that start from the same configuration.  Every block of the map
     must agree within 5 standard errors and the blocks together must scatter like chi-square."""
     import ensemble as en
-
-    scen = sc.genome_10mb(total=320, bend_energy=0.7)
-    steps, r_gpu, r_cpu, contact = 1500, 192, 48, 0.25
 
     nbin, maps = 16, {}
 
@@ -384,9 +381,26 @@ def test_statistical_equivalence_with_reference_noise(engine, oracle):
     assert np.abs(zscore).max() < 5.0, (np.abs(zscore).max(), int(used.sum()))
     assert abs((zscore ** 2).sum() - used.sum()) < 6.0 * np.sqrt(2.0 * used.sum()) + 0.15 * used.sum(), (zscore ** 2).sum()
     # the run did move the chains away from their start by far more than the resolution of the test
-    assert abs(b[:, 0].mean() - start[0]) > 20 * np.sqrt(b[:, 0].var(ddof=1) / r_cpu)
+    k = moved_observable
+    assert abs(b[:, k].mean() - start[k]) > 20 * np.sqrt(b[:, k].var(ddof=1) / r_cpu)
     gpu.close()
     cpu.close()
+
+
+def test_statistical_equivalence_with_reference_noise(engine, oracle):
+    """the 10Mb ana/telophase model (320 beads, blocks of 20 beads), 1500 steps"""
+    ensemble_statistics_agree(engine, oracle, sc.genome_10mb(total=320, bend_energy=0.7), steps=1500, r_gpu=192, r_cpu=48,
+                              contact=0.25, moved_observable=0)
+
+
+@pytest.mark.slow
+def test_statistical_equivalence_on_the_100kb_model(engine, oracle):
+    """the 100kb interphase model -- the one the paper compares with Hi-C -- at 3 060 beads in its ellipsoid (46 chains,
+    nucleoli, both walls): 400 steps take the overlapping start to a quarter fewer contacts; radius of gyration,
+    contact count and the 16 x 16 contact map of 96 device replicas against 16 replicas of the CPU restatement with
+    the reference's own generator"""
+    ensemble_statistics_agree(engine, oracle, sc.genome_100kb(3000, 30), steps=400, r_gpu=96, r_cpu=16, contact=0.36,
+                              moved_observable=1)
 
 
 @pytest.mark.gpu
